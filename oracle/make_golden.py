@@ -1,0 +1,150 @@
+"""Generate tests/golden/*.npz by running the reference's own Krylov files UNMODIFIED
+(/root/reference, imported by path) over the numpy stand-in of the NGSolve la layer
+(oracle/ngs_standin).  Run in the build container only; the GPU box has no /root/reference.
+
+    python oracle/make_golden.py
+
+Fixtures hold: solver outputs (histories, iteration counts, solutions), the injected lambda_min,
+and a fingerprint of the assembled inputs so a drifting assembler is detected by the tests.
+"""
+import contextlib
+import importlib.util
+import io
+import os
+import re
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "ngs_standin"))   # the stand-in named `ngsolve`
+sys.path.insert(0, os.path.dirname(HERE))
+
+import ngsolve  # noqa: E402  (stand-in)
+from ngsolve import BaseVector, BlockVector, BlockMatrix, SparseMatrix, DiagonalMatrix  # noqa: E402
+from ngsolve import la as ngla  # noqa: E402
+from oracle.cases import Case, GOLDEN_DIR  # noqa: E402
+
+REF = os.environ.get("NSB_REFERENCE", "/root/reference")
+
+
+def load_ref(relpath, name):
+    spec = importlib.util.spec_from_file_location(name, os.path.join(REF, relpath))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+ref_minres = load_ref("minres.py", "ref_minres")
+ref_bpcg1 = load_ref("bramble_pasciak_cg.py", "ref_bpcg1")
+ref_bpcg2 = load_ref("solvers/bramblepasciak_new.py", "ref_bpcg2")
+ref_orth = load_ref("orthonormalization.py", "ref_orth")
+ref_rk = load_ref("runge_kutta_method.py", "ref_rk")
+
+
+def quiet(fn, *a, **k):
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        out = fn(*a, **k)
+    return out, buf.getvalue()
+
+
+def gold_minres(mesh, initialize, tol, maxsteps, use_pre=True, tag=""):
+    c = Case(mesh)
+    A, B = SparseMatrix(c.A), SparseMatrix(c.B)
+    K = BlockMatrix([[A, B.T], [B, None]])                               # run.py:45
+    C = BlockMatrix([[DiagonalMatrix(c.dA), None], [None, DiagonalMatrix(c.dM)]]) if use_pre else None
+    rhs = BlockVector([BaseVector(c.f.copy()), BaseVector(c.g.copy())])
+    gfu, gfp = BaseVector(c.u0.copy()), BaseVector(np.zeros(c.n_p))
+    sol = BlockVector([gfu, gfp])
+    (u, errors), _ = quiet(ref_minres.MinRes, mat=K, pre=C, rhs=rhs, sol=sol, initialize=initialize,
+                           tol=tol, maxsteps=maxsteps)                   # run.py:52
+    assert u is sol
+    name = "minres_%s%s" % (mesh, tag)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, name), errors=np.array(errors), sol=sol.NumPy().copy(),
+                        gfu=gfu.NumPy().copy(), fingerprint=c.fingerprint(),
+                        args=np.array([float(initialize), tol, maxsteps, float(use_pre)]))
+    print(name, "iterations", len(errors) - 1, "final", errors[-1])
+
+
+def gold_bpcg(mesh, tol, maxsteps, tag=""):
+    c = Case(mesh)
+    lam = c.lam_min()
+    A, B = SparseMatrix(c.A), SparseMatrix(c.B)
+    preA, preM = DiagonalMatrix(c.dA), DiagonalMatrix(c.dM)
+    # ---- v1  (stokes_hcurldiv.py:75-77, run.py:33-38)
+    gfu, gfp = BaseVector(c.u0.copy()), BaseVector(np.zeros(c.n_p))
+    solution = BlockVector([gfu, gfp])
+    ngla.inject_eigenvalues([lam, 1.0])
+    (sol1, errors1), _ = quiet(ref_bpcg1.bramble_pasciak_cg, A, B, None, preA, preM,
+                               BaseVector(c.f.copy()), BaseVector(c.g.copy()), solution=solution,
+                               tolerance=tol, max_steps=maxsteps)
+    # ---- v2  (templates/NavierStokesSIMPLE_iterative.py:397)
+    class Blf:
+        def __init__(self, m):
+            self.mat = m
+            self.condense = False
+    gfu2, gfp2 = BaseVector(c.u0.copy()), BaseVector(np.zeros(c.n_p))
+    sol2 = BlockVector([gfu2, gfp2])
+    ngla.inject_eigenvalues([lam, 1.0])
+    (it2, secs), out = quiet(ref_bpcg2.BramblePasciakCG, Blf(A), Blf(B), None, BaseVector(c.f.copy()),
+                             BaseVector(c.g.copy()), preA, preM, sol2, initialize=False, tol=tol,
+                             maxsteps=maxsteps, rel_err=True)
+    hist2 = [float(m.group(2)) for m in re.finditer(r"it =\s+(\d+)\s+err =\s+(\S+)", out)]
+    err0 = float(re.search(r"err0 (\S+)", out).group(1))
+    name = "bpcg_%s%s" % (mesh, tag)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, name), lam_min=lam, errors_v1=np.array(errors1),
+                        sol_v1=sol1.NumPy().copy(), it_v2=it2, hist_v2=np.array(hist2), err0_v2=err0,
+                        sol_v2=sol2.NumPy().copy(), fingerprint=c.fingerprint(),
+                        args=np.array([tol, maxsteps]))
+    print(name, "v1 passes", len(errors1), "v2 it", it2, "hist", len(hist2), "lam_min", lam)
+
+
+def gold_orth():
+    rng = np.random.default_rng(7)
+    n, m = 777, 5
+    base = rng.standard_normal((m, n))
+    base[3] = base[0] * 0.5 + 1e-3 * base[3]      # nearly dependent column: exercises the 3 sweeps
+    basis = [BaseVector(base[i].copy()) for i in range(m)]
+    out = ref_orth.orthonormalize(basis)
+    assert out is basis
+    Q = np.stack([b.NumPy() for b in basis])
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "orthonormalize"), input=base, Q=Q)
+    print("orthonormalize", np.abs(Q @ Q.T - np.eye(m)).max())
+
+
+def gold_rk():
+    out = {}
+    for deg in (3, 10):
+        w = ref_rk.ImplicitRungeKuttaMethodWeights(deg)                  # heat.py:76 uses 10
+        out["a%d" % deg] = w.a.NumPy().copy()
+        out["b%d" % deg] = w.b.NumPy().copy()
+        out["c%d" % deg] = np.array(w.c)
+        rng = np.random.default_rng(deg)
+        Msym = rng.standard_normal((5, 5))
+        evo = -(Msym @ Msym.T) - np.eye(5)
+        y = rng.standard_normal(5)
+        nxt = ref_rk.linear_implicit_runge_kutta_step(w, ngsolve.Matrix(evo.copy()), ngsolve._DVec(y.copy()), 0.01)
+        out["evo%d" % deg] = evo
+        out["y%d" % deg] = y
+        out["next%d" % deg] = nxt.NumPy().copy()
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "runge_kutta"), **out)
+    print("runge_kutta ok")
+
+
+if __name__ == "__main__":
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    gold_minres("sq8", initialize=False, tol=1e-7, maxsteps=10000)
+    gold_minres("sq8", initialize=True, tol=1e-7, maxsteps=10000, tag="_init")
+    gold_minres("sq8", initialize=False, tol=1e-7, maxsteps=40, tag="_cap40")          # non-convergence exit
+    gold_minres("sq8", initialize=True, tol=1e-3, maxsteps=10000, use_pre=False, tag="_nopre")
+    gold_minres("sq20", initialize=False, tol=1e-7, maxsteps=10000)                    # config 1
+    gold_minres("chan2d", initialize=False, tol=1e-7, maxsteps=10000)
+    gold_minres("chan3d", initialize=False, tol=1e-7, maxsteps=10000)
+    gold_bpcg("sq8", tol=1e-10, maxsteps=10000)
+    gold_bpcg("sq8", tol=1e-12, maxsteps=10000, tag="_floor")   # tolerance at the rounding floor: count is chaotic
+    gold_bpcg("chan2d", tol=1e-10, maxsteps=10000)
+    gold_bpcg("chan3d", tol=1e-10, maxsteps=100000)
+    gold_bpcg("sq8", tol=1e-12, maxsteps=25, tag="_cap25")
+    gold_orth()
+    gold_rk()

@@ -1,0 +1,24 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def cases():
+    from oracle.cases import Case
+    cache = {}
+
+    def get(mesh):
+        if mesh not in cache:
+            cache[mesh] = Case(mesh)
+        return cache[mesh]
+    return get
