@@ -1,0 +1,155 @@
+/* nsb200.h -- C ABI of the B200-native Krylov solve path (libnsb200.so).
+ *
+ * The reference (matschiner/navier-stokes-solver) is pure Python over NGSolve and has no FFI of its
+ * own; its boundary for this path is the Python signature of each solver plus NGSolve's duck-typed
+ * operator/vector protocol.  This header is the C boundary a binding for that path
+ * has to bind: every entry point names the reference interface (file:line under the reference tree)
+ * it replaces.  The Python mirror of the reference signatures lives in
+ * navier-stokes-solver_b200/{la,solvers}.py and calls these functions through ctypes.
+ *
+ * Conventions
+ *   - all functions return NSB_OK (0) or a negative error code; nsb_last_error() gives the text
+ *     of the last failure on the calling thread.  No C++ exception crosses this boundary.
+ *   - "const double* / double*" vector arguments may be HOST or DEVICE pointers (resolved through
+ *     unified virtual addressing).  Host buffers are copied in at the start of a call and results
+ *     are copied back into the same caller buffer before the call returns (the reference mutates
+ *     `sol` in place: minres.py:50,118; bramble_pasciak_cg.py:131; solvers/bramblepasciak_new.py:137,228).
+ *   - matrices are fp64 CSR with int32 column indices; row pointers may be given as int32 or int64.
+ *   - one CUDA stream per context; a context is used by one host thread at a time (the reference's
+ *     solvers are single-caller, SURVEY.md 8(b) "Threading").
+ *   - distributed contexts (one process per GPU) row-partition every operator; vectors passed to the
+ *     solvers then hold the rank's OWNED rows only.
+ */
+#ifndef NSB200_H
+#define NSB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define NSB_API __attribute__((visibility("default")))
+#else
+#define NSB_API
+#endif
+
+#define NSB_OK 0
+#define NSB_ERR_INVALID -1   /* bad argument */
+#define NSB_ERR_CUDA -2      /* CUDA runtime failure */
+#define NSB_ERR_NCCL -3      /* NCCL failure / NCCL not loadable */
+#define NSB_ERR_BREAKDOWN -4 /* non-finite or zero pivot in a recurrence */
+#define NSB_ERR_UNSUPPORTED -5
+
+/* solver exit status (written to *status) */
+#define NSB_CONVERGED 0        /* left through the relative-tolerance break */
+#define NSB_MAXSTEPS 1         /* loop condition ended the iteration: step cap  (minres.py:96,145; bramble_pasciak_cg.py:144; bramblepasciak_new.py:248) */
+#define NSB_ABSTOL 2           /* MinRes only: loop condition ended on the absolute test ResNorm > tol (minres.py:96) */
+#define NSB_ZERO_RESIDUAL 3    /* BramblePasciakCG early return when <w,d> == 0 (bramblepasciak_new.py:191-192) */
+#define NSB_BREAKDOWN 4        /* a reduced scalar became non-finite; iteration stopped */
+
+typedef struct nsb_ctx_s* nsb_ctx;
+typedef struct nsb_mat_s* nsb_mat;
+typedef struct nsb_pre_s* nsb_pre;
+typedef struct nsb_halo_s* nsb_halo;
+
+/* ---- library / context ------------------------------------------------------------------- */
+NSB_API int nsb_version(void);
+NSB_API const char* nsb_last_error(void);
+
+/* Single-GPU context on CUDA device `device`. */
+NSB_API int nsb_ctx_create(int device, nsb_ctx* out);
+/* Row-partitioned context: rank `rank` of `nranks`, NCCL communicator bootstrapped from a 128-byte
+ * unique id obtained on rank 0 with nsb_nccl_unique_id() and broadcast by the caller
+ * (torch.distributed in the Python host).  No reference counterpart (the reference is
+ * single-process: SURVEY.md 2, 8(e)). */
+NSB_API int nsb_nccl_unique_id(char out[128]);
+NSB_API int nsb_ctx_create_dist(int device, int rank, int nranks, const char unique_id[128], nsb_ctx* out);
+NSB_API int nsb_ctx_destroy(nsb_ctx ctx);
+NSB_API int nsb_ctx_sync(nsb_ctx ctx);
+/* raw cudaStream_t of the context (for callers that order their own device work against it) */
+NSB_API void* nsb_ctx_stream(nsb_ctx ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches claim) */
+NSB_API int64_t nsb_ctx_launch_count(nsb_ctx ctx);
+/* capture the per-iteration kernel sequence in CUDA graphs (default on for single-GPU contexts) */
+NSB_API int nsb_ctx_set_graphs(nsb_ctx ctx, int enabled);
+
+/* ---- operators: replaces NGSolve SparseMatrix / BilinearForm.mat (run.py:106,
+ *      stokes_hcurldiv.py:76, solvers/bramblepasciak_new.py:108-109) -------------------------- */
+NSB_API int nsb_csr_create(nsb_ctx ctx, int64_t rows, int64_t cols, int64_t nnz, const void* rowptr,
+                   int rowptr_bits /*32|64*/, const int32_t* colidx, const double* values, nsb_mat* out);
+/* explicit transpose, built once on the device (matB.CreateTranspose(), bramblepasciak_new.py:198; b.T, run.py:45) */
+NSB_API int nsb_csr_transpose(nsb_ctx ctx, nsb_mat a, nsb_mat* out);
+/* K = [[A, BT], [B, C]] as ONE merged CSR so A and B^T are applied in a single pass
+ * (BlockMatrix([[a, b.T], [b, None]]) run.py:45; bramble_pasciak_cg.py:77-78).  BT may be NULL (built by
+ * transposition); C may be NULL. */
+NSB_API int nsb_saddle_create(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_mat C, nsb_mat* out);
+NSB_API int nsb_mat_destroy(nsb_mat m);
+NSB_API int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz);
+/* main diagonal of a square (or owned-square) operator, length rows */
+NSB_API int nsb_mat_diagonal(nsb_ctx ctx, nsb_mat m, double* out);
+/* y = M x   (the `mat * vec` primitive, e.g. minres.py:97).  x has `cols`, y has `rows` entries. */
+NSB_API int nsb_spmv(nsb_ctx ctx, nsb_mat m, const double* x, double* y);
+/* device-timed SpMV micro-benchmark on resident vectors: `reps` launches after `warmup`, average
+ * milliseconds per launch by CUDA events on the context's stream. */
+NSB_API int nsb_spmv_bench(nsb_ctx ctx, nsb_mat m, int warmup, int reps, double* ms_per_launch);
+
+/* Row-partition support: attach the halo plan of a row-partitioned operator whose column indices
+ * are renumbered [owned | halo].  send_idx lists, per neighbour, the owned entries to ship;
+ * the halo tail is filled neighbour by neighbour in `neighbors` order.   */
+NSB_API int nsb_halo_create(nsb_ctx ctx, int64_t n_owned, int64_t n_halo, int n_neighbors, const int32_t* neighbors,
+                    const int64_t* send_counts, const int32_t* send_idx, const int64_t* recv_counts, nsb_halo* out);
+NSB_API int nsb_halo_destroy(nsb_halo h);
+NSB_API int nsb_mat_set_halo(nsb_mat m, nsb_halo h);
+
+/* ---- preconditioners: replaces Preconditioner(bf, 'local') and block smoothers
+ *      (run.py:61-62, stokes_hcurldiv.py:53, NavierStokesSIMPLE_iterative.py:199,360-373) -------- */
+/* y = d .* x with caller-supplied d (already inverted; zero on constrained dofs) */
+NSB_API int nsb_pre_create_diag(nsb_ctx ctx, int64_t n, const double* d, nsb_pre* out);
+/* Jacobi from the operator's diagonal; free_mask (n bytes, 1 = free) may be NULL */
+NSB_API int nsb_pre_create_jacobi(nsb_ctx ctx, nsb_mat m, const uint8_t* free_mask, nsb_pre* out);
+/* block-diagonal of two diagonal preconditioners: BlockMatrix([[preA, None], [None, preS]]) (run.py:46) */
+NSB_API int nsb_pre_create_blockdiag2(nsb_ctx ctx, nsb_pre a, nsb_pre b, nsb_pre* out);
+NSB_API int nsb_pre_destroy(nsb_pre p);
+NSB_API int nsb_pre_apply(nsb_ctx ctx, nsb_pre p, const double* x, double* y);
+
+/* ---- solvers ------------------------------------------------------------------------------- */
+/* MinRes(mat, rhs, pre, sol, maxsteps, printrates, initialize, tol)   minres.py:12-149.
+ * history: capacity maxsteps+1, history[0] = 1.0, one relative entry per iteration (minres.py:95,125).
+ * iterations = number of entries written minus one.  pre may be NULL (minres.py:68,101). */
+NSB_API int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs, double* sol, int maxsteps, double tol,
+               int initialize, double* history, int* iterations, double* seconds, int* status);
+
+/* Bramble-Pasciak CG engine serving both reference variants:
+ *   mode 2: BramblePasciakCG(blfA, blfB, matC, f, g, preA_unscaled, preM, sol, tol, maxsteps, printrates,
+ *           initialize, rel_err)      solvers/bramblepasciak_new.py:24-253   (update, then test the previous error)
+ *   mode 1: bramble_pasciak_cg(a, b, c, pre_a, pre_schur, upper_rhs, lower_rhs, solution, tolerance,
+ *           max_steps, print_rates)   bramble_pasciak_cg.py:65-148            (test, then update)
+ * k_scale is the factor k = 1/lambda_min + 1e-3 (bramble_pasciak_cg.py:71; bramblepasciak_new.py:118).
+ * sol holds (u, p) contiguously.  history[i] = sqrt|<w,d>| before update i (capacity maxsteps+1);
+ * updates = number of solution updates performed; err0 = history[0]. */
+NSB_API int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre preA, nsb_pre preM, double k_scale,
+             const double* f, const double* g, double* sol, int maxsteps, double tol, int initialize, int rel_err,
+             int mode, double* history, int* updates, double* seconds, int* status);
+
+/* Preconditioned CG with NGSolve CGSolver's stopping rule sqrt<Cr,r> <= tol * initial
+ * (CGSolver(mstar, pre, precision=1e-4) NavierStokesSIMPLE_iterative.py:93,128; stands in for the direct
+ * heat.mat.Inverse of heat.py:72).  history: absolute errors, capacity maxsteps+1. */
+NSB_API int nsb_cg(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* rhs, double* sol, int maxsteps, double tol,
+           int initialize, double* history, int* iterations, double* seconds, int* status);
+
+/* Extreme eigenvalues of pre*A by CG-Lanczos (EigenValues_Preconditioner(mat, pre, tol):
+ * bramble_pasciak_cg.py:70, bramblepasciak_new.py:115).  start (length rows) may be NULL: the
+ * deterministic vector 1 + 0.5 sin(i+1) is used.  Stops when lambda_min moved < tol relative. */
+NSB_API int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* start, int maxsteps, double tol,
+                             double* lam_min, double* lam_max, int* steps);
+
+/* orthonormalize(basis, tries=3)   orthonormalization.py:5-16: modified Gram-Schmidt, `tries` sweeps,
+ * in place.  basis = m vectors of length n stored one after another (stride n). */
+NSB_API int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int tries);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NSB200_H */

@@ -1,0 +1,365 @@
+// bpcg.cu -- Bramble-Pasciak CG, device-resident engine for both reference variants:
+//   solvers/bramblepasciak_new.py:24-253 (mode 2) and bramble_pasciak_cg.py:65-148 (mode 1; same iterates,
+//   SURVEY.md 8(c)(iii)).  The iteration is v2's (one A apply per step, A*s0 and A*w0 by recurrence):
+//   B1  SpMV B^T s1, row epilogue:  As0 = beta As0 + z0 ; tmp0 = As0 + B^T s1 ; tmp1 = k dA tmp0 ;
+//                                   tmp4 = tmp1 - s0                                   (:205-209,:212)
+//   B2  SpMV A tmp1 -> tmp2,        fused  sum s0 (tmp2 - tmp0)                        (:210,:218,:222)
+//   B3  SpMV B tmp4 -> tmp3,        fused  sum s1 tmp3            -> alpha             (:213,:219,:222,:226)
+//   B4  u += a s ; d -= a v ; w0 -= a tmp1 ; w1 -= a dM tmp3 ; z0 -= a tmp2,  fused <w,d> -> beta, err, exit (:228-247)
+//   B5  s = beta s + w                                                                 (:240-241)
+// z_old of :215 is folded away: beta*As0 + z_old - alpha*tmp2 == beta*As0 + z0(after :238).
+// Traffic beyond the three SpMVs: 8*(24 n_u + 13 n_p) bytes per iteration.
+// Only diagonal preA / preM are fused here (the reference's BDDC / AMG live in NGSolve: BASELINE.md 4).
+#include <math.h>
+
+#include "spmv.cuh"
+
+namespace nsb {
+
+struct BpcgState {
+    double k, wd, wdn, alpha, beta, as_part, err0, tol_abs;
+    double red[3];
+    int it, maxsteps, stop, mode, status, nupd;
+};
+
+__device__ void bpcg_after_as(BpcgState* S, double part_u, double part_p) {
+    const double as_s = part_u + part_p;   // :222
+    S->alpha = S->wd / as_s;               // :226
+    if (!isfinite(S->alpha)) {
+        S->stop = 1;
+        S->status = NSB_BREAKDOWN;
+    }
+}
+
+__device__ void bpcg_after_wd(BpcgState* S, double wdn, double* hist) {
+    const int it = S->it;
+    const double wd = S->wd;
+    S->wdn = wdn;                          // :235
+    S->beta = wdn / wd;                    // :236
+    S->nupd = it + 1;
+    const double err_next = sqrt(fabs(wdn));
+    hist[it + 1] = err_next;
+    if (!isfinite(wdn)) {
+        S->stop = 1;
+        S->status = NSB_BREAKDOWN;
+        return;
+    }
+    if (S->mode == 2) {
+        const double err = sqrt(fabs(wd));                   // :243  (value from before this update)
+        if (err < S->tol_abs) { S->stop = 1; S->status = NSB_CONVERGED; }          // :246
+        else if (it + 1 >= S->maxsteps) { S->stop = 1; S->status = NSB_MAXSTEPS; } // :248
+    } else {
+        if (it + 1 >= S->maxsteps) { S->stop = 1; S->status = NSB_MAXSTEPS; }      // bramble_pasciak_cg.py:110,144
+        else if (err_next < S->tol_abs) { S->stop = 1; S->status = NSB_CONVERGED; } // bramble_pasciak_cg.py:119
+    }
+    S->it = it + 1;
+    S->wd = wdn;                           // :221
+}
+
+__global__ void k_bpcg_scalar(BpcgState* S, int which, double* hist) {
+    if (S->stop) return;
+    if (which == 0) bpcg_after_as(S, S->red[0], S->red[1]);
+    else bpcg_after_wd(S, S->red[2], hist);
+}
+
+struct BpcgB1Op {
+    BpcgState* S;
+    double* __restrict__ As0;
+    const double* __restrict__ z0;
+    const double* __restrict__ dA;
+    const double* __restrict__ s0;
+    double* __restrict__ tmp0;
+    double* __restrict__ tmp1;
+    double* __restrict__ tmp4;
+    __device__ bool skip() const { return S->stop != 0; }
+    __device__ void row(int64_t i, double ax, double (&)[1]) const {
+        const double as0 = S->beta * As0[i] + z0[i];
+        const double t0 = as0 + ax;
+        const double t1 = S->k * (dA[i] * t0);
+        As0[i] = as0;
+        tmp0[i] = t0;
+        tmp1[i] = t1;
+        tmp4[i] = t1 - s0[i];
+    }
+    __device__ void finish(const double (&)[1]) const {}
+};
+
+struct BpcgB2Op {
+    BpcgState* S;
+    double* __restrict__ tmp2;
+    const double* __restrict__ tmp0;
+    const double* __restrict__ s0;
+    bool fused;
+    __device__ bool skip() const { return S->stop != 0; }
+    __device__ void row(int64_t i, double ax, double (&acc)[1]) const {
+        tmp2[i] = ax;
+        acc[0] = fma(s0[i], ax - tmp0[i], acc[0]);
+    }
+    __device__ void finish(const double (&tot)[1]) const {
+        if (fused) S->as_part = tot[0];
+        else S->red[0] = tot[0];
+    }
+};
+
+struct BpcgB3Op {
+    BpcgState* S;
+    double* __restrict__ tmp3;
+    const double* __restrict__ s1;
+    bool fused;
+    __device__ bool skip() const { return S->stop != 0; }
+    __device__ void row(int64_t j, double ax, double (&acc)[1]) const {
+        tmp3[j] = ax;
+        acc[0] = fma(s1[j], ax, acc[0]);
+    }
+    __device__ void finish(const double (&tot)[1]) const {
+        if (fused) bpcg_after_as(S, S->as_part, tot[0]);
+        else S->red[1] = tot[0];
+    }
+};
+
+struct BpcgVecs {
+    double *u0, *u1, *d0, *d1, *w0, *w1, *s0, *s1, *z0;
+    const double *tmp0, *tmp1, *tmp2, *tmp3, *dM;
+    int64_t n_u, n_p;
+};
+
+__global__ void __launch_bounds__(kBlock) k_bpcg_b4(BpcgState* S, BpcgVecs V, double* hist, double* partials,
+                                                    unsigned int* ticket, bool fused) {
+    if (S->stop) return;
+    const double a = S->alpha;
+    double acc[1] = {0.0};
+    const int64_t n = V.n_u + V.n_p;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (i < V.n_u) {
+            const double t2 = V.tmp2[i];
+            V.u0[i] += a * V.s0[i];                         // :228
+            const double d = V.d0[i] + (-a) * (t2 - V.tmp0[i]);   // :229 with v0 = tmp2 - tmp0 (:218)
+            const double w = V.w0[i] + (-a) * V.tmp1[i];    // :232
+            V.d0[i] = d;
+            V.w0[i] = w;
+            V.z0[i] -= a * t2;                              // :238
+            acc[0] = fma(w, d, acc[0]);
+        } else {
+            const int64_t j = i - V.n_u;
+            const double t3 = V.tmp3[j];
+            V.u1[j] += a * V.s1[j];
+            const double d = V.d1[j] + (-a) * t3;           // :229 with v1 = tmp3 (:219)
+            const double w = V.w1[j] + (-a) * (V.dM ? V.dM[j] * t3 : t3);   // :233
+            V.d1[j] = d;
+            V.w1[j] = w;
+            acc[0] = fma(w, d, acc[0]);
+        }
+    }
+    if (grid_sum<1>(acc, partials, ticket)) {
+        if (threadIdx.x == 0) {
+            if (fused) bpcg_after_wd(S, acc[0], hist);
+            else S->red[2] = acc[0];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_bpcg_b5(const BpcgState* S, BpcgVecs V) {
+    if (S->stop) return;
+    const double b = S->beta;
+    const int64_t n = V.n_u + V.n_p;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (i < V.n_u) V.s0[i] = b * V.s0[i] + V.w0[i];     // :240-241
+        else V.s1[i - V.n_u] = b * V.s1[i - V.n_u] + V.w1[i - V.n_u];
+    }
+}
+
+__global__ void k_bpcg_init_scalar(BpcgState* S, double k, double wdn_u, const double* wdn_dev, int maxsteps, double tol,
+                                   int rel_err, int mode, double* hist) {
+    const double wdn = wdn_dev[0] + wdn_dev[1];   // :185
+    (void)wdn_u;
+    S->k = k;
+    S->wdn = wdn;
+    S->wd = wdn;
+    S->alpha = 0.0;
+    S->beta = 0.0;                        // first pass: As0 = 0*As0 + z0 = A s0 (:202-203)
+    S->as_part = 0.0;
+    S->err0 = sqrt(fabs(wdn));            // :187
+    S->tol_abs = tol * (rel_err ? S->err0 : 1.0);   // :246
+    S->it = 0;
+    S->maxsteps = maxsteps;
+    S->mode = mode;
+    S->nupd = 0;
+    S->stop = 0;
+    S->status = NSB_MAXSTEPS;
+    hist[0] = S->err0;
+    if (wdn == 0.0) { S->stop = 1; S->status = NSB_ZERO_RESIDUAL; }           // :191-192
+    else if (!isfinite(wdn)) { S->stop = 1; S->status = NSB_BREAKDOWN; }
+    else if (maxsteps <= 0) { S->stop = 1; S->status = NSB_MAXSTEPS; }
+    else if (mode == 1 && S->err0 < S->tol_abs) { S->stop = 1; S->status = NSB_CONVERGED; }
+}
+
+// y = M x with the halo exchange the operator needs
+static int apply(Context& c, nsb_mat_s* m, double* x, double* y) {
+    NSB_CHECK(halo_exchange(c, m->halo, x));
+    return spmv_plain(c, m, x, y);
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre preA, nsb_pre preM, double k_scale,
+                        const double* f, const double* g, double* sol, int maxsteps, double tol, int initialize,
+                        int rel_err, int mode, double* history, int* updates, double* seconds, int* status) {
+    NSB_REQUIRE(ctx && A && B && BT && preA && f && g && sol && history, "nsb_bpcg: NULL argument");
+    NSB_REQUIRE(mode == 1 || mode == 2, "nsb_bpcg: mode must be 1 or 2");
+    NSB_REQUIRE(isfinite(k_scale) && k_scale > 0.0, "nsb_bpcg: k_scale must be positive and finite");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    const int64_t n_u = A->rows, n_p = B->rows;
+    const int64_t nxu = A->cols, nxp = BT->cols;
+    NSB_REQUIRE(B->cols == nxu, "nsb_bpcg: B has %lld columns, A has %lld", (long long)B->cols, (long long)nxu);
+    NSB_REQUIRE(BT->rows == n_u, "nsb_bpcg: BT must have n_u rows");
+    NSB_REQUIRE(preA->n == n_u, "nsb_bpcg: preA size mismatch");
+    if (preM) NSB_REQUIRE(preM->n == n_p, "nsb_bpcg: preM size mismatch");
+    NSB_REQUIRE(maxsteps >= 0, "nsb_bpcg: maxsteps < 0");
+    const bool fused = c.nranks == 1;
+    const double* dA = preA->d.p;
+    const double* dM = preM ? preM->d.p : nullptr;
+
+    DevBuf<double> u0, u1, d0, d1, w0, w1, s0, s1, z0, As0, tmp0, tmp1, tmp2, tmp3, tmp4, df, dg, fnew, gnew, hist;
+    DevBuf<BpcgState> st;
+    for (DevBuf<double>* b : {&u0, &s0, &tmp0, &tmp1, &tmp4}) NSB_CHECK(b->alloc(nxu));
+    for (DevBuf<double>* b : {&d0, &w0, &z0, &As0, &tmp2, &df, &fnew}) NSB_CHECK(b->alloc(n_u));
+    for (DevBuf<double>* b : {&u1, &s1}) NSB_CHECK(b->alloc(nxp));
+    for (DevBuf<double>* b : {&d1, &w1, &tmp3, &dg, &gnew}) NSB_CHECK(b->alloc(n_p > 0 ? n_p : 1));
+    NSB_CHECK(hist.alloc(maxsteps + 2));
+    NSB_CHECK(st.alloc(1));
+    BpcgState* S = st.p;
+
+    // ---- set-up, solvers/bramblepasciak_new.py:124-189 (not condensed)
+    NSB_CHECK(copy_in(c, df.p, f, n_u));
+    NSB_CHECK(copy_in(c, dg.p, g, n_p));
+    NSB_CHECK(vec_diagmul(c, tmp0.p, 1.0, dA, df.p, n_u));                       // preA_unscaled f
+    NSB_CHECK(vec_lincomb(c, tmp0.p, k_scale, tmp0.p, 0, nullptr, 0, nullptr, n_u));   // k * (.)   :122,:129
+    NSB_CHECK(apply(c, A, tmp0.p, fnew.p));
+    NSB_CHECK(vec_lincomb(c, fnew.p, 1.0, fnew.p, -1.0, df.p, 0, nullptr, n_u));  // :130
+    NSB_CHECK(apply(c, B, tmp0.p, gnew.p));
+    NSB_CHECK(vec_lincomb(c, gnew.p, 1.0, gnew.p, -1.0, dg.p, 0, nullptr, n_p));  // :133  (== tmp5, :177)
+    NSB_CHECK(vec_lincomb(c, w0.p, 1.0, tmp0.p, 0, nullptr, 0, nullptr, n_u));    // pr0 (:173) parked in w0
+    if (initialize) {                                                              // :138-139
+        NSB_CHECK(vec_set(c, u0.p, 0.0, nxu));
+        NSB_CHECK(vec_set(c, u1.p, 0.0, nxp));
+    } else {
+        NSB_CHECK(copy_in(c, u0.p, sol, n_u));
+        NSB_CHECK(copy_in(c, u1.p, sol + n_u, n_p));
+    }
+    NSB_CHECK(apply(c, A, u0.p, tmp0.p));                                          // :160
+    NSB_CHECK(apply(c, BT, u1.p, tmp2.p));
+    NSB_CHECK(vec_lincomb(c, tmp0.p, 1.0, tmp0.p, 1.0, tmp2.p, 0, nullptr, n_u));
+    NSB_CHECK(vec_diagmul(c, tmp1.p, 1.0, dA, tmp0.p, n_u));                       // :162
+    NSB_CHECK(vec_lincomb(c, tmp1.p, k_scale, tmp1.p, 0, nullptr, 0, nullptr, n_u));
+    NSB_CHECK(apply(c, A, tmp1.p, tmp2.p));                                        // :163
+    NSB_CHECK(vec_lincomb(c, tmp4.p, 1.0, tmp1.p, -1.0, u0.p, 0, nullptr, n_u));   // :165
+    NSB_CHECK(apply(c, B, tmp4.p, tmp3.p));                                        // :166
+    NSB_CHECK(vec_lincomb(c, d0.p, 1.0, fnew.p, -1.0, tmp2.p, 1.0, tmp0.p, n_u)); // :169
+    NSB_CHECK(vec_lincomb(c, d1.p, 1.0, gnew.p, -1.0, tmp3.p, 0, nullptr, n_p));  // :170
+    NSB_CHECK(vec_lincomb(c, w0.p, 1.0, w0.p, -1.0, tmp1.p, 0, nullptr, n_u));    // :182
+    NSB_CHECK(vec_lincomb(c, gnew.p, 1.0, gnew.p, -1.0, tmp3.p, 0, nullptr, n_p)); // tmp5 - tmp3
+    NSB_CHECK(vec_diagmul(c, w1.p, 1.0, dM, gnew.p, n_p));                         // :179,:183 (preM linear)
+    NSB_CHECK(vec_dot(c, w0.p, d0.p, n_u, &S->red[0]));                            // :185
+    NSB_CHECK(vec_dot(c, w1.p, d1.p, n_p, &S->red[1]));
+    k_bpcg_init_scalar<<<1, 1, 0, c.stream>>>(S, k_scale, 0.0, S->red, maxsteps, tol, rel_err, mode, hist.p);
+    c.launches++;
+    NSB_CHECK(vec_lincomb(c, s0.p, 1.0, w0.p, 0, nullptr, 0, nullptr, n_u));      // :189
+    NSB_CHECK(vec_lincomb(c, s1.p, 1.0, w1.p, 0, nullptr, 0, nullptr, n_p));
+    NSB_CHECK(apply(c, A, s0.p, As0.p));                                           // :202
+    NSB_CHECK(vec_lincomb(c, z0.p, 1.0, As0.p, 0, nullptr, 0, nullptr, n_u));     // :203
+
+    cudaEvent_t e0, e1;
+    NSB_CUDA(cudaEventCreate(&e0));
+    NSB_CUDA(cudaEventCreate(&e1));
+    NSB_CUDA(cudaEventRecord(e0, c.stream));                                       // timer_its (:195-196)
+
+    BpcgVecs V{u0.p, u1.p, d0.p, d1.p, w0.p, w1.p, s0.p, s1.p, z0.p, tmp0.p, tmp1.p, tmp2.p, tmp3.p, dM, n_u, n_p};
+    const int vg = vec_grid(n_u + n_p, c.num_sms);
+    auto launch_iteration = [&]() -> int {
+        NSB_CHECK(halo_exchange(c, BT->halo, s1.p));
+        NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, tmp0.p, tmp1.p, tmp4.p}));
+        // tmp1 and tmp4 travel in the velocity halo
+        NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
+        NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
+        NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
+        NSB_CHECK(spmv_launch<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, fused}));
+        if (!fused) {
+            NSB_CHECK(allreduce_sum(c, &S->red[0], 2));
+            k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
+            c.launches++;
+        }
+        k_bpcg_b4<<<vg, kBlock, 0, c.stream>>>(S, V, hist.p, c.partials, c.ticket, fused);
+        c.launches++;
+        if (!fused) {
+            NSB_CHECK(allreduce_sum(c, &S->red[2], 1));
+            k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
+            c.launches++;
+        }
+        k_bpcg_b5<<<vg, kBlock, 0, c.stream>>>(S, V);
+        c.launches++;
+        NSB_CUDA(cudaGetLastError());
+        return NSB_OK;
+    };
+
+    int* h_flags = (int*)c.h_mail;
+    h_flags[0] = 0;
+    const int chunk = (n_u + n_p) < 200000 ? 16 : 4;   // iterations in flight between host checks
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t gexec = nullptr;
+    int64_t graph_launches = 0;
+    int rc = NSB_OK;
+    if (c.use_graphs && maxsteps > 0) {
+        const int64_t before = c.launches;
+        NSB_CUDA(cudaStreamBeginCapture(c.stream, cudaStreamCaptureModeThreadLocal));
+        for (int j = 0; j < chunk && rc == NSB_OK; ++j) rc = launch_iteration();
+        cudaError_t ce = cudaStreamEndCapture(c.stream, &graph);
+        graph_launches = c.launches - before;
+        c.launches = before;
+        if (rc == NSB_OK && ce != cudaSuccess) {
+            set_error("nsb_bpcg: graph capture failed: %s", cudaGetErrorString(ce));
+            rc = NSB_ERR_CUDA;
+        }
+        if (rc == NSB_OK) NSB_CUDA(cudaGraphInstantiate(&gexec, graph, 0));
+    }
+    int launched = 0;
+    while (rc == NSB_OK && launched < maxsteps) {
+        if (gexec) {
+            cudaError_t ge = cudaGraphLaunch(gexec, c.stream);
+            if (ge != cudaSuccess) {
+                set_error("nsb_bpcg: graph launch failed: %s", cudaGetErrorString(ge));
+                rc = NSB_ERR_CUDA;
+            }
+            c.launches += graph_launches;
+        } else {
+            for (int j = 0; j < chunk && rc == NSB_OK; ++j) rc = launch_iteration();
+        }
+        launched += chunk;
+        if (rc != NSB_OK) break;
+        NSB_CUDA(cudaMemcpyAsync(h_flags, &S->stop, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+        NSB_CUDA(cudaStreamSynchronize(c.stream));
+        if (h_flags[0]) break;
+    }
+    if (gexec) cudaGraphExecDestroy(gexec);
+    if (graph) cudaGraphDestroy(graph);
+    NSB_CHECK(rc);
+
+    NSB_CUDA(cudaEventRecord(e1, c.stream));
+    BpcgState hs;
+    NSB_CUDA(cudaMemcpyAsync(&hs, S, sizeof(BpcgState), cudaMemcpyDeviceToHost, c.stream));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    NSB_CHECK(copy_out(c, sol, u0.p, n_u));
+    NSB_CHECK(copy_out(c, sol + n_u, u1.p, n_p));
+    NSB_CHECK(copy_out(c, history, hist.p, hs.nupd + 1));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    if (updates) *updates = hs.nupd;
+    if (seconds) *seconds = (double)ms * 1e-3;
+    if (status) *status = hs.status;
+    return NSB_OK;
+}

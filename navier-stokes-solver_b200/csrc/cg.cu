@@ -1,0 +1,446 @@
+// cg.cu -- preconditioned CG, CG-Lanczos eigenvalue estimate and modified Gram-Schmidt.
+//   nsb_cg            NGSolve CGSolver as used at templates/NavierStokesSIMPLE_iterative.py:93,128 and the
+//                     Jacobi-CG that stands in for heat.mat.Inverse (heat.py:72)
+//   nsb_lanczos_eigs  EigenValues_Preconditioner (bramble_pasciak_cg.py:70; solvers/bramblepasciak_new.py:115)
+//   nsb_orthonormalize  orthonormalization.py:5-16
+// CG iteration = 3 kernels:  C1 SpMV q = A s, fused <s,q> -> alpha ;  C2 u += a s, d -= a q, w = C d,
+// fused <w,d> -> beta, err, exit ;  C3 s = beta s + w.
+#include <math.h>
+
+#include <algorithm>
+
+#include "spmv.cuh"
+
+namespace nsb {
+
+struct CgState {
+    double wd, wdn, alpha, beta, err0, tol_abs;
+    double red[2];
+    int it, maxsteps, stop, status, record;
+};
+
+__device__ void cg_after_as(CgState* S, double as_s, double* alphas) {
+    S->alpha = S->wd / as_s;
+    if (alphas) alphas[S->it] = S->alpha;
+    if (!isfinite(S->alpha)) { S->stop = 1; S->status = NSB_BREAKDOWN; }
+}
+
+__device__ void cg_after_wd(CgState* S, double wdn, double* hist, double* betas) {
+    const int it = S->it;
+    S->wdn = wdn;
+    S->beta = wdn / S->wd;
+    if (betas) betas[it] = S->beta;
+    const double err = sqrt(fabs(wdn));
+    if (hist) hist[it + 1] = err;
+    S->it = it + 1;
+    S->wd = wdn;
+    if (!isfinite(wdn) || (betas && wdn <= 0.0)) { S->stop = 1; S->status = NSB_BREAKDOWN; return; }
+    if (!betas && err <= S->tol_abs) { S->stop = 1; S->status = NSB_CONVERGED; }
+    else if (it + 1 >= S->maxsteps) { S->stop = 1; S->status = NSB_MAXSTEPS; }
+}
+
+__global__ void k_cg_scalar(CgState* S, int which, double* hist, double* alphas, double* betas) {
+    if (S->stop) return;
+    if (which == 0) cg_after_as(S, S->red[0], alphas);
+    else cg_after_wd(S, S->red[1], hist, betas);
+}
+
+struct CgC1Op {
+    CgState* S;
+    double* __restrict__ q;
+    const double* __restrict__ s;
+    double* alphas;
+    bool fused;
+    __device__ bool skip() const { return S->stop != 0; }
+    __device__ void row(int64_t i, double ax, double (&acc)[1]) const {
+        q[i] = ax;
+        acc[0] = fma(s[i], ax, acc[0]);
+    }
+    __device__ void finish(const double (&tot)[1]) const {
+        if (fused) cg_after_as(S, tot[0], alphas);
+        else S->red[0] = tot[0];
+    }
+};
+
+__global__ void __launch_bounds__(kBlock) k_cg_c2(CgState* S, double* __restrict__ u, const double* __restrict__ s,
+                                                  double* __restrict__ d, const double* __restrict__ q,
+                                                  const double* __restrict__ dinv, double* __restrict__ w, int64_t n,
+                                                  double* hist, double* betas, double* partials, unsigned int* ticket,
+                                                  bool fused) {
+    if (S->stop) return;
+    const double a = S->alpha;
+    double acc[1] = {0.0};
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (u) u[i] += a * s[i];
+        const double di = d[i] + (-a) * q[i];
+        const double wi = dinv ? dinv[i] * di : di;
+        d[i] = di;
+        w[i] = wi;
+        acc[0] = fma(wi, di, acc[0]);
+    }
+    if (grid_sum<1>(acc, partials, ticket)) {
+        if (threadIdx.x == 0) {
+            if (fused) cg_after_wd(S, acc[0], hist, betas);
+            else S->red[1] = acc[0];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_cg_c3(const CgState* S, double* __restrict__ s, const double* __restrict__ w,
+                                                  int64_t n) {
+    if (S->stop) return;
+    const double b = S->beta;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        s[i] = b * s[i] + w[i];
+}
+
+__global__ void k_cg_init_scalar(CgState* S, int maxsteps, double tol, double* hist, int lanczos) {
+    const double wdn = S->red[0];
+    S->wd = S->wdn = wdn;
+    S->alpha = S->beta = 0.0;
+    S->err0 = sqrt(fabs(wdn));
+    S->tol_abs = tol * S->err0;
+    S->it = 0;
+    S->maxsteps = maxsteps;
+    S->stop = 0;
+    S->status = NSB_MAXSTEPS;
+    S->record = lanczos;
+    if (hist) hist[0] = S->err0;
+    if (S->err0 == 0.0) { S->stop = 1; S->status = NSB_CONVERGED; }
+    else if (!isfinite(wdn)) { S->stop = 1; S->status = NSB_BREAKDOWN; }
+    else if (maxsteps <= 0) { S->stop = 1; S->status = NSB_MAXSTEPS; }
+}
+
+__global__ void __launch_bounds__(kBlock) k_lanczos_start(double* __restrict__ r, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        r[i] = 1.0 + 0.5 * sin((double)(i + 1));
+}
+
+struct ResidualOp2 {  // d = rhs - A u
+    const double* __restrict__ rhs;
+    double* __restrict__ out;
+    __device__ bool skip() const { return false; }
+    __device__ void row(int64_t r, double ax, double (&)[1]) const { out[r] = rhs[r] - ax; }
+    __device__ void finish(const double (&)[1]) const {}
+};
+
+// shared driver: CG on (A, dinv) from residual d (already on device); u may be null (Lanczos)
+struct CgBuffers {
+    DevBuf<double> u, d, w, s, q, hist, alphas, betas;
+    DevBuf<CgState> st;
+};
+
+static int cg_run(Context& c, nsb_mat_s* A, const double* dinv, CgBuffers& b, bool want_u, int maxsteps, double tol,
+                  bool lanczos, int chunk, bool (*host_check)(void*, const CgState&), void* check_arg, CgState* out_state,
+                  float* out_ms) {
+    const int64_t n = A->rows;
+    const bool fused = c.nranks == 1;
+    CgState* S = b.st.p;
+    const int vg = vec_grid(n, c.num_sms);
+    double* u = want_u ? b.u.p : nullptr;
+    double* hist = lanczos ? nullptr : b.hist.p;
+    double* alphas = lanczos ? b.alphas.p : nullptr;
+    double* betas = lanczos ? b.betas.p : nullptr;
+    // w = C d ; s = w ; wd = <w, d>
+    NSB_CHECK(vec_diagmul(c, b.w.p, 1.0, dinv, b.d.p, n));
+    NSB_CHECK(vec_lincomb(c, b.s.p, 1.0, b.w.p, 0, nullptr, 0, nullptr, n));
+    NSB_CHECK(vec_dot(c, b.w.p, b.d.p, n, &S->red[0]));
+    k_cg_init_scalar<<<1, 1, 0, c.stream>>>(S, maxsteps, tol, hist, lanczos ? 1 : 0);
+    c.launches++;
+    cudaEvent_t e0, e1;
+    NSB_CUDA(cudaEventCreate(&e0));
+    NSB_CUDA(cudaEventCreate(&e1));
+    NSB_CUDA(cudaEventRecord(e0, c.stream));
+    auto launch_iteration = [&]() -> int {
+        NSB_CHECK(halo_exchange(c, A->halo, b.s.p));
+        NSB_CHECK(spmv_launch<1>(c, A, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused}));
+        if (!fused) {
+            NSB_CHECK(allreduce_sum(c, &S->red[0], 1));
+            k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist, alphas, betas);
+            c.launches++;
+        }
+        k_cg_c2<<<vg, kBlock, 0, c.stream>>>(S, u, b.s.p, b.d.p, b.q.p, dinv, b.w.p, n, hist, betas, c.partials, c.ticket, fused);
+        c.launches++;
+        if (!fused) {
+            NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
+            k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
+            c.launches++;
+        }
+        k_cg_c3<<<vg, kBlock, 0, c.stream>>>(S, b.s.p, b.w.p, n);
+        c.launches++;
+        NSB_CUDA(cudaGetLastError());
+        return NSB_OK;
+    };
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t gexec = nullptr;
+    int64_t graph_launches = 0;
+    int rc = NSB_OK;
+    if (c.use_graphs && maxsteps > 0) {
+        const int64_t before = c.launches;
+        NSB_CUDA(cudaStreamBeginCapture(c.stream, cudaStreamCaptureModeThreadLocal));
+        for (int j = 0; j < chunk && rc == NSB_OK; ++j) rc = launch_iteration();
+        cudaError_t ce = cudaStreamEndCapture(c.stream, &graph);
+        graph_launches = c.launches - before;
+        c.launches = before;
+        if (rc == NSB_OK && ce != cudaSuccess) {
+            set_error("cg: graph capture failed: %s", cudaGetErrorString(ce));
+            rc = NSB_ERR_CUDA;
+        }
+        if (rc == NSB_OK) NSB_CUDA(cudaGraphInstantiate(&gexec, graph, 0));
+    }
+    CgState hs;
+    memset(&hs, 0, sizeof(hs));
+    int launched = 0;
+    while (rc == NSB_OK && launched < maxsteps) {
+        if (gexec) {
+            if (cudaGraphLaunch(gexec, c.stream) != cudaSuccess) {
+                set_error("cg: graph launch failed");
+                rc = NSB_ERR_CUDA;
+            }
+            c.launches += graph_launches;
+        } else {
+            for (int j = 0; j < chunk && rc == NSB_OK; ++j) rc = launch_iteration();
+        }
+        launched += chunk;
+        if (rc != NSB_OK) break;
+        NSB_CUDA(cudaMemcpyAsync(&hs, S, sizeof(CgState), cudaMemcpyDeviceToHost, c.stream));
+        NSB_CUDA(cudaStreamSynchronize(c.stream));
+        if (hs.stop) break;
+        if (host_check && host_check(check_arg, hs)) break;
+    }
+    if (gexec) cudaGraphExecDestroy(gexec);
+    if (graph) cudaGraphDestroy(graph);
+    NSB_CHECK(rc);
+    NSB_CUDA(cudaEventRecord(e1, c.stream));
+    NSB_CUDA(cudaMemcpyAsync(&hs, S, sizeof(CgState), cudaMemcpyDeviceToHost, c.stream));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *out_state = hs;
+    if (out_ms) *out_ms = ms;
+    return NSB_OK;
+}
+
+// ---- symmetric tridiagonal extreme eigenvalues by Sturm bisection (host) -------------------------
+static int sturm_count(const std::vector<double>& d, const std::vector<double>& e, int m, double x) {
+    int cnt = 0;
+    double q = d[0] - x;
+    if (q < 0) cnt++;
+    for (int i = 1; i < m; ++i) {
+        const double qq = (q == 0.0) ? 1e-300 : q;
+        q = d[i] - x - e[i - 1] * e[i - 1] / qq;
+        if (q < 0) cnt++;
+    }
+    return cnt;  // number of eigenvalues < x
+}
+
+static double tridiag_kth(const std::vector<double>& d, const std::vector<double>& e, int m, int k) {
+    double lo = d[0], hi = d[0];
+    for (int i = 0; i < m; ++i) {
+        const double r = (i > 0 ? fabs(e[i - 1]) : 0.0) + (i < m - 1 ? fabs(e[i]) : 0.0);
+        lo = std::min(lo, d[i] - r);
+        hi = std::max(hi, d[i] + r);
+    }
+    for (int it = 0; it < 200; ++it) {
+        const double mid = 0.5 * (lo + hi);
+        if (mid <= lo || mid >= hi) break;
+        if (sturm_count(d, e, m, mid) > k) hi = mid;
+        else lo = mid;
+    }
+    return 0.5 * (lo + hi);
+}
+
+struct LanczosCheck {
+    Context* c;
+    CgBuffers* b;
+    double tol;
+    std::vector<double> alphas, betas, diag, off;
+    int used = 0;       // iterations folded into the tridiagonal so far
+    double lam_prev = 0.0;
+    bool have_prev = false;
+    bool converged = false;
+    double lam_min = 0.0, lam_max = 0.0;
+    int steps = 0;
+};
+
+// Fold the newly available CG coefficients into T and apply the oracle's stopping rule iteration by
+// iteration (oracle/krylov_oracle.py: lanczos_eigs): stop once lambda_min moved < tol relative, it >= 4.
+static bool lanczos_host_check(void* arg, const CgState& hs) {
+    LanczosCheck& L = *(LanczosCheck*)arg;
+    const int avail = hs.it;
+    if (avail <= L.used) return false;
+    L.alphas.resize(avail);
+    L.betas.resize(avail);
+    cudaMemcpy(L.alphas.data() + L.used, L.b->alphas.p + L.used, sizeof(double) * (avail - L.used), cudaMemcpyDeviceToHost);
+    cudaMemcpy(L.betas.data() + L.used, L.b->betas.p + L.used, sizeof(double) * (avail - L.used), cudaMemcpyDeviceToHost);
+    for (int it = L.used; it < avail; ++it) {
+        if (it == 0) L.diag.push_back(1.0 / L.alphas[0]);
+        else {
+            L.diag.push_back(1.0 / L.alphas[it] + L.betas[it - 1] / L.alphas[it - 1]);
+            L.off.push_back(sqrt(L.betas[it - 1]) / L.alphas[it - 1]);
+        }
+        const int m = (int)L.diag.size();
+        const double lam = tridiag_kth(L.diag, L.off, m, 0);
+        L.lam_min = lam;
+        L.lam_max = tridiag_kth(L.diag, L.off, m, m - 1);
+        L.steps = m;
+        if (L.have_prev && fabs(lam - L.lam_prev) <= L.tol * fabs(lam) && it >= 4) {
+            L.converged = true;
+            L.used = avail;
+            return true;
+        }
+        L.lam_prev = lam;
+        L.have_prev = true;
+    }
+    L.used = avail;
+    return false;
+}
+
+// ---- Gram-Schmidt kernels ------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_dots2(const double* __restrict__ bi, const double* __restrict__ bj, int64_t n,
+                                                  double* out, double* partials, unsigned int* ticket) {
+    double acc[2] = {0.0, 0.0};
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double a = bi[i];
+        acc[0] = fma(a, bj[i], acc[0]);
+        acc[1] = fma(a, a, acc[1]);
+    }
+    if (grid_sum<2>(acc, partials, ticket)) {
+        if (threadIdx.x == 0) { out[0] = acc[0]; out[1] = acc[1]; }
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_gs_axpy(double* __restrict__ bj, const double* __restrict__ bi,
+                                                    const double* __restrict__ dots, int64_t n) {
+    const double coef = dots[0] / dots[1];   // orthonormalization.py:11-12
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        bj[i] -= coef * bi[i];
+}
+
+__global__ void __launch_bounds__(kBlock) k_gs_scale(double* __restrict__ bj, const double* __restrict__ nrm2, int64_t n) {
+    const double sc = 1.0 / sqrt(nrm2[0]);   // orthonormalization.py:13
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        bj[i] = sc * bj[i];
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+static int cg_alloc(CgBuffers& b, nsb_mat A, int maxsteps, bool lanczos) {
+    const int64_t n = A->rows, nx = A->cols;
+    NSB_CHECK(b.u.alloc(nx));
+    NSB_CHECK(b.s.alloc(nx));
+    NSB_CHECK(b.d.alloc(n));
+    NSB_CHECK(b.w.alloc(n));
+    NSB_CHECK(b.q.alloc(n));
+    NSB_CHECK(b.hist.alloc(maxsteps + 2));
+    NSB_CHECK(b.st.alloc(1));
+    if (lanczos) {
+        NSB_CHECK(b.alphas.alloc(maxsteps + 2));
+        NSB_CHECK(b.betas.alloc(maxsteps + 2));
+    }
+    return NSB_OK;
+}
+
+extern "C" int nsb_cg(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* rhs, double* sol, int maxsteps, double tol,
+                      int initialize, double* history, int* iterations, double* seconds, int* status) {
+    NSB_REQUIRE(ctx && A && rhs && sol, "nsb_cg: NULL argument");
+    NSB_REQUIRE(maxsteps >= 0, "nsb_cg: maxsteps < 0");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    const int64_t n = A->rows;
+    if (pre) NSB_REQUIRE(pre->n == n, "nsb_cg: preconditioner size mismatch");
+    CgBuffers b;
+    NSB_CHECK(cg_alloc(b, A, maxsteps, false));
+    NSB_CHECK(copy_in(c, b.q.p, rhs, n));
+    if (initialize) {
+        NSB_CHECK(vec_set(c, b.u.p, 0.0, A->cols));
+        NSB_CHECK(vec_lincomb(c, b.d.p, 1.0, b.q.p, 0, nullptr, 0, nullptr, n));
+    } else {
+        NSB_CHECK(copy_in(c, b.u.p, sol, n));
+        NSB_CHECK(halo_exchange(c, A->halo, b.u.p));
+        NSB_CHECK(spmv_launch<0>(c, A, b.u.p, ResidualOp2{b.q.p, b.d.p}));
+    }
+    CgState hs;
+    float ms = 0.f;
+    const int chunk = n < 200000 ? 16 : 4;
+    NSB_CHECK(cg_run(c, A, pre ? pre->d.p : nullptr, b, true, maxsteps, tol, false, chunk, nullptr, nullptr, &hs, &ms));
+    NSB_CHECK(copy_out(c, sol, b.u.p, n));
+    if (history) NSB_CHECK(copy_out(c, history, b.hist.p, hs.it + 1));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    if (iterations) *iterations = hs.it;
+    if (seconds) *seconds = (double)ms * 1e-3;
+    if (status) *status = hs.status;
+    return NSB_OK;
+}
+
+extern "C" int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* start, int maxsteps, double tol,
+                                double* lam_min, double* lam_max, int* steps) {
+    NSB_REQUIRE(ctx && A && lam_min, "nsb_lanczos_eigs: NULL argument");
+    NSB_REQUIRE(maxsteps > 0, "nsb_lanczos_eigs: maxsteps must be positive");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    const int64_t n = A->rows;
+    if (pre) NSB_REQUIRE(pre->n == n, "nsb_lanczos_eigs: preconditioner size mismatch");
+    CgBuffers b;
+    NSB_CHECK(cg_alloc(b, A, maxsteps, true));
+    if (start) NSB_CHECK(copy_in(c, b.d.p, start, n));
+    else {
+        k_lanczos_start<<<vec_grid(n, c.num_sms), kBlock, 0, c.stream>>>(b.d.p, n);
+        c.launches++;
+    }
+    LanczosCheck L;
+    L.c = &c;
+    L.b = &b;
+    L.tol = tol;
+    CgState hs;
+    float ms = 0.f;
+    NSB_CHECK(cg_run(c, A, pre ? pre->d.p : nullptr, b, false, maxsteps, 0.0, true, 8, lanczos_host_check, &L, &hs, &ms));
+    if (!L.converged) lanczos_host_check(&L, hs);  // fold whatever the last chunk produced
+    NSB_REQUIRE(L.steps > 0, "nsb_lanczos_eigs: Lanczos produced no step (zero start residual?)");
+    *lam_min = L.lam_min;
+    if (lam_max) *lam_max = L.lam_max;
+    if (steps) *steps = L.steps;
+    return NSB_OK;
+}
+
+extern "C" int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int tries) {
+    NSB_REQUIRE(ctx && basis && n >= 0 && m >= 0 && tries >= 0, "nsb_orthonormalize: bad argument");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    if (m == 0 || n == 0) return NSB_OK;
+    const bool on_dev = is_device_ptr(basis);
+    DevBuf<double> own;
+    double* Q = basis;
+    if (!on_dev) {
+        NSB_CHECK(own.alloc(n * m));
+        NSB_CHECK(copy_in(c, own.p, basis, n * m));
+        Q = own.p;
+    }
+    DevBuf<double> sc;
+    NSB_CHECK(sc.alloc(2));
+    const int vg = vec_grid(n, c.num_sms);
+    for (int t = 0; t < tries; ++t) {                                   // :8
+        for (int j = 0; j < m; ++j) {                                   // :9
+            double* bj = Q + (int64_t)j * n;
+            for (int i = 0; i < j; ++i) {                               // :10
+                const double* bi = Q + (int64_t)i * n;
+                k_dots2<<<vg, kBlock, 0, c.stream>>>(bi, bj, n, sc.p, c.partials, c.ticket);
+                NSB_CHECK(allreduce_sum(c, sc.p, 2));
+                k_gs_axpy<<<vg, kBlock, 0, c.stream>>>(bj, bi, sc.p, n);
+                c.launches += 2;
+            }
+            k_dots2<<<vg, kBlock, 0, c.stream>>>(bj, bj, n, sc.p, c.partials, c.ticket);
+            NSB_CHECK(allreduce_sum(c, sc.p, 2));
+            k_gs_scale<<<vg, kBlock, 0, c.stream>>>(bj, sc.p, n);
+            c.launches += 2;
+        }
+    }
+    NSB_CUDA(cudaGetLastError());
+    if (!on_dev) NSB_CHECK(copy_out(c, basis, Q, n * m));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    return NSB_OK;
+}

@@ -1,0 +1,237 @@
+// common.cuh -- internal declarations shared by the translation units of libnsb200.so
+// (context, device buffers, error handling, deterministic block/grid reductions).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/nsb200.h"
+
+namespace nsb {
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+extern thread_local char g_err[1024];
+
+#define NSB_CUDA(call)                                                                          \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess) {                                                               \
+            nsb::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return NSB_ERR_CUDA;                                                                \
+        }                                                                                       \
+    } while (0)
+
+#define NSB_CHECK(call)                  \
+    do {                                 \
+        int r__ = (call);                \
+        if (r__ != NSB_OK) return r__;   \
+    } while (0)
+
+#define NSB_REQUIRE(cond, ...)           \
+    do {                                 \
+        if (!(cond)) {                   \
+            nsb::set_error(__VA_ARGS__); \
+            return NSB_ERR_INVALID;      \
+        }                                \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// launch geometry.  Vector kernels are persistent grid-stride loops: a fixed grid (a multiple of
+// the SM count) keeps every reduction tree identical from run to run for a given length.
+// ---------------------------------------------------------------------------------------------
+constexpr int kBlock = 256;          // threads per block of the vector kernels
+constexpr int kMaxBlocks = 148 * 8;  // 148 SMs x 8 resident 256-thread blocks
+constexpr int kMaxRed = 4;           // doubles reduced per kernel at most
+
+inline int vec_grid(int64_t n, int num_sms) {
+    int64_t want = (n + (int64_t)kBlock * 2 - 1) / ((int64_t)kBlock * 2);
+    int64_t cap = (int64_t)num_sms * 8;
+    if (want < 1) want = 1;
+    return (int)(want < cap ? want : cap);
+}
+
+// ---------------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------------
+struct NcclApi;  // dist.cu
+
+struct Context {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    int64_t launches = 0;
+    bool use_graphs = true;
+    // reduction scratch: per-block partials and the arrival ticket of the last-block pattern
+    double* partials = nullptr;  // kMaxRed * max grid
+    unsigned int* ticket = nullptr;
+    int max_grid = 0;
+    // pinned host mailbox for scalar read-back
+    double* h_mail = nullptr;
+    double* d_mail = nullptr;
+    // distributed
+    int rank = 0, nranks = 1;
+    void* nccl_comm = nullptr;
+    NcclApi* nccl = nullptr;
+};
+
+// device buffer with RAII (host-side owner)
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    int64_t n = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    int alloc(int64_t count) {
+        release();
+        n = count;
+        if (count <= 0) return NSB_OK;
+        cudaError_t e = cudaMalloc((void**)&p, sizeof(T) * (size_t)count);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            set_error("cudaMalloc(%lld bytes) failed: %s", (long long)(sizeof(T) * (size_t)count), cudaGetErrorString(e));
+            return NSB_ERR_CUDA;
+        }
+        return NSB_OK;
+    }
+};
+
+}  // namespace nsb
+
+// ---------------------------------------------------------------------------------------------
+// opaque handle bodies
+// ---------------------------------------------------------------------------------------------
+struct nsb_ctx_s {
+    nsb::Context c;
+};
+
+struct nsb_halo_s {
+    nsb::Context* ctx = nullptr;
+    int64_t n_owned = 0, n_halo = 0;
+    std::vector<int> neighbors;
+    std::vector<int64_t> send_counts, recv_counts;
+    int64_t n_send = 0;
+    nsb::DevBuf<int32_t> send_idx;  // owned entries to ship, neighbour by neighbour
+    nsb::DevBuf<double> send_buf;
+};
+
+struct nsb_mat_s {
+    nsb::Context* ctx = nullptr;
+    int64_t rows = 0, cols = 0, nnz = 0;
+    nsb::DevBuf<int32_t> rowptr;  // rows + 1
+    nsb::DevBuf<int32_t> colidx;  // nnz
+    nsb::DevBuf<double> values;   // nnz
+    int threads_per_row = 8;      // sub-warp width of the CSR-vector kernel, chosen from nnz/rows
+    nsb_halo_s* halo = nullptr;   // not owned
+    // saddle composition bookkeeping (rows of the velocity block; 0 for a plain matrix)
+    int64_t n_u = 0, n_p = 0;
+};
+
+struct nsb_pre_s {
+    nsb::Context* ctx = nullptr;
+    int64_t n = 0;
+    nsb::DevBuf<double> d;  // diagonal preconditioner: y = d .* x
+};
+
+namespace nsb {
+
+// ---------------------------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block-wide sum of NS values with a fixed tree (warp shuffle, then one warp over the warp sums).
+// Result valid in thread 0.
+template <int NS>
+__device__ __forceinline__ void block_sum(double (&v)[NS]) {
+    __shared__ double sm[NS][32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+        double s = warp_sum(v[k]);
+        if (lane == 0) sm[k][wid] = s;
+    }
+    __syncthreads();
+    if (wid == 0) {
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+            double s = lane < nw ? sm[k][lane] : 0.0;
+            v[k] = warp_sum(s);
+        }
+    }
+    __syncthreads();
+}
+
+// Grid-wide deterministic reduction, "last block finishes" pattern.  Every block publishes its NS
+// block sums, takes a ticket, and the block that draws the last ticket sums the partials of all
+// blocks in a fixed order.  Returns true in ALL threads of that last block, with the totals in
+// v[] valid in thread 0.  The ticket is reset for the next kernel.
+template <int NS>
+__device__ __forceinline__ bool grid_sum(double (&v)[NS], double* partials, unsigned int* ticket) {
+    block_sum<NS>(v);
+    __shared__ bool is_last;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < NS; ++k) partials[(size_t)k * gridDim.x + blockIdx.x] = v[k];
+        __threadfence();
+        unsigned int t = atomicAdd(ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return false;
+    __threadfence();
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+        double s = 0.0;
+        for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x)
+            s += __ldcg(&partials[(size_t)k * gridDim.x + b]);
+        v[k] = s;
+    }
+    block_sum<NS>(v);
+    if (threadIdx.x == 0) *ticket = 0u;
+    return true;
+}
+
+#endif  // __CUDACC__
+
+// ---------------------------------------------------------------------------------------------
+// host-side utilities implemented in context.cu / vecops.cu
+// ---------------------------------------------------------------------------------------------
+int copy_in(Context& c, double* dst_dev, const double* src_any, int64_t n);   // host|device -> device, async on stream
+int copy_out(Context& c, double* dst_any, const double* src_dev, int64_t n);  // device -> host|device, async on stream
+bool is_device_ptr(const void* p);
+
+// generic (unfused) vector ops used by set-up phases
+int vec_set(Context& c, double* y, double a, int64_t n);
+int vec_lincomb(Context& c, double* y, double a, const double* x1, double b, const double* x2, double cc,
+                const double* x3, int64_t n);                               // y = a x1 + b x2 + cc x3 (x2,x3 may be null)
+int vec_diagmul(Context& c, double* y, double s, const double* d, const double* x, int64_t n);  // y = s d.*x (d null: y = s x)
+int vec_dot(Context& c, const double* x, const double* y, int64_t n, double* out_dev);          // *out_dev = <x,y> (+ allreduce when distributed)
+int allreduce_sum(Context& c, double* dev, int count);                       // no-op for nranks == 1
+int halo_exchange(Context& c, nsb_halo_s* h, double* x);                     // fills x[n_owned .. n_owned+n_halo)
+
+// plain SpMV launch (spmv.cu): y = M x on the context stream; x must have room for the halo tail
+int spmv_plain(Context& c, const nsb_mat_s* m, const double* x, double* y);
+
+}  // namespace nsb
