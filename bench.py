@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""Headline benchmark: Bramble-Pasciak CG (solvers/bramblepasciak_new.py semantics) on the 3D Stokes
+channel of templates/NavierStokesSIMPLE_test_3D.py refined to ~20M Taylor-Hood unknowns
+(BASELINE.json configs[4]), Krylov iterations/s, plus the SpMV roofline of the dominant kernel.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1 under torchrun, one rank per GPU)
+    python bench.py --impl reference ...                      (CPU oracle port on the host cores)
+
+A step = one BramblePasciakCG call of exactly --iters iterations (tol = 0 never triggers) from the same
+start vector on the same assembled system.  `value` times K steps with every input resident in HBM;
+`e2e` times the same call with host (pinned) f, g, sol buffers, copies inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# Algorithmic bytes per BPCG v2 iteration beyond the SpMVs' own x/y traffic (frozen):
+#   B1 epilogue r(As0,z0,dA,s0) w(As0,tmp1,tmp4) = 7 n_u ; B2 epilogue r(s0,tmp0) = 2 n_u ; B3 epilogue r(s1) = 1 n_p
+#   B4 velocity r8 w4 = 12 n_u, pressure r6 w3 = 9 n_p ; B5 r2 w1 = 3 n_u + 3 n_p
+BPCG_VEC_PASSES_U = 24
+BPCG_VEC_PASSES_P = 13
+
+
+def spmv_bytes(rows, cols, nnz):
+    return 12 * nnz + 4 * (rows + 1) + 8 * cols + 8 * rows
+
+
+def bpcg_iter_bytes(n_u, n_p, nnzA, nnzB):
+    return (spmv_bytes(n_u, n_u, nnzA) + spmv_bytes(n_p, n_u, nnzB) + spmv_bytes(n_u, n_p, nnzB)
+            + 8 * (BPCG_VEC_PASSES_U * n_u + BPCG_VEC_PASSES_P * n_p))
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_oracle_rate(target_dofs, iters, log=None):
+    """Reference arm / cpu_baseline: the numpy/scipy oracle port of solvers/bramblepasciak_new.py on a
+    bounded sample of the workload, on the host cores.  Returns (its_per_s_scaled_to_full, info)."""
+    import torch
+    from oracle import krylov_oracle as ko
+    import navier_stokes_solver_b200.synthetic as syn
+    sample_dofs = min(target_dofs, 1.2e6)
+    cells = syn.stokes_cells_for_dofs(sample_dofs)
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    S = syn.assemble_stokes(cells, (2.5, 0.41, 0.41), device=dev)
+    A, B, BT = S.A.to_scipy(), S.B.to_scipy(), S.BT.to_scipy()
+    dA = syn.jacobi_inverse(S.A, free=S.free_u).cpu().numpy()
+    dM = syn.jacobi_inverse(S.Mp).cpu().numpy()
+    f, g = S.f.cpu().numpy(), S.g.cpu().numpy()
+    u0 = np.concatenate([S.u0.cpu().numpy(), np.zeros(S.n_p)])
+    n = S.n_u + S.n_p
+    ritz = ko.lanczos_eigs(A, dA, S.n_u, maxsteps=60, tol=1e-2)
+    lam = float(ritz[0]) * 0.5   # safe under-estimate: the sample only times the loop
+    sol = u0.copy()
+    t0 = time.perf_counter()
+    _, hist, info = ko.bramble_pasciak_cg_v2(A, B, f, g, dA, dM, sol=sol, tol=0.0, maxsteps=iters, initialize=False,
+                                             lam_min=lam, BT=BT)
+    wall = time.perf_counter() - t0
+    loop_s = info["seconds"]
+    rate_sample = iters / loop_s
+    scaled = rate_sample * (n / float(target_dofs)) if target_dofs > n else rate_sample
+    return scaled, dict(sample_dofs=int(n), iters=iters, loop_seconds=loop_s, wall_seconds=wall,
+                        rate_at_sample=rate_sample, threads=1)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    iters = min(args.iters, 20)
+    rates, info = [], None
+    for i in range(args.warmup + args.steps):
+        r, info = cpu_oracle_rate(args.dofs, iters)
+        if i >= args.warmup:
+            rates.append(r)
+        if i == 0 and info["wall_seconds"] > 60:   # keep the whole arm within minutes
+            rates = rates or [r]
+            break
+    v = float(np.mean(rates))
+    sample = ("oracle port (numpy/scipy, oracle/krylov_oracle.py: bramble_pasciak_cg_v2) of solvers/bramblepasciak_new.py; "
+              "%d iterations on a %d-dof refinement of the same 3D channel, iterations/s scaled by dof ratio to the "
+              "%.3g-dof workload; NGSolve absent so scipy CSR mat-vec, 1 thread" % (iters, info["sample_dofs"], args.dofs))
+    line = {"impl": "reference", "metric": "bpcg_krylov_iterations_per_s", "value": v, "unit": "iterations/s",
+            "n_gpus": args.gpus, "steps": len(rates), "warmup": args.warmup, "ms_per_step": 1e3 * iters / (v if v else 1),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "3D Stokes channel, Taylor-Hood P2/P1, ~%.3g dofs, BramblePasciakCG, Jacobi preA/preM" % args.dofs},
+            "cpu_baseline": {"value": v, "unit": "iterations/s", "cores": 1, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--dofs", type=float, default=20e6)
+    ap.add_argument("--iters", type=int, default=100, help="Krylov iterations per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lanczos-steps", type=int, default=1500)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import navier_stokes_solver_b200 as nsb
+    import navier_stokes_solver_b200.synthetic as syn
+    from navier_stokes_solver_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        ctx = nsb.Context.from_torch_distributed(device=local)
+    else:
+        ctx = nsb.Context(device=local)
+    nsb.set_default_context(ctx)
+
+    cells = syn.stokes_cells_for_dofs(args.dofs)
+    lengths = (2.5, 0.41, 0.41)
+    t_asm = time.perf_counter()
+    if world == 1:
+        S = syn.assemble_stokes(cells, lengths, device="cuda")
+        A = nsb.SparseMatrix.from_csr(S.A, ctx)
+        B = nsb.SparseMatrix.from_csr(S.B, ctx)
+        BT = nsb.SparseMatrix.from_csr(S.BT, ctx)
+        B.set_transpose(BT)
+        dA = syn.jacobi_inverse(S.A, free=S.free_u)
+        dM = syn.jacobi_inverse(S.Mp)
+        n_u, n_p = S.n_u, S.n_p
+        nnzA, nnzB = S.A.nnz, S.B.nnz
+        f_d, g_d = S.f, S.g
+        u_start = torch.cat([S.u0, torch.zeros(n_p, dtype=torch.float64, device="cuda")])
+        S.A = S.B = S.BT = None
+        start_vec = None
+    else:
+        from navier_stokes_solver_b200 import partition
+        P = partition.build_distributed_stokes(cells, lengths, ctx, rank, world)
+        A, B, BT, dA, dM = P.A, P.B, P.BT, P.dA, P.dM
+        n_u, n_p, nnzA, nnzB = P.n_u_global, P.n_p_global, P.nnzA_global, P.nnzB_global
+        f_d, g_d, u_start, start_vec = P.f, P.g, P.u_start, P.lanczos_start
+    torch.cuda.synchronize()
+    t_asm = time.perf_counter() - t_asm
+    pA = nsb.DiagonalPreconditioner.from_diagonal(dA, ctx)
+    pM = nsb.DiagonalPreconditioner.from_diagonal(dM, ctx)
+    torch.cuda.empty_cache()
+
+    # scale factor k = 1/lambda_min + 1e-3 by device Lanczos (bramblepasciak_new.py:115-118), once per assembly
+    t_l = time.perf_counter()
+    lams = nsb.EigenValues_Preconditioner(A, pA, tol=1e-5, maxsteps=args.lanczos_steps, start=start_vec)
+    lanczos_steps = nsb.solvers.last_info["iterations"]
+    t_l = time.perf_counter() - t_l
+    lam_min = min(lams)
+
+    lib = ctx._lib
+    import ctypes as C
+    BTm = B.CreateTranspose()
+    k_scale = 1.0 / lam_min + 1e-3
+    n_loc = int(f_d.numel() + g_d.numel())
+    hist = np.zeros(args.iters + 2)
+
+    def step(f_buf, g_buf, sol_buf):
+        upd, secs, status = C.c_int(), C.c_double(), C.c_int()
+        pf, _, _ = nsb.la.buffer_of(f_buf)
+        pg, _, _ = nsb.la.buffer_of(g_buf)
+        ps, _, _ = nsb.la.buffer_of(sol_buf)
+        _lib.check(lib.nsb_bpcg(ctx.h, A.h, B.h, BTm.h, pA.h, pM.h, k_scale, pf, pg, ps, args.iters, 0.0, 0, 1, 2,
+                                hist.ctypes.data, C.byref(upd), C.byref(secs), C.byref(status)), "nsb_bpcg")
+        assert upd.value == args.iters, (upd.value, status.value)
+        return secs.value
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ctx.sync()
+
+    def timed(nsteps, fn):
+        barrier()
+        t0 = time.perf_counter()
+        loop = 0.0
+        for _ in range(nsteps):
+            loop += fn()
+        barrier()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt, loop], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt, loop = float(t[0]), float(t[1])
+        return dt, loop
+
+    # ---- device-resident leg
+    sol_d = u_start.clone()
+
+    def dev_step():
+        sol_d.copy_(u_start)
+        torch.cuda.current_stream().synchronize()
+        return step(f_d, g_d, sol_d)
+
+    timed(args.warmup, dev_step)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launch_count()
+    dt, loop = timed(args.steps, dev_step)
+    launches = ctx.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    its = args.iters * args.steps
+    value = its / dt
+    hist_dev = hist[:args.iters + 1].copy()
+
+    # ---- end-to-end leg: host pinned f, g, sol; H2D/D2H inside the timed region
+    f_h = torch.empty(f_d.numel(), dtype=torch.float64).pin_memory()
+    g_h = torch.empty(g_d.numel(), dtype=torch.float64).pin_memory()
+    s_h = torch.empty(u_start.numel(), dtype=torch.float64).pin_memory()
+    u_h = u_start.cpu()
+    f_h.copy_(f_d)
+    g_h.copy_(g_d)
+
+    def e2e_step():
+        return step(f_h, g_h, s_h)   # sol carries over between steps (tol = 0: always --iters iterations)
+
+    s_h.copy_(u_h)
+    timed(1, e2e_step)
+    same = np.allclose(hist[:args.iters + 1], hist_dev, rtol=1e-12)   # first host step == device leg
+    dt_e, _ = timed(args.steps, e2e_step)
+    e2e_value = its / dt_e
+    h2d = 8 * (f_h.numel() + g_h.numel() + s_h.numel())
+    d2h = 8 * s_h.numel() + 8 * (args.iters + 1)
+
+    # ---- roofline of the dominant kernel (SpMV with A): CUDA events on the context's stream
+    ms_A = A.spmv_bench(warmup=10, reps=50)
+    ms_B = B.spmv_bench(warmup=5, reps=20)
+    ms_BT = BTm.spmv_bench(warmup=5, reps=20)
+    peak, peak_src = measured_peaks()
+    bytes_A = A.spmv_bytes()
+    ach_A = bytes_A / (ms_A * 1e-3) / 1e9
+    iter_bytes = bpcg_iter_bytes(n_u, n_p, nnzA, nnzB)
+    iter_gbs = iter_bytes * (its / loop) / 1e9 / world if loop > 0 else None
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    line = {
+        "metric": "bpcg_krylov_iterations_per_s", "value": value, "unit": "iterations/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "3D Stokes channel [0,2.5]x[0,0.41]^2 (NavierStokesSIMPLE_test_3D.py), Taylor-Hood P2/P1, "
+                               "BramblePasciakCG (bramblepasciak_new.py) with Jacobi preA/preM, %d iterations per step" % args.iters,
+                   "cells": list(cells), "dofs": int(n_u + n_p), "n_u": int(n_u), "n_p": int(n_p), "nnz_A": int(nnzA),
+                   "nnz_B": int(nnzB), "iters_per_step": args.iters, "row_partition": "x-slabs" if world > 1 else "none",
+                   "l2_policy": "inputs larger than L2 (%.1f GB of CSR per iteration)" % (12e-9 * (nnzA + 2 * nnzB)),
+                   "lambda_min": lam_min, "lanczos_steps": lanczos_steps, "assembly_s": t_asm, "lanczos_s": t_l},
+        "iteration_loop": {"iterations_per_s": its / loop if loop else None, "algorithmic_bytes_per_iteration": iter_bytes,
+                           "achieved_gbs_per_gpu": iter_gbs, "frac_of_measured_peak": iter_gbs / peak if iter_gbs else None,
+                           "frac_of_nominal_8TBs": iter_gbs / 8000.0 if iter_gbs else None},
+        "roofline": {"bound": "hbm", "kernel": "spmv_csrvec_kernel (A, %d nnz)" % nnzA, "achieved": ach_A, "peak": peak,
+                     "peak_source": peak_src, "unit": "GB/s", "frac": ach_A / peak, "frac_of_nominal_8TBs": ach_A / 8000.0,
+                     "algorithmic_bytes": bytes_A, "ms": ms_A, "traffic": None,
+                     "other": {"spmv_B_gbs": B.spmv_bytes() / ms_B / 1e6, "spmv_BT_gbs": BTm.spmv_bytes() / ms_BT / 1e6}},
+        "e2e": {"value": e2e_value, "unit": "iterations/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "history_matches_device_leg": bool(same)},
+        "gpu_launches": int(launches), "clocks": clocks,
+    }
+    if not args.no_cpu_baseline:
+        v, info = cpu_oracle_rate(args.dofs, 10)
+        line["cpu_baseline"] = {"value": v, "unit": "iterations/s", "cores": 1, "kind": "port",
+                                "sample": "numpy/scipy oracle port of bramblepasciak_new.py, 10 iterations at %d dofs "
+                                          "(same channel, coarser), its/s scaled by dof ratio; rate at sample %.2f its/s"
+                                          % (info["sample_dofs"], info["rate_at_sample"])}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -109,6 +109,9 @@ def buffer_of(x, dtype=np.float64):
         want = {np.float64: torch.float64, np.int32: torch.int32, np.int64: torch.int64, np.uint8: torch.uint8}[dtype]
         if x.dtype != want or not x.is_contiguous():
             raise TypeError("tensor must be contiguous %s" % want)
+        if x.is_cuda:
+            # the library runs on its own stream: work torch queued on this tensor must have landed
+            torch.cuda.current_stream(x.device).synchronize()
         return x.data_ptr(), x.numel(), x
     if isinstance(x, np.ndarray):
         if x.dtype != dtype or not x.flags.c_contiguous:
