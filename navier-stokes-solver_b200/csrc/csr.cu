@@ -192,6 +192,7 @@ int nsb_csr_create(nsb_ctx ctx, int64_t rows, int64_t cols, int64_t nnz, const v
             r = NSB_ERR_INVALID;
         }
     }
+    if (r == NSB_OK) r = build_lx(c, m);
     if (r != NSB_OK) {
         delete m;
         return r;
@@ -242,6 +243,7 @@ int nsb_csr_transpose(nsb_ctx ctx, nsb_mat a, nsb_mat* out) {
         set_error("nsb_csr_transpose: %s", cudaGetErrorString(e));
         r = NSB_ERR_CUDA;
     }
+    if (r == NSB_OK) r = build_lx(c, t);
     if (r != NSB_OK) {
         delete t;
         return r;
@@ -284,6 +286,7 @@ int nsb_saddle_create(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_mat C, 
         }
     }
     delete bt_owned;
+    if (r == NSB_OK) r = build_lx(c, K);
     if (r != NSB_OK) {
         delete K;
         return r;
@@ -304,6 +307,17 @@ int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz) {
     if (rows) *rows = m->rows;
     if (cols) *cols = m->cols;
     if (nnz) *nnz = m->nnz;
+    return NSB_OK;
+}
+
+int nsb_mat_format(nsb_mat m, int* lx_rows_per_chunk, int* lx_chunks, int* lx_max_distinct, int64_t* lx_total_distinct,
+                   int* threads_per_row) {
+    NSB_REQUIRE(m, "nsb_mat_format: NULL matrix");
+    if (lx_rows_per_chunk) *lx_rows_per_chunk = m->lx_R;
+    if (lx_chunks) *lx_chunks = m->lx_nchunks;
+    if (lx_max_distinct) *lx_max_distinct = m->lx_max_uniq;
+    if (lx_total_distinct) *lx_total_distinct = m->lx_total_uniq;
+    if (threads_per_row) *threads_per_row = m->threads_per_row;
     return NSB_OK;
 }
 
