@@ -87,11 +87,13 @@ NSB_API int nsb_csr_transpose(nsb_ctx ctx, nsb_mat a, nsb_mat* out);
 NSB_API int nsb_saddle_create(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_mat C, nsb_mat* out);
 NSB_API int nsb_mat_destroy(nsb_mat m);
 NSB_API int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz);
-/* storage actually used by the SpMV kernels: lx_rows_per_chunk > 0 when the chunk-local-index companion
- * (x staged in shared memory, 16-bit local column indices) is active, else the CSR-vector kernel runs.
- * total_distinct = sum over chunks of distinct columns (4 B each of extra index traffic per SpMV). */
-NSB_API int nsb_mat_format(nsb_mat m, int* lx_rows_per_chunk, int* lx_chunks, int* lx_max_distinct, int64_t* lx_total_distinct,
-                           int* threads_per_row);
+/* storage actually used by the SpMV kernels: rows_per_chunk > 0 when the SELL-LX companion (rows sorted by
+ * length inside chunks, sliced-ELL pair-blocks, x staged in shared memory, 16-bit chunk-local column indices)
+ * is active, else the CSR-vector kernel runs.  total_distinct = sum over chunks of distinct columns (4 B each
+ * of extra index traffic per SpMV); stored_nnz = nonzeros including slice padding; lanes_per_row = lanes that
+ * share a row in the active kernel. */
+NSB_API int nsb_mat_format(nsb_mat m, int* rows_per_chunk, int* chunks, int* max_distinct, int64_t* total_distinct,
+                           int* lanes_per_row, int64_t* stored_nnz);
 /* main diagonal of a square (or owned-square) operator, length rows */
 NSB_API int nsb_mat_diagonal(nsb_ctx ctx, nsb_mat m, double* out);
 /* y = M x   (the `mat * vec` primitive, e.g. minres.py:97).  x has `cols`, y has `rows` entries. */

@@ -50,10 +50,9 @@ extern thread_local char g_err[1024];
 constexpr int kBlock = 256;          // threads per block of the vector kernels
 constexpr int kMaxBlocks = 148 * 8;  // 148 SMs x 8 resident 256-thread blocks
 constexpr int kMaxRed = 4;           // doubles reduced per kernel at most
-// chunk-local-index ("LX") SpMV: block size, staged x entries per chunk, target nonzeros per chunk
-constexpr int kLxBlock = 512;
-constexpr int kLxCap = 8192;
-constexpr double kLxTargetNnz = 24000.0;
+// SELL-LX SpMV (spmv.cuh, sell.cu): staged x entries a chunk may need at most, target nonzeros per chunk
+constexpr int kSellCap = 8192;
+constexpr double kSellTargetNnz = 24000.0;
 
 inline int vec_grid(int64_t n, int num_sms) {
     int64_t want = (n + (int64_t)kBlock * 2 - 1) / ((int64_t)kBlock * 2);
@@ -140,11 +139,15 @@ struct nsb_mat_s {
     nsb::DevBuf<int32_t> colidx;  // nnz
     nsb::DevBuf<double> values;   // nnz
     int threads_per_row = 8;      // sub-warp width of the CSR-vector kernel, chosen from nnz/rows
-    // chunk-local column index companion (lx.cu); lx_R == 0 when absent
-    int lx_R = 0, lx_nchunks = 0, lx_max_uniq = 0, lx_total_uniq = 0;
-    nsb::DevBuf<unsigned short> lx_lcol;  // nnz: index into the chunk's distinct-column list
-    nsb::DevBuf<int32_t> lx_uptr;         // nchunks + 1
-    nsb::DevBuf<int32_t> lx_ucol;         // distinct columns, chunk by chunk, ascending
+    // SELL-LX companion (sell.cu); sell_R == 0 when absent (small or too scattered operators)
+    int sell_R = 0, sell_log2R = 0, sell_T = 1, sell_nchunks = 0, sell_max_uniq = 0, sell_cap = 0;
+    int64_t sell_total_uniq = 0, sell_stored = 0;   // distinct-column list length; stored (padded) nonzeros
+    nsb::DevBuf<double> sell_vals;            // pair-blocks of 32 x 2 values
+    nsb::DevBuf<unsigned short> sell_lcol;    // same layout: index into the chunk's distinct-column list
+    nsb::DevBuf<unsigned int> sell_off;       // per slice (+1), in pair-blocks
+    nsb::DevBuf<unsigned short> sell_perm;    // nchunks * R: sorted position -> row inside the chunk
+    nsb::DevBuf<int32_t> sell_uptr;           // nchunks + 1
+    nsb::DevBuf<int32_t> sell_ucol;           // distinct columns, chunk by chunk, ascending
     nsb_halo_s* halo = nullptr;   // not owned
     // saddle composition bookkeeping (rows of the velocity block; 0 for a plain matrix)
     int64_t n_u = 0, n_p = 0;
@@ -240,7 +243,7 @@ int vec_dot(Context& c, const double* x, const double* y, int64_t n, double* out
 int allreduce_sum(Context& c, double* dev, int count);                       // no-op for nranks == 1
 int halo_exchange(Context& c, nsb_halo_s* h, double* x);                     // fills x[n_owned .. n_owned+n_halo)
 
-int build_lx(Context& c, nsb_mat_s* m);   // lx.cu
+int build_sell(Context& c, nsb_mat_s* m);   // sell.cu
 
 // plain SpMV launch (spmv.cu): y = M x on the context stream; x must have room for the halo tail
 int spmv_plain(Context& c, const nsb_mat_s* m, const double* x, double* y);

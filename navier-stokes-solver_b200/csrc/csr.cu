@@ -192,7 +192,7 @@ int nsb_csr_create(nsb_ctx ctx, int64_t rows, int64_t cols, int64_t nnz, const v
             r = NSB_ERR_INVALID;
         }
     }
-    if (r == NSB_OK) r = build_lx(c, m);
+    if (r == NSB_OK) r = build_sell(c, m);
     if (r != NSB_OK) {
         delete m;
         return r;
@@ -243,7 +243,7 @@ int nsb_csr_transpose(nsb_ctx ctx, nsb_mat a, nsb_mat* out) {
         set_error("nsb_csr_transpose: %s", cudaGetErrorString(e));
         r = NSB_ERR_CUDA;
     }
-    if (r == NSB_OK) r = build_lx(c, t);
+    if (r == NSB_OK) r = build_sell(c, t);
     if (r != NSB_OK) {
         delete t;
         return r;
@@ -286,7 +286,7 @@ int nsb_saddle_create(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_mat C, 
         }
     }
     delete bt_owned;
-    if (r == NSB_OK) r = build_lx(c, K);
+    if (r == NSB_OK) r = build_sell(c, K);
     if (r != NSB_OK) {
         delete K;
         return r;
@@ -310,14 +310,15 @@ int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz) {
     return NSB_OK;
 }
 
-int nsb_mat_format(nsb_mat m, int* lx_rows_per_chunk, int* lx_chunks, int* lx_max_distinct, int64_t* lx_total_distinct,
-                   int* threads_per_row) {
+int nsb_mat_format(nsb_mat m, int* rows_per_chunk, int* chunks, int* max_distinct, int64_t* total_distinct,
+                   int* lanes_per_row, int64_t* stored_nnz) {
     NSB_REQUIRE(m, "nsb_mat_format: NULL matrix");
-    if (lx_rows_per_chunk) *lx_rows_per_chunk = m->lx_R;
-    if (lx_chunks) *lx_chunks = m->lx_nchunks;
-    if (lx_max_distinct) *lx_max_distinct = m->lx_max_uniq;
-    if (lx_total_distinct) *lx_total_distinct = m->lx_total_uniq;
-    if (threads_per_row) *threads_per_row = m->threads_per_row;
+    if (rows_per_chunk) *rows_per_chunk = m->sell_R;
+    if (chunks) *chunks = m->sell_nchunks;
+    if (max_distinct) *max_distinct = m->sell_max_uniq;
+    if (total_distinct) *total_distinct = m->sell_total_uniq;
+    if (lanes_per_row) *lanes_per_row = m->sell_R > 0 ? m->sell_T : m->threads_per_row;
+    if (stored_nnz) *stored_nnz = m->sell_R > 0 ? m->sell_stored : m->nnz;
     return NSB_OK;
 }
 

@@ -1,0 +1,293 @@
+// sell.cu -- builds the SELL-LX companion of a CSR operator on the device (kernel: spmv.cuh).
+//
+// Why this format.  ncu on the CSR-vector kernel (profiles/r1_spmv_csrvec_A_2Mdofs_ncu.csv) showed DRAM
+// traffic equal to the algorithmic bytes but the L1 data pipe at 72 %: every warp-wide gather of x touches
+// 5+ cache lines, so L1, not HBM, bounded it at ~60 % of the copy roofline.  The first fix (x staged in
+// shared memory, 16-bit chunk-local columns over plain CSR rows) reached 67 % of DRAM peak and was latency
+// bound (profiles/r1_bpcg_iteration_ncu.md: long-scoreboard stalls, dependent row-pointer -> value loads,
+// 64-bit / 16-bit loads).  SELL-LX keeps the staging and stores the nonzeros in the order the lanes
+// consume them:
+//   * rows are cut into chunks of R consecutive rows; per chunk the sorted set of distinct columns is
+//     stored once (ucol, 4 B each) and every nonzero stores a 16-bit index into that set (lcol);
+//   * inside a chunk the rows are sorted by length (sigma = R) and cut into slices of 32/T rows, T lanes
+//     per row; a slice is padded to its longest row and stored as pair-blocks of 32 lanes x 2 entries,
+//     so loads are 128-bit (values) / 32-bit (indices), fully coalesced, with no row pointers.
+// Traffic per SpMV: 10 B per stored nonzero (padding is 2-4 % on the P2/P1 blocks) + 4 B per distinct
+// column + 2 B per row (perm) + x once + y once.
+// An operator whose chunks need more than kSellCap distinct columns even at the smallest R keeps the
+// CSR-vector kernel.
+#include <cub/cub.cuh>
+#include <stdlib.h>
+
+#include "spmv.cuh"
+
+namespace nsb {
+
+// ---- chunk-local column numbering ----------------------------------------------------------------
+__global__ void k_sell_keys(CsrView A, int log2R, long long* __restrict__ keys, int* __restrict__ pos) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = warp; r < A.rows; r += nwarps) {
+        const int p0 = A.rowptr[r], p1 = A.rowptr[r + 1];
+        const long long hi = (long long)(r >> log2R) << 32;
+        for (int p = p0 + lane; p < p1; p += 32) {
+            keys[p] = hi | (long long)A.colidx[p];
+            pos[p] = p;
+        }
+    }
+}
+
+__global__ void k_sell_heads(const long long* __restrict__ keys, int* __restrict__ head, int64_t nnz) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (int64_t)gridDim.x * blockDim.x)
+        head[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1 : 0;
+}
+
+// uptr[c] = number of distinct (chunk, col) pairs with chunk < c
+__global__ void k_sell_uptr(const long long* __restrict__ keys, const int* __restrict__ gidx_incl, int64_t nnz,
+                            int* __restrict__ uptr, int nchunks) {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c <= nchunks; c += gridDim.x * blockDim.x) {
+        const long long target = (long long)c << 32;
+        int64_t lo = 0, hi = nnz;  // first i with keys[i] >= target
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (keys[mid] < target) lo = mid + 1;
+            else hi = mid;
+        }
+        uptr[c] = lo == 0 ? 0 : gidx_incl[lo - 1];
+    }
+}
+
+// lcol in CSR order (temporary) and the distinct-column lists
+__global__ void k_sell_localcols(const long long* __restrict__ keys, const int* __restrict__ pos,
+                                 const int* __restrict__ head, const int* __restrict__ gidx_incl,
+                                 const int* __restrict__ uptr, unsigned short* __restrict__ lcol_csr,
+                                 int* __restrict__ ucol, int64_t nnz) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (int64_t)gridDim.x * blockDim.x) {
+        const long long k = keys[i];
+        const int chunk = (int)(k >> 32);
+        const int g = gidx_incl[i] - 1;
+        lcol_csr[pos[i]] = (unsigned short)(g - uptr[chunk]);
+        if (head[i]) ucol[g] = (int)(k & 0xffffffffLL);
+    }
+}
+
+__global__ void k_sell_maxuniq(const int* __restrict__ uptr, int nchunks, int* __restrict__ out) {
+    int m = 0;
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < nchunks; c += gridDim.x * blockDim.x)
+        m = max(m, uptr[c + 1] - uptr[c]);
+    atomicMax(out, m);
+}
+
+// ---- sorting the rows of every chunk by length ------------------------------------------------------
+constexpr unsigned long long kLenMax = 0xFFFFFFull;
+
+// key = chunk | (kLenMax - len) | row-in-chunk : ascending sort = chunks in order, longest row first,
+// ties by row number (so neighbouring mesh rows stay neighbours).  Virtual rows past the end have len 0.
+__global__ void k_sell_rowkeys(CsrView A, int log2R, int64_t nvr, unsigned long long* __restrict__ keys) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvr; i += (int64_t)gridDim.x * blockDim.x) {
+        unsigned long long len = i < A.rows ? (unsigned long long)(A.rowptr[i + 1] - A.rowptr[i]) : 0ull;
+        if (len > kLenMax) len = kLenMax;
+        keys[i] = ((unsigned long long)(i >> log2R) << 40) | ((kLenMax - len) << 16) |
+                  (unsigned long long)(i & ((1LL << log2R) - 1));
+    }
+}
+
+// perm and the pair-block count of every slice (taken from the slice's first = longest row)
+__global__ void k_sell_slices(const unsigned long long* __restrict__ keys, int64_t nvr, int rps, int T,
+                              unsigned short* __restrict__ perm, unsigned int* __restrict__ npb) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvr; i += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long k = keys[i];
+        perm[i] = (unsigned short)(k & 0xFFFFull);
+        if (i % rps == 0) {
+            const unsigned int len = (unsigned int)(kLenMax - ((k >> 16) & kLenMax));
+            npb[i / rps] = (len + 2 * T - 1) / (2 * T);
+        }
+    }
+}
+
+// one warp per sorted row position: copy the row's entries to their lanes' slots
+__global__ void k_sell_fill(CsrView A, const unsigned short* __restrict__ lcol_csr, int log2R, int64_t nvr, int rps, int T,
+                            const unsigned short* __restrict__ perm, const unsigned int* __restrict__ off,
+                            double* __restrict__ vals, unsigned short* __restrict__ lcol) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t i = warp; i < nvr; i += nwarps) {
+        const int64_t r = ((i >> log2R) << log2R) + perm[i];
+        if (r >= A.rows) continue;
+        const int p0 = A.rowptr[r], len = A.rowptr[r + 1] - p0;
+        const int64_t base = (int64_t)off[i / rps] * 64;
+        const int ris = (int)(i % rps);
+        for (int e = lane; e < len; e += 32) {
+            const int pair = e >> 1;
+            const int64_t dst = base + (int64_t)(pair / T) * 64 + (ris * T + pair % T) * 2 + (e & 1);
+            vals[dst] = A.values[p0 + e];
+            lcol[dst] = lcol_csr[p0 + e];
+        }
+    }
+}
+
+static int ilog2(int64_t v) {
+    int l = 0;
+    while ((1LL << (l + 1)) <= v) ++l;
+    return l;
+}
+
+static int pick_lanes_per_row(double mean) {
+    const char* env = getenv("NSB_SELL_T");
+    if (env) {
+        int v = atoi(env);
+        if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) return v;
+    }
+    if (mean <= 48.0) return 1;
+    if (mean <= 96.0) return 2;
+    if (mean <= 192.0) return 4;
+    if (mean <= 384.0) return 8;
+    if (mean <= 768.0) return 16;
+    return 32;
+}
+
+// Try to build the SELL-LX companion of m.  Leaves m->sell_R == 0 when the operator does not qualify.
+int build_sell(Context& c, nsb_mat_s* m) {
+    m->sell_R = 0;
+    const char* env = getenv("NSB_SELL");
+    if (env && atoi(env) == 0) return NSB_OK;
+    const int64_t nnz = m->nnz, rows = m->rows;
+    const int64_t min_nnz = getenv("NSB_SELL_MIN_NNZ") ? atoll(getenv("NSB_SELL_MIN_NNZ")) : 200000;
+    const bool debug = getenv("NSB_SELL_DEBUG") != nullptr;
+    if (nnz < min_nnz || rows < 1 || nnz < 1) return NSB_OK;
+    const double mean = (double)nnz / (double)rows;
+    const int T = pick_lanes_per_row(mean);
+    const int rps = 32 / T;
+    const int minlog = ilog2((int64_t)rps * kSellWarps);   // at least one slice per warp
+    double want = kSellTargetNnz / (mean > 1.0 ? mean : 1.0);
+    int log2R = ilog2((int64_t)(want * 1.41421356));        // nearest power of two
+    const char* envR = getenv("NSB_SELL_LOG2R");
+    if (envR) log2R = atoi(envR);
+    if (log2R > 11) log2R = 11;
+    if (log2R < minlog) log2R = minlog;
+    CsrView A = view_of(m);
+    const int vg = vec_grid(nnz, c.num_sms);
+
+    // ---- phase A: chunk-local column numbering (largest R whose chunks fit the staging buffer)
+    DevBuf<unsigned short> lcol_csr;
+    int nchunks = 0, max_uniq = 0, total_uniq = 0;
+    bool found = false;
+    {
+        DevBuf<long long> k0, k1;
+        DevBuf<int> p0, p1, head, gidx, dmax;
+        DevBuf<char> tmp;
+        NSB_CHECK(k0.alloc(nnz));
+        NSB_CHECK(k1.alloc(nnz));
+        NSB_CHECK(p0.alloc(nnz));
+        NSB_CHECK(p1.alloc(nnz));
+        NSB_CHECK(head.alloc(nnz));
+        NSB_CHECK(gidx.alloc(nnz));
+        NSB_CHECK(dmax.alloc(1));
+        size_t sort_bytes = 0, scan_bytes = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, k0.p, k1.p, p0.p, p1.p, (int)nnz, 0, 64, c.stream);
+        cub::DeviceScan::InclusiveSum(nullptr, scan_bytes, head.p, gidx.p, (int)nnz, c.stream);
+        NSB_CHECK(tmp.alloc((int64_t)(sort_bytes > scan_bytes ? sort_bytes : scan_bytes) + 16));
+        for (; log2R >= minlog && !found; --log2R) {
+            const int64_t R = 1LL << log2R;
+            nchunks = (int)((rows + R - 1) / R);
+            const int end_bit = 32 + ilog2(nchunks) + 1;
+            const int64_t kg = (rows + 7) / 8 < (int64_t)c.num_sms * 8 ? (rows + 7) / 8 : (int64_t)c.num_sms * 8;
+            k_sell_keys<<<(int)kg, kBlock, 0, c.stream>>>(A, log2R, k0.p, p0.p);
+            NSB_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, sort_bytes, k0.p, k1.p, p0.p, p1.p, (int)nnz, 0,
+                                                     end_bit < 64 ? end_bit : 64, c.stream));
+            k_sell_heads<<<vg, kBlock, 0, c.stream>>>(k1.p, head.p, nnz);
+            NSB_CUDA(cub::DeviceScan::InclusiveSum(tmp.p, scan_bytes, head.p, gidx.p, (int)nnz, c.stream));
+            DevBuf<int> uptr;
+            NSB_CHECK(uptr.alloc(nchunks + 1));
+            k_sell_uptr<<<(nchunks + 1 + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(k1.p, gidx.p, nnz, uptr.p, nchunks);
+            NSB_CUDA(cudaMemsetAsync(dmax.p, 0, sizeof(int), c.stream));
+            k_sell_maxuniq<<<(nchunks + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(uptr.p, nchunks, dmax.p);
+            int h[2] = {0, 0};
+            NSB_CUDA(cudaMemcpyAsync(&h[0], dmax.p, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+            NSB_CUDA(cudaMemcpyAsync(&h[1], uptr.p + nchunks, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+            NSB_CUDA(cudaStreamSynchronize(c.stream));
+            if (debug)
+                fprintf(stderr, "[sell] rows=%lld nnz=%lld T=%d log2R=%d nchunks=%d max_distinct=%d total=%d\n",
+                        (long long)rows, (long long)nnz, T, log2R, nchunks, h[0], h[1]);
+            if (h[0] > kSellCap) continue;  // too many distinct columns for the staging buffer: halve the chunk
+            NSB_CHECK(lcol_csr.alloc(nnz));
+            NSB_CHECK(m->sell_ucol.alloc(h[1] > 0 ? h[1] : 1));
+            k_sell_localcols<<<vg, kBlock, 0, c.stream>>>(k1.p, p1.p, head.p, gidx.p, uptr.p, lcol_csr.p, m->sell_ucol.p, nnz);
+            NSB_CUDA(cudaStreamSynchronize(c.stream));
+            m->sell_uptr.release();
+            m->sell_uptr.p = uptr.p;   // adopt
+            m->sell_uptr.n = uptr.n;
+            uptr.p = nullptr;
+            max_uniq = h[0];
+            total_uniq = h[1];
+            found = true;
+            break;
+        }
+    }
+    if (!found) {
+        m->sell_ucol.release();
+        return NSB_OK;
+    }
+    const int64_t R = 1LL << log2R;
+    const int64_t nvr = (int64_t)nchunks * R;        // virtual rows (last chunk padded)
+    const int64_t nslices = nvr / rps;
+
+    // ---- phase B: sort the rows of each chunk by length, lay out the slices
+    DevBuf<unsigned long long> rk0, rk1;
+    DevBuf<unsigned int> npb;
+    DevBuf<char> tmp;
+    NSB_CHECK(rk0.alloc(nvr));
+    NSB_CHECK(rk1.alloc(nvr));
+    NSB_CHECK(npb.alloc(nslices + 1));
+    NSB_CHECK(m->sell_perm.alloc(nvr));
+    NSB_CHECK(m->sell_off.alloc(nslices + 1));
+    size_t sort_bytes = 0, scan_bytes = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, rk0.p, rk1.p, (int)nvr, 0, 64, c.stream);
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, npb.p, m->sell_off.p, (int)(nslices + 1), c.stream);
+    NSB_CHECK(tmp.alloc((int64_t)(sort_bytes > scan_bytes ? sort_bytes : scan_bytes) + 16));
+    const int rg = vec_grid(nvr, c.num_sms);
+    k_sell_rowkeys<<<rg, kBlock, 0, c.stream>>>(A, log2R, nvr, rk0.p);
+    const int end_bit = 40 + ilog2(nchunks) + 1;
+    NSB_CUDA(cub::DeviceRadixSort::SortKeys(tmp.p, sort_bytes, rk0.p, rk1.p, (int)nvr, 0, end_bit < 64 ? end_bit : 64, c.stream));
+    NSB_CUDA(cudaMemsetAsync(npb.p, 0, sizeof(unsigned int) * (size_t)(nslices + 1), c.stream));
+    k_sell_slices<<<rg, kBlock, 0, c.stream>>>(rk1.p, nvr, rps, T, m->sell_perm.p, npb.p);
+    NSB_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, scan_bytes, npb.p, m->sell_off.p, (int)(nslices + 1), c.stream));
+    unsigned int total_pb = 0;
+    NSB_CUDA(cudaMemcpyAsync(&total_pb, m->sell_off.p + nslices, sizeof(unsigned int), cudaMemcpyDeviceToHost, c.stream));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    const int64_t stored = (int64_t)total_pb * 64;
+    if (stored > 6 * nnz + 4096 || total_pb > 0x7FFFFFFFu / 2) {   // pathological padding: keep CSR-vector
+        if (debug) fprintf(stderr, "[sell] rejected: stored=%lld for nnz=%lld\n", (long long)stored, (long long)nnz);
+        m->sell_perm.release();
+        m->sell_off.release();
+        m->sell_uptr.release();
+        m->sell_ucol.release();
+        return NSB_OK;
+    }
+    NSB_CHECK(m->sell_vals.alloc(stored > 0 ? stored : 64));
+    NSB_CHECK(m->sell_lcol.alloc(stored > 0 ? stored : 64));
+    NSB_CUDA(cudaMemsetAsync(m->sell_vals.p, 0, sizeof(double) * (size_t)(stored > 0 ? stored : 64), c.stream));
+    NSB_CUDA(cudaMemsetAsync(m->sell_lcol.p, 0, sizeof(unsigned short) * (size_t)(stored > 0 ? stored : 64), c.stream));
+    const int64_t fg = (nvr + 7) / 8 < (int64_t)c.num_sms * 8 ? (nvr + 7) / 8 : (int64_t)c.num_sms * 8;
+    k_sell_fill<<<(int)fg, kBlock, 0, c.stream>>>(A, lcol_csr.p, log2R, nvr, rps, T, m->sell_perm.p, m->sell_off.p,
+                                                 m->sell_vals.p, m->sell_lcol.p);
+    NSB_CUDA(cudaGetLastError());
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    m->sell_R = (int)R;
+    m->sell_log2R = log2R;
+    m->sell_T = T;
+    m->sell_nchunks = nchunks;
+    m->sell_max_uniq = max_uniq;
+    m->sell_cap = (max_uniq + 31) & ~31;
+    if (m->sell_cap < 32) m->sell_cap = 32;
+    m->sell_total_uniq = total_uniq;
+    m->sell_stored = stored;
+    if (debug)
+        fprintf(stderr, "[sell] built: R=%lld T=%d chunks=%d stored=%lld (%.2f%% padding) smem=%zu B\n", (long long)R, T, nchunks,
+                (long long)stored, 100.0 * (double)(stored - nnz) / (double)nnz, sell_smem_bytes(m));
+    return NSB_OK;
+}
+
+}  // namespace nsb

@@ -124,69 +124,116 @@ inline int spmv_grid(int64_t rows, int tpr, int num_sms) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// LX kernel: x staged in shared memory per chunk of rows, 16-bit chunk-local column indices (lx.cu).
-// Lane l of a TPR-wide group takes nonzeros p0+l, p0+l+TPR, ... so a group reads contiguous runs of the
-// value stream (64-bit loads) and of the index stream (16-bit loads) and consecutive columns land
-// in consecutive shared-memory banks; four loads per stream are in flight per lane.
-struct LxView {
-    int R, nchunks;
+// SELL-LX kernel: sliced-ELL storage sorted inside chunks of R rows, x staged in shared memory per
+// chunk, 16-bit chunk-local column indices (format built by sell.cu).
+//
+//   chunk   = R consecutive rows; its distinct columns are listed once (ucol) and x[ucol] is staged into
+//             shared memory with coalesced loads, so the per-nonzero gather costs shared-memory bank
+//             cycles instead of L1/L2 sectors and the index stream is 2 B per nonzero;
+//   slice   = 32/T rows of a chunk after sorting the chunk's rows by length; T lanes share a row.  A slice
+//             is stored as pair-blocks of 32 x (2 values) so that every lane issues 128-bit value loads and
+//             32-bit index loads and a warp reads 512 B / 128 B contiguous per load;
+//   warp    = takes the slices of a chunk in snake order (longest with shortest) so the warps of a block
+//             finish together; no row pointers are read.
+// Row sums land in shared memory (sy) in natural row order; after a barrier the RowOp epilogue runs
+// with thread t on row r0 + t, so every fused vector read/write is coalesced.
+constexpr int kSellBlock = 256;
+constexpr int kSellWarps = kSellBlock / 32;
+constexpr int kSellMaxSmem = 160 * 1024;
+
+struct SellView {
+    int64_t rows;
+    int R, log2R, nchunks, nsl;   // rows per chunk, chunks, slices per chunk (R * T / 32)
+    int cap;                      // staged x entries a chunk may need (max distinct columns, padded)
+    const double* __restrict__ vals;
     const unsigned short* __restrict__ lcol;
+    const unsigned int* __restrict__ off;      // per slice, in pair-blocks (64 elements)
+    const unsigned short* __restrict__ perm;   // sorted position -> row inside the chunk
     const int* __restrict__ uptr;
     const int* __restrict__ ucol;
 };
 
-template <int TPR, int NS, class RowOp>
-__global__ void __launch_bounds__(kLxBlock) spmv_lx_kernel(CsrView A, LxView L, const double* __restrict__ x, RowOp op,
-                                                           double* partials, unsigned int* ticket) {
-    extern __shared__ double sx[];
+__device__ __forceinline__ unsigned int ld_stream_b32(const void* p) {
+    unsigned int r;
+    asm volatile("ld.global.nc.L1::no_allocate.b32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+
+template <int T, int NS, class RowOp>
+__global__ void __launch_bounds__(kSellBlock) spmv_sell_kernel(SellView S, const double* __restrict__ x, RowOp op,
+                                                               double* partials, unsigned int* ticket) {
+    extern __shared__ double smem[];
     if (op.skip()) return;
+    double* sx = smem;
+    double* sy = smem + S.cap;
+    unsigned int* soff = reinterpret_cast<unsigned int*>(sy + S.R);
     constexpr int NSA = NS > 0 ? NS : 1;
-    constexpr int GPB = kLxBlock / TPR;
+    constexpr int RPS = 32 / T;   // rows per slice
     double acc[NSA];
 #pragma unroll
     for (int k = 0; k < NSA; ++k) acc[k] = 0.0;
-    const int lane = threadIdx.x & (TPR - 1);
-    const int gib = threadIdx.x / TPR;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-    for (int chunk = blockIdx.x; chunk < L.nchunks; chunk += gridDim.x) {
-        const int u0 = __ldg(L.uptr + chunk);
-        const int nu = __ldg(L.uptr + chunk + 1) - u0;
-        __syncthreads();  // the previous chunk's gathers are done with sx
-        for (int i = threadIdx.x; i < nu; i += 4 * kLxBlock) {
+    for (int chunk = blockIdx.x; chunk < S.nchunks; chunk += gridDim.x) {
+        const int u0 = __ldg(S.uptr + chunk);
+        const int nu = __ldg(S.uptr + chunk + 1) - u0;
+        __syncthreads();   // previous chunk: gathers done with sx, epilogue done with sy
+        for (int i = threadIdx.x; i <= S.nsl; i += kSellBlock) soff[i] = __ldg(S.off + (size_t)chunk * S.nsl + i);
+        for (int i = threadIdx.x; i < nu; i += 4 * kSellBlock) {
             int c[4];
             double v[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) c[k] = (i + k * kLxBlock < nu) ? __ldg(L.ucol + u0 + i + k * kLxBlock) : 0;
+            for (int k = 0; k < 4; ++k) c[k] = (i + k * kSellBlock < nu) ? __ldg(S.ucol + u0 + i + k * kSellBlock) : 0;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) v[k] = (i + k * kLxBlock < nu) ? __ldg(x + c[k]) : 0.0;
+            for (int k = 0; k < 4; ++k) v[k] = (i + k * kSellBlock < nu) ? __ldg(x + c[k]) : 0.0;
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-                if (i + k * kLxBlock < nu) sx[i + k * kLxBlock] = v[k];
+                if (i + k * kSellBlock < nu) sx[i + k * kSellBlock] = v[k];
         }
         __syncthreads();
-        const int64_t r0 = (int64_t)chunk * L.R;
-        for (int rb = 0; rb < L.R; rb += GPB) {
-            if (r0 + rb >= A.rows) break;  // block-uniform
-            const int64_t r = r0 + rb + gib;
-            const bool valid = r < A.rows;
-            const int p0 = valid ? __ldg(A.rowptr + r) : 0;
-            const int p1 = valid ? __ldg(A.rowptr + r + 1) : 0;
-            double s = 0.0;
-            for (int p = p0 + lane; p < p1; p += 4 * TPR) {
-                double v[4];
-                unsigned short lc[4];
+        for (int base = 0, pass = 0; base < S.nsl; base += kSellWarps, ++pass) {
+            // snake order over the length-sorted slices
+            const int cnt = min(kSellWarps, S.nsl - base);
+            if (warp >= cnt) continue;
+            const int sl = base + ((pass & 1) ? cnt - 1 - warp : warp);
+            const unsigned int o0 = soff[sl], o1 = soff[sl + 1];
+            const int k = sl * RPS + lane / T;   // sorted position inside the chunk
+            const unsigned short lr = __ldg(S.perm + ((size_t)chunk << S.log2R) + k);
+            const double2* vp = reinterpret_cast<const double2*>(S.vals) + (size_t)o0 * 32 + lane;
+            const unsigned int* cp = reinterpret_cast<const unsigned int*>(S.lcol) + (size_t)o0 * 32 + lane;
+            const int n = (int)(o1 - o0);
+            double s0 = 0.0, s1 = 0.0;
+            int j = 0;
+            for (; j + 4 <= n; j += 4) {
+                double2 v[4];
+                unsigned int c[4];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const bool on = p + k * TPR < p1;
-                    v[k] = on ? __ldg(A.values + p + k * TPR) : 0.0;
-                    lc[k] = on ? __ldg(L.lcol + p + k * TPR) : (unsigned short)0;
+                for (int k2 = 0; k2 < 4; ++k2) {
+                    v[k2] = ld_stream_f64x2(reinterpret_cast<const double*>(vp + (size_t)(j + k2) * 32));
+                    c[k2] = ld_stream_b32(cp + (size_t)(j + k2) * 32);
                 }
 #pragma unroll
-                for (int k = 0; k < 4; ++k) s = fma(v[k], sx[lc[k]], s);
+                for (int k2 = 0; k2 < 4; ++k2) {
+                    s0 = fma(v[k2].x, sx[c[k2] & 0xffffu], s0);
+                    s1 = fma(v[k2].y, sx[c[k2] >> 16], s1);
+                }
             }
+            for (; j < n; ++j) {
+                const double2 v = ld_stream_f64x2(reinterpret_cast<const double*>(vp + (size_t)j * 32));
+                const unsigned int c = ld_stream_b32(cp + (size_t)j * 32);
+                s0 = fma(v.x, sx[c & 0xffffu], s0);
+                s1 = fma(v.y, sx[c >> 16], s1);
+            }
+            double s = s0 + s1;
 #pragma unroll
-            for (int o = TPR / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0 && valid) op.row(r, s, acc);
+            for (int o = T / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if ((lane & (T - 1)) == 0) sy[lr] = s;
+        }
+        __syncthreads();
+        const int64_t r0 = (int64_t)chunk << S.log2R;
+        for (int t = threadIdx.x; t < S.R; t += kSellBlock) {
+            const int64_t r = r0 + t;
+            if (r < S.rows) op.row(r, sy[t], acc);
         }
     }
     if constexpr (NS > 0) {
@@ -196,21 +243,36 @@ __global__ void __launch_bounds__(kLxBlock) spmv_lx_kernel(CsrView A, LxView L, 
     }
 }
 
-template <int TPR, int NS, class RowOp>
-int spmv_lx_launch_t(Context& c, const nsb_mat_s* m, const double* x, RowOp op) {
-    static int blocks_per_sm = 0;   // per instantiation
-    const size_t smem = sizeof(double) * kLxCap;
-    if (blocks_per_sm == 0) {
-        NSB_CUDA(cudaFuncSetAttribute(spmv_lx_kernel<TPR, NS, RowOp>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        int b = 0;
-        NSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, spmv_lx_kernel<TPR, NS, RowOp>, kLxBlock, smem));
-        blocks_per_sm = b > 0 ? b : 1;
+inline SellView sell_view_of(const nsb_mat_s* m) {
+    return SellView{m->rows, m->sell_R, m->sell_log2R, m->sell_nchunks, m->sell_R * m->sell_T / 32, m->sell_cap,
+                    m->sell_vals.p, m->sell_lcol.p, m->sell_off.p, m->sell_perm.p, m->sell_uptr.p, m->sell_ucol.p};
+}
+
+inline size_t sell_smem_bytes(const nsb_mat_s* m) {
+    const int nsl = m->sell_R * m->sell_T / 32;
+    return sizeof(double) * ((size_t)m->sell_cap + m->sell_R) + sizeof(unsigned int) * ((size_t)nsl + 2);
+}
+
+template <int T, int NS, class RowOp>
+int spmv_sell_launch_t(Context& c, const nsb_mat_s* m, const double* x, RowOp op) {
+    static bool attr_set = false;        // per instantiation
+    static size_t cached_smem = ~(size_t)0;
+    static int cached_bps = 0;
+    const size_t smem = sell_smem_bytes(m);
+    if (!attr_set) {
+        NSB_CUDA(cudaFuncSetAttribute(spmv_sell_kernel<T, NS, RowOp>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSellMaxSmem));
+        attr_set = true;
     }
-    int grid = c.num_sms * blocks_per_sm;
-    if (grid > m->lx_nchunks) grid = m->lx_nchunks;
+    if (smem != cached_smem) {
+        int b = 0;
+        NSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, spmv_sell_kernel<T, NS, RowOp>, kSellBlock, smem));
+        cached_bps = b > 0 ? b : 1;
+        cached_smem = smem;
+    }
+    int grid = c.num_sms * cached_bps;
+    if (grid > m->sell_nchunks) grid = m->sell_nchunks;
     if (grid > c.max_grid) grid = c.max_grid;
-    LxView L{m->lx_R, m->lx_nchunks, m->lx_lcol.p, m->lx_uptr.p, m->lx_ucol.p};
-    spmv_lx_kernel<TPR, NS, RowOp><<<grid, kLxBlock, smem, c.stream>>>(view_of(m), L, x, op, c.partials, c.ticket);
+    spmv_sell_kernel<T, NS, RowOp><<<grid, kSellBlock, smem, c.stream>>>(sell_view_of(m), x, op, c.partials, c.ticket);
     c.launches++;
     NSB_CUDA(cudaGetLastError());
     return NSB_OK;
@@ -219,13 +281,14 @@ int spmv_lx_launch_t(Context& c, const nsb_mat_s* m, const double* x, RowOp op) 
 // Launch with the matrix's sub-warp width.  x must cover cols (+ halo tail when partitioned).
 template <int NS, class RowOp>
 int spmv_launch(Context& c, const nsb_mat_s* m, const double* x, RowOp op) {
-    if (m->lx_R > 0) {
-        switch (m->threads_per_row) {
-            case 2: return spmv_lx_launch_t<2, NS, RowOp>(c, m, x, op);
-            case 4: return spmv_lx_launch_t<4, NS, RowOp>(c, m, x, op);
-            case 8: return spmv_lx_launch_t<8, NS, RowOp>(c, m, x, op);
-            case 16: return spmv_lx_launch_t<16, NS, RowOp>(c, m, x, op);
-            default: return spmv_lx_launch_t<32, NS, RowOp>(c, m, x, op);
+    if (m->sell_R > 0) {
+        switch (m->sell_T) {
+            case 1: return spmv_sell_launch_t<1, NS, RowOp>(c, m, x, op);
+            case 2: return spmv_sell_launch_t<2, NS, RowOp>(c, m, x, op);
+            case 4: return spmv_sell_launch_t<4, NS, RowOp>(c, m, x, op);
+            case 8: return spmv_sell_launch_t<8, NS, RowOp>(c, m, x, op);
+            case 16: return spmv_sell_launch_t<16, NS, RowOp>(c, m, x, op);
+            default: return spmv_sell_launch_t<32, NS, RowOp>(c, m, x, op);
         }
     }
     CsrView A = view_of(m);

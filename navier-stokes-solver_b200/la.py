@@ -323,14 +323,14 @@ class SparseMatrix(BaseMatrix):
         self._T, t._T = t, self
 
     def format(self):
-        """Which SpMV kernel this operator runs: dict(lx_rows_per_chunk, lx_chunks, lx_max_distinct,
-        lx_total_distinct, threads_per_row); lx_rows_per_chunk == 0 means the plain CSR-vector kernel."""
+        """Which SpMV kernel this operator runs: dict(rows_per_chunk, chunks, max_distinct, total_distinct,
+        lanes_per_row, stored_nnz); rows_per_chunk == 0 means the plain CSR-vector kernel, > 0 the SELL-LX kernel."""
         a, b, c_, t = C.c_int(), C.c_int(), C.c_int(), C.c_int()
-        d = C.c_int64()
-        _lib.check(self.ctx._lib.nsb_mat_format(self.h, C.byref(a), C.byref(b), C.byref(c_), C.byref(d), C.byref(t)),
-                   "nsb_mat_format")
-        return dict(lx_rows_per_chunk=a.value, lx_chunks=b.value, lx_max_distinct=c_.value, lx_total_distinct=d.value,
-                    threads_per_row=t.value)
+        d, e = C.c_int64(), C.c_int64()
+        _lib.check(self.ctx._lib.nsb_mat_format(self.h, C.byref(a), C.byref(b), C.byref(c_), C.byref(d), C.byref(t),
+                                                C.byref(e)), "nsb_mat_format")
+        return dict(rows_per_chunk=a.value, chunks=b.value, max_distinct=c_.value, total_distinct=d.value,
+                    lanes_per_row=t.value, stored_nnz=e.value)
 
     def diagonal(self):
         out = np.empty(self.height)

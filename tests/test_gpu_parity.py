@@ -109,24 +109,24 @@ def test_spmv_ragged_and_empty_rows(nsb):
 
 
 @pytest.mark.parametrize("log2r", [None, 3, 5, 7])
-def test_spmv_lx_format_matches_scipy(nsb, cases, monkeypatch, log2r):
-    """The chunk-local-index kernel (x staged in shared memory) forced on the small cases."""
+def test_spmv_sell_format_matches_scipy(nsb, cases, monkeypatch, log2r):
+    """The SELL-LX kernel (sorted sliced-ELL, x staged in shared memory) forced on the small cases."""
     import scipy.sparse as sp
-    monkeypatch.setenv("NSB_LX_MIN_NNZ", "0")
+    monkeypatch.setenv("NSB_SELL_MIN_NNZ", "0")
     if log2r is not None:
-        monkeypatch.setenv("NSB_LX_LOG2R", str(log2r))
+        monkeypatch.setenv("NSB_SELL_LOG2R", str(log2r))
     c = cases("chan3d")
     rng = np.random.default_rng(11)
     xu, xp = rng.uniform(-1, 1, c.n_u), rng.uniform(-1, 1, c.n_p)
     A, B = nsb.SparseMatrix.from_scipy(c.A), nsb.SparseMatrix.from_scipy(c.B)
     BT = B.T
     for M in (A, B, BT):
-        assert M.format()["lx_rows_per_chunk"] > 0
+        assert M.format()["rows_per_chunk"] > 0
     np.testing.assert_allclose((A * xu).NumPy(), c.A @ xu, rtol=0, atol=1e-12)
     np.testing.assert_allclose((B * xu).NumPy(), c.B @ xu, rtol=0, atol=1e-12)
     np.testing.assert_allclose((BT * xp).NumPy(), c.BT @ xp, rtol=0, atol=1e-12)
     K = nsb.BlockMatrix([[A, BT], [B, None]])
-    assert K.saddle().format()["lx_rows_per_chunk"] > 0
+    assert K.saddle().format()["rows_per_chunk"] > 0
     yr = np.concatenate([c.A @ xu + c.BT @ xp, c.B @ xu])
     np.testing.assert_allclose((K * np.concatenate([xu, xp])).NumPy(), yr, rtol=0, atol=1e-12)
     # ragged: dense row, empty rows, wide column spread (forces small chunks or the CSR-vector fallback)
@@ -140,10 +140,10 @@ def test_spmv_lx_format_matches_scipy(nsb, cases, monkeypatch, log2r):
     np.testing.assert_allclose((D * x).NumPy(), M @ x, rtol=0, atol=1e-11)
 
 
-def test_solvers_on_lx_format(nsb, cases, monkeypatch):
-    """MinRes and BPCG parity with every operator in the LX format."""
+def test_solvers_on_sell_format(nsb, cases, monkeypatch):
+    """MinRes and BPCG parity with every operator in the SELL-LX format."""
     from oracle.cases import load_golden
-    monkeypatch.setenv("NSB_LX_MIN_NNZ", "0")
+    monkeypatch.setenv("NSB_SELL_MIN_NNZ", "0")
     c = cases("chan3d")
     A, B = nsb.SparseMatrix.from_scipy(c.A), nsb.SparseMatrix.from_scipy(c.B)
     pA, pM = nsb.DiagonalPreconditioner.from_diagonal(c.dA), nsb.DiagonalPreconditioner.from_diagonal(c.dM)

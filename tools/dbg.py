@@ -1,6 +1,6 @@
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-os.environ["NSB_LX_MIN_NNZ"]="0"; os.environ["NSB_LX_DEBUG"]="1"
+os.environ["NSB_SELL_MIN_NNZ"]="0"; os.environ["NSB_SELL_DEBUG"]="1"
 import numpy as np
 import navier_stokes_solver_b200 as nsb
 from oracle.cases import Case
