@@ -21,6 +21,7 @@ LIB = os.path.join(HERE, "libnsb200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr"]
+FLAGS += os.environ.get("NSB_NVCC_EXTRA", "").split()   # tuning sweeps: e.g. -DNSB_SELL_UNROLL=4
 
 
 def _sources():

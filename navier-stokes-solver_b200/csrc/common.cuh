@@ -50,8 +50,9 @@ extern thread_local char g_err[1024];
 constexpr int kBlock = 256;          // threads per block of the vector kernels
 constexpr int kMaxBlocks = 148 * 8;  // 148 SMs x 8 resident 256-thread blocks
 constexpr int kMaxRed = 4;           // doubles reduced per kernel at most
-// SELL-LX SpMV (spmv.cuh, sell.cu): staged x entries a chunk may need at most, target nonzeros per chunk
-constexpr int kSellCap = 8192;
+// SELL-LX SpMV (spmv.cuh, sell.cu): shared-memory doubles a chunk may stage (distinct columns + R row
+// sums; 36 KB per block), target nonzeros per chunk
+constexpr int kSellStage = 4600;
 constexpr double kSellTargetNnz = 24000.0;
 
 inline int vec_grid(int64_t n, int num_sms) {

@@ -14,8 +14,10 @@
 //     so loads are 128-bit (values) / 32-bit (indices), fully coalesced, with no row pointers.
 // Traffic per SpMV: 10 B per stored nonzero (padding is 2-4 % on the P2/P1 blocks) + 4 B per distinct
 // column + 2 B per row (perm) + x once + y once.
-// An operator whose chunks need more than kSellCap distinct columns even at the smallest R keeps the
-// CSR-vector kernel.
+// R is the largest power of two whose staging buffers (distinct columns + R row sums) fit kSellStage
+// doubles: 4 resident blocks then use ~144 KB of shared memory and leave ~84 KB of L1 for the x gathers of
+// the staging phase (with 228 KB of shared memory in use the same kernel ran 20 % slower).  An operator
+// that does not fit even at the smallest R keeps the CSR-vector kernel.
 #include <cub/cub.cuh>
 #include <stdlib.h>
 
@@ -140,11 +142,12 @@ static int pick_lanes_per_row(double mean) {
         int v = atoi(env);
         if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) return v;
     }
-    if (mean <= 48.0) return 1;
-    if (mean <= 96.0) return 2;
-    if (mean <= 192.0) return 4;
-    if (mean <= 384.0) return 8;
-    if (mean <= 768.0) return 16;
+    // measured on the 20M-dof P2/P1 blocks (tools/sweep_sell.sh): A (28/row) best at 1, B (189/row) at 8
+    if (mean <= 32.0) return 1;
+    if (mean <= 64.0) return 2;
+    if (mean <= 128.0) return 4;
+    if (mean <= 256.0) return 8;
+    if (mean <= 512.0) return 16;
     return 32;
 }
 
@@ -211,7 +214,7 @@ int build_sell(Context& c, nsb_mat_s* m) {
             if (debug)
                 fprintf(stderr, "[sell] rows=%lld nnz=%lld T=%d log2R=%d nchunks=%d max_distinct=%d total=%d\n",
                         (long long)rows, (long long)nnz, T, log2R, nchunks, h[0], h[1]);
-            if (h[0] > kSellCap) continue;  // too many distinct columns for the staging buffer: halve the chunk
+            if (h[0] + R > kSellStage) continue;  // staging buffers (x + row sums) over budget: halve the chunk
             NSB_CHECK(lcol_csr.alloc(nnz));
             NSB_CHECK(m->sell_ucol.alloc(h[1] > 0 ? h[1] : 1));
             k_sell_localcols<<<vg, kBlock, 0, c.stream>>>(k1.p, p1.p, head.p, gidx.p, uptr.p, lcol_csr.p, m->sell_ucol.p, nnz);

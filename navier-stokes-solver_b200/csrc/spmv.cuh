@@ -140,6 +140,12 @@ inline int spmv_grid(int64_t rows, int tpr, int num_sms) {
 constexpr int kSellBlock = 256;
 constexpr int kSellWarps = kSellBlock / 32;
 constexpr int kSellMaxSmem = 160 * 1024;
+#ifndef NSB_SELL_UNROLL
+#define NSB_SELL_UNROLL 8
+#endif
+#ifndef NSB_SELL_MINBLOCKS
+#define NSB_SELL_MINBLOCKS 4
+#endif
 
 struct SellView {
     int64_t rows;
@@ -160,7 +166,7 @@ __device__ __forceinline__ unsigned int ld_stream_b32(const void* p) {
 }
 
 template <int T, int NS, class RowOp>
-__global__ void __launch_bounds__(kSellBlock) spmv_sell_kernel(SellView S, const double* __restrict__ x, RowOp op,
+__global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kernel(SellView S, const double* __restrict__ x, RowOp op,
                                                                double* partials, unsigned int* ticket) {
     extern __shared__ double smem[];
     if (op.skip()) return;
@@ -169,6 +175,7 @@ __global__ void __launch_bounds__(kSellBlock) spmv_sell_kernel(SellView S, const
     unsigned int* soff = reinterpret_cast<unsigned int*>(sy + S.R);
     constexpr int NSA = NS > 0 ? NS : 1;
     constexpr int RPS = 32 / T;   // rows per slice
+    constexpr int U = NSB_SELL_UNROLL;
     double acc[NSA];
 #pragma unroll
     for (int k = 0; k < NSA; ++k) acc[k] = 0.0;
@@ -203,26 +210,21 @@ __global__ void __launch_bounds__(kSellBlock) spmv_sell_kernel(SellView S, const
             const unsigned int* cp = reinterpret_cast<const unsigned int*>(S.lcol) + (size_t)o0 * 32 + lane;
             const int n = (int)(o1 - o0);
             double s0 = 0.0, s1 = 0.0;
-            int j = 0;
-            for (; j + 4 <= n; j += 4) {
-                double2 v[4];
-                unsigned int c[4];
+            // U predicated pair-loads (128-bit values + 32-bit indices) in flight per lane
+            for (int j = 0; j < n; j += U) {
+                double2 v[U];
+                unsigned int c[U];
 #pragma unroll
-                for (int k2 = 0; k2 < 4; ++k2) {
-                    v[k2] = ld_stream_f64x2(reinterpret_cast<const double*>(vp + (size_t)(j + k2) * 32));
-                    c[k2] = ld_stream_b32(cp + (size_t)(j + k2) * 32);
+                for (int k2 = 0; k2 < U; ++k2) {
+                    const bool on = j + k2 < n;
+                    v[k2] = on ? ld_stream_f64x2(reinterpret_cast<const double*>(vp + (size_t)(j + k2) * 32)) : make_double2(0.0, 0.0);
+                    c[k2] = on ? ld_stream_b32(cp + (size_t)(j + k2) * 32) : 0u;
                 }
 #pragma unroll
-                for (int k2 = 0; k2 < 4; ++k2) {
+                for (int k2 = 0; k2 < U; ++k2) {
                     s0 = fma(v[k2].x, sx[c[k2] & 0xffffu], s0);
                     s1 = fma(v[k2].y, sx[c[k2] >> 16], s1);
                 }
-            }
-            for (; j < n; ++j) {
-                const double2 v = ld_stream_f64x2(reinterpret_cast<const double*>(vp + (size_t)j * 32));
-                const unsigned int c = ld_stream_b32(cp + (size_t)j * 32);
-                s0 = fma(v.x, sx[c & 0xffffu], s0);
-                s1 = fma(v.y, sx[c >> 16], s1);
             }
             double s = s0 + s1;
 #pragma unroll
