@@ -365,3 +365,31 @@ def build_distributed_stokes(cells, lengths, ctx, rank, world, device="cuda", gr
                             int(counts[0]), int(counts[1]), (hu, hp))
     L.A = L.B = L.BT = None   # the CSR triples now live in the library
     return out
+
+
+def host_halo_exchange(plan, x_owned: torch.Tensor, group=None) -> torch.Tensor:
+    """The halo exchange of dist.cu restated with torch.distributed point-to-point calls on host
+    tensors: returns [x_owned | halo tail].  Used to check plans under gloo (tests) -- the solvers run
+    the exchange on the device (nsb_halo_create / halo_exchange)."""
+    import torch.distributed as dist
+    p = plan if isinstance(plan, dict) else dict(n_owned=plan.n_owned, n_halo=plan.n_halo, neighbors=plan.neighbors,
+                                                 send_counts=plan.send_counts, send_idx=plan.send_idx,
+                                                 recv_counts=plan.recv_counts)
+    out = torch.zeros(p["n_owned"] + p["n_halo"], dtype=x_owned.dtype)
+    out[:p["n_owned"]] = x_owned
+    send_idx = torch.as_tensor(np.asarray(p["send_idx"], dtype=np.int64))
+    reqs, so, ro = [], 0, 0
+    bufs = []
+    for k, nb in enumerate(p["neighbors"]):
+        sc, rc = int(p["send_counts"][k]), int(p["recv_counts"][k])
+        if sc:
+            buf = x_owned[send_idx[so:so + sc]].contiguous()
+            bufs.append(buf)
+            reqs.append(dist.isend(buf, int(nb), group=group))
+        if rc:
+            reqs.append(dist.irecv(out[p["n_owned"] + ro:p["n_owned"] + ro + rc], int(nb), group=group))
+        so += sc
+        ro += rc
+    for r in reqs:
+        r.wait()
+    return out

@@ -1,0 +1,41 @@
+"""Row-partitioned solvers on 2 GPUs (NCCL halo exchange + scalar all-reduce) against the single-GPU
+solve of the same global system: iteration counts +-1, histories 1e-10 over 50 iterations, solutions
+1e-8 (north-star tolerances).  Skipped on a box with fewer than two GPUs."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sell", ["0", "200000"])
+def test_two_rank_bpcg_and_minres_match_single_gpu(sell):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    env = dict(os.environ, NSB_SELL_MIN_NNZ=sell)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "dist_worker.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    rows = [json.loads(l.split("DISTRESULT ", 1)[1]) for l in res.stdout.splitlines() if "DISTRESULT " in l]
+    assert len(rows) == 2
+    for r in rows:
+        assert abs(r["it"] - r["it1"]) <= 1, r
+        assert r["hist_rel"] < 1e-10, r
+        assert r["sol_rel"] < 1e-8, r
+        assert r["lam_rel"] < 1e-6, r
+        assert abs(r["minres_it"] - r["minres_it1"]) <= 1, r
+        assert r["minres_hist_rel"] < 1e-10, r
+        assert r["minres_sol_rel"] < 1e-8, r
