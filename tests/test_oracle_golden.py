@@ -152,3 +152,47 @@ def test_pcg_oracle(cases):
     u, errs, info = ko.pcg(c.A, b, pre=c.dA, tol=1e-12, maxsteps=2000)
     r = (b - c.A @ u) * c.free_u
     assert info["converged"] and np.linalg.norm(r) < 1e-9 * np.linalg.norm(b)
+
+
+# ---- C + OpenMP twin of the oracle (oracle/c/krylov_omp.c): the timed CPU baseline of bench.py -----------------
+# bpcg_sq8 is left to the numpy oracle: at 1e-10 it runs ~150 iterations past the point where rounding
+# decorrelates the recurrence (history differences reach 1e-2 by iteration 120 between any two summation
+# orders), so its exit index and final iterate move with the OpenMP thread count.
+@pytest.mark.parametrize("name,mesh", [("bpcg_chan2d", "chan2d"), ("bpcg_chan3d", "chan3d")])
+def test_c_oracle_bpcg_matches_reference_golden(cases, name, mesh):
+    from oracle import cbuild
+    from oracle.cases import load_golden
+    c, gold = cases(mesh), load_golden(name)
+    bl = cbuild.Blocks(c.A, c.B, c.BT)
+    sol = c.start()
+    tol, maxsteps = gold["args"]
+    it, h, err0, _ = cbuild.bpcg_v2(bl, c.f, c.g, c.dA, c.dM, ko.bpcg_scale(float(gold["lam_min"])), sol, tol=float(tol),
+                                    maxsteps=int(maxsteps), initialize=False)
+    assert abs(it - int(gold["it_v2"])) <= 1
+    np.testing.assert_allclose(err0, float(gold["err0_v2"]), rtol=1e-12)
+    np.testing.assert_allclose(h[:50], gold["hist_v2"][:50], rtol=HIST_RTOL)
+    assert relerr(sol, gold["sol_v2"]) < max(SOL_RTOL, 1e3 * float(tol))
+
+
+@pytest.mark.parametrize("name,mesh", [("minres_sq8", "sq8"), ("minres_chan2d", "chan2d"), ("minres_chan3d", "chan3d")])
+def test_c_oracle_minres_matches_reference_golden(cases, name, mesh):
+    from oracle import cbuild
+    from oracle.cases import load_golden
+    c, gold = cases(mesh), load_golden(name)
+    bl = cbuild.Blocks(c.A, c.B, c.BT)
+    sol = c.start()
+    initialize, tol, maxsteps, use_pre = gold["args"]
+    assert use_pre
+    errors, conv, _ = cbuild.minres(bl, np.concatenate([c.dA, c.dM]), c.rhs(), sol, tol=float(tol), maxsteps=int(maxsteps),
+                                    initialize=bool(initialize))
+    assert abs(len(errors) - len(gold["errors"])) <= 1
+    np.testing.assert_allclose(errors[:50], gold["errors"][:50], rtol=HIST_RTOL)
+    assert relerr(sol, gold["sol"]) < SOL_RTOL
+
+
+def test_c_oracle_spmv_and_threads(cases):
+    from oracle import cbuild
+    c = cases("chan3d")
+    x = np.random.default_rng(0).uniform(-1, 1, c.n_u)
+    np.testing.assert_allclose(cbuild.spmv(c.A, x), c.A @ x, rtol=0, atol=1e-13)
+    assert cbuild.num_threads() >= 1
