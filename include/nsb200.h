@@ -156,6 +156,17 @@ NSB_API int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* 
  * in place.  basis = m vectors of length n stored one after another (stride n). */
 NSB_API int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int tries);
 
+/* One pass of the time-loop body of heat.py:81-146 ("exponential integrator" in an m-dimensional subspace):
+ * basis u, then m-1 implicit Euler sub-steps u -= dt H^-1 K u with dt = time_step/m (heat.py:95-98; H = M + dt K is
+ * solved by Jacobi-CG in place of the direct heat.mat.Inverse of heat.py:72), orthonormalize (:100), projected
+ * m x m diffusion and mass matrices (:109-118), Gauss collocation step of the projected ODE on the host
+ * (runge_kutta_method.py:26-59; rk_a is stages x stages row-major, rk_b has `stages` entries) and the lift back
+ * (:140-142).  u (length rows; host or device) is replaced by the new temperature.  Khat_out / Mhat_out
+ * (m*m, row-major, host) may be NULL. */
+NSB_API int nsb_heat_step(nsb_ctx ctx, nsb_mat K, nsb_mat M, nsb_mat H, nsb_pre preH, double* u, double time_step, int m,
+                          int stages, const double* rk_a, const double* rk_b, double cg_tol, int cg_maxsteps,
+                          int* cg_iterations, double* Khat_out, double* Mhat_out);
+
 #ifdef __cplusplus
 }
 #endif

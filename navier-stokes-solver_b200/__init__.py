@@ -7,7 +7,8 @@ from . import _lib, la, solvers  # noqa: F401
 from .la import (BaseVector, BlockMatrix, BlockVector, Context, DiagonalPreconditioner, IdentityMatrix,  # noqa: F401
                  InnerProduct, Norm, Preconditioner, SparseMatrix, default_context, set_default_context)
 from .solvers import (BramblePasciakCG, CGSolve, CGSolver, EigenValues_Preconditioner, MinRes,  # noqa: F401
-                      ImplicitRungeKuttaMethodWeights, bramble_pasciak_cg, linear_implicit_runge_kutta_step,
+                      ImplicitRungeKuttaMethodWeights, bramble_pasciak_cg, heat_large_step,
+                      linear_implicit_runge_kutta_step,
                       orthonormalize)
 
 __version__ = "0.1.0"

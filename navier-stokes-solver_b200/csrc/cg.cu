@@ -345,6 +345,21 @@ static int cg_alloc(CgBuffers& b, nsb_mat A, int maxsteps, bool lanczos) {
     return NSB_OK;
 }
 
+// CG on device-resident rhs (in b.q) -> b.u; used by nsb_cg and the heat stepper
+static int cg_solve_device(Context& c, nsb_mat A, nsb_pre pre, CgBuffers& b, bool initialize, int maxsteps, double tol,
+                           CgState* hs, float* ms) {
+    const int64_t n = A->rows;
+    if (initialize) {
+        NSB_CHECK(vec_set(c, b.u.p, 0.0, A->cols));
+        NSB_CHECK(vec_lincomb(c, b.d.p, 1.0, b.q.p, 0, nullptr, 0, nullptr, n));
+    } else {
+        NSB_CHECK(halo_exchange(c, A->halo, b.u.p));
+        NSB_CHECK(spmv_launch<0>(c, A, b.u.p, ResidualOp2{b.q.p, b.d.p}));
+    }
+    const int chunk = n < 200000 ? 16 : 4;
+    return cg_run(c, A, pre ? pre->d.p : nullptr, b, true, maxsteps, tol, false, chunk, nullptr, nullptr, hs, ms);
+}
+
 extern "C" int nsb_cg(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* rhs, double* sol, int maxsteps, double tol,
                       int initialize, double* history, int* iterations, double* seconds, int* status) {
     NSB_REQUIRE(ctx && A && rhs && sol, "nsb_cg: NULL argument");
@@ -356,18 +371,10 @@ extern "C" int nsb_cg(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* rhs, do
     CgBuffers b;
     NSB_CHECK(cg_alloc(b, A, maxsteps, false));
     NSB_CHECK(copy_in(c, b.q.p, rhs, n));
-    if (initialize) {
-        NSB_CHECK(vec_set(c, b.u.p, 0.0, A->cols));
-        NSB_CHECK(vec_lincomb(c, b.d.p, 1.0, b.q.p, 0, nullptr, 0, nullptr, n));
-    } else {
-        NSB_CHECK(copy_in(c, b.u.p, sol, n));
-        NSB_CHECK(halo_exchange(c, A->halo, b.u.p));
-        NSB_CHECK(spmv_launch<0>(c, A, b.u.p, ResidualOp2{b.q.p, b.d.p}));
-    }
+    if (!initialize) NSB_CHECK(copy_in(c, b.u.p, sol, n));
     CgState hs;
     float ms = 0.f;
-    const int chunk = n < 200000 ? 16 : 4;
-    NSB_CHECK(cg_run(c, A, pre ? pre->d.p : nullptr, b, true, maxsteps, tol, false, chunk, nullptr, nullptr, &hs, &ms));
+    NSB_CHECK(cg_solve_device(c, A, pre, b, initialize != 0, maxsteps, tol, &hs, &ms));
     NSB_CHECK(copy_out(c, sol, b.u.p, n));
     if (history) NSB_CHECK(copy_out(c, history, b.hist.p, hs.it + 1));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
@@ -407,19 +414,8 @@ extern "C" int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const doubl
     return NSB_OK;
 }
 
-extern "C" int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int tries) {
-    NSB_REQUIRE(ctx && basis && n >= 0 && m >= 0 && tries >= 0, "nsb_orthonormalize: bad argument");
-    Context& c = ctx->c;
-    NSB_CUDA(cudaSetDevice(c.device));
-    if (m == 0 || n == 0) return NSB_OK;
-    const bool on_dev = is_device_ptr(basis);
-    DevBuf<double> own;
-    double* Q = basis;
-    if (!on_dev) {
-        NSB_CHECK(own.alloc(n * m));
-        NSB_CHECK(copy_in(c, own.p, basis, n * m));
-        Q = own.p;
-    }
+// modified Gram-Schmidt on m device-resident vectors of length n (stride n), orthonormalization.py:8-13
+static int gs_device(Context& c, double* Q, int64_t n, int m, int tries) {
     DevBuf<double> sc;
     NSB_CHECK(sc.alloc(2));
     const int vg = vec_grid(n, c.num_sms);
@@ -439,8 +435,200 @@ extern "C" int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, 
             c.launches += 2;
         }
     }
+    return NSB_OK;
+}
+
+extern "C" int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int tries) {
+    NSB_REQUIRE(ctx && basis && n >= 0 && m >= 0 && tries >= 0, "nsb_orthonormalize: bad argument");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    if (m == 0 || n == 0) return NSB_OK;
+    const bool on_dev = is_device_ptr(basis);
+    DevBuf<double> own;
+    double* Q = basis;
+    if (!on_dev) {
+        NSB_CHECK(own.alloc(n * m));
+        NSB_CHECK(copy_in(c, own.p, basis, n * m));
+        Q = own.p;
+    }
+    NSB_CHECK(gs_device(c, Q, n, m, tries));
     NSB_CUDA(cudaGetLastError());
     if (!on_dev) NSB_CHECK(copy_out(c, basis, Q, n * m));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
+    return NSB_OK;
+}
+
+// ---- heat.py time-loop body (exponential-integrator step in a Krylov-like subspace) ----------------
+namespace nsb {
+
+constexpr int kHeatMaxDim = 8;
+
+struct BasisPtrs {
+    const double* q[kHeatMaxDim];
+};
+
+// out[k] = <Q_k, r>, k < m, from one read of r and the m basis vectors (heat.py:111-118: the inner loops
+// over `row` are m InnerProducts against the same residual)
+template <int M>
+__global__ void __launch_bounds__(kBlock) k_multidot(BasisPtrs B, const double* __restrict__ r, int64_t n, double* out,
+                                                     double* partials, unsigned int* ticket) {
+    double acc[M];
+#pragma unroll
+    for (int k = 0; k < M; ++k) acc[k] = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double ri = r[i];
+#pragma unroll
+        for (int k = 0; k < M; ++k) acc[k] = fma(B.q[k][i], ri, acc[k]);
+    }
+    if (grid_sum<M>(acc, partials, ticket)) {
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int k = 0; k < M; ++k) out[k] = acc[k];
+        }
+    }
+}
+
+// u = sum_k coef[k] Q_k   (heat.py:140-142)
+__global__ void __launch_bounds__(kBlock) k_lift(BasisPtrs B, const double* __restrict__ coef, int m, double* __restrict__ u,
+                                                 int64_t n) {
+    double cf[kHeatMaxDim];
+    for (int k = 0; k < m; ++k) cf[k] = coef[k];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        double s = 0.0;
+        for (int k = 0; k < m; ++k) s += cf[k] * B.q[k][i];   // same order as the reference's accumulation
+        u[i] = s;
+    }
+}
+
+static int multidot(Context& c, const BasisPtrs& B, int m, const double* r, int64_t n, double* out) {
+    const int vg = vec_grid(n, c.num_sms);
+    BasisPtrs P = B;
+    for (int k = m; k < kHeatMaxDim; ++k) P.q[k] = B.q[0];
+    if (m <= 4) k_multidot<4><<<vg, kBlock, 0, c.stream>>>(P, r, n, out, c.partials, c.ticket);
+    else k_multidot<8><<<vg, kBlock, 0, c.stream>>>(P, r, n, out, c.partials, c.ticket);
+    c.launches++;
+    NSB_CUDA(cudaGetLastError());
+    return allreduce_sum(c, out, m <= 4 ? 4 : 8);
+}
+
+// dense solve A x = b (n x n row-major, partial pivoting), host; A and b are overwritten
+static bool dense_solve(std::vector<double>& A, std::vector<double>& b, int n) {
+    for (int k = 0; k < n; ++k) {
+        int p = k;
+        for (int i = k + 1; i < n; ++i)
+            if (fabs(A[(size_t)i * n + k]) > fabs(A[(size_t)p * n + k])) p = i;
+        if (A[(size_t)p * n + k] == 0.0) return false;
+        if (p != k) {
+            for (int j = 0; j < n; ++j) std::swap(A[(size_t)k * n + j], A[(size_t)p * n + j]);
+            std::swap(b[k], b[p]);
+        }
+        for (int i = k + 1; i < n; ++i) {
+            const double f = A[(size_t)i * n + k] / A[(size_t)k * n + k];
+            if (f == 0.0) continue;
+            for (int j = k; j < n; ++j) A[(size_t)i * n + j] -= f * A[(size_t)k * n + j];
+            b[i] -= f * b[k];
+        }
+    }
+    for (int i = n - 1; i >= 0; --i) {
+        double s = b[i];
+        for (int j = i + 1; j < n; ++j) s -= A[(size_t)i * n + j] * b[j];
+        b[i] = s / A[(size_t)i * n + i];
+    }
+    return true;
+}
+
+}  // namespace nsb
+
+extern "C" int nsb_heat_step(nsb_ctx ctx, nsb_mat K, nsb_mat M, nsb_mat H, nsb_pre preH, double* u, double time_step, int m,
+                             int stages, const double* rk_a, const double* rk_b, double cg_tol, int cg_maxsteps,
+                             int* cg_iterations, double* Khat_out, double* Mhat_out) {
+    NSB_REQUIRE(ctx && K && M && H && u && rk_a && rk_b, "nsb_heat_step: NULL argument");
+    NSB_REQUIRE(m >= 1 && m <= kHeatMaxDim, "nsb_heat_step: subspace dimension must be in [1, %d]", kHeatMaxDim);
+    NSB_REQUIRE(stages >= 1 && stages <= 64, "nsb_heat_step: stages must be in [1, 64]");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    const int64_t n = K->rows, nx = K->cols;
+    NSB_REQUIRE(M->rows == n && H->rows == n && M->cols == nx && H->cols == nx, "nsb_heat_step: operator sizes differ");
+    if (preH) NSB_REQUIRE(preH->n == n, "nsb_heat_step: preconditioner size mismatch");
+    const double dt = time_step / m;                                      // heat.py:75
+    DevBuf<double> Q, xu, r, sc, coef;
+    NSB_CHECK(Q.alloc((int64_t)m * n));
+    NSB_CHECK(xu.alloc(nx));                                               // temperature with halo room
+    NSB_CHECK(r.alloc(nx));
+    NSB_CHECK(sc.alloc(2 * kHeatMaxDim * kHeatMaxDim + 16));
+    NSB_CHECK(coef.alloc(kHeatMaxDim));
+    CgBuffers b;
+    NSB_CHECK(cg_alloc(b, H, cg_maxsteps, false));
+    NSB_CHECK(copy_in(c, xu.p, u, n));
+    NSB_CHECK(vec_lincomb(c, Q.p, 1.0, xu.p, 0, nullptr, 0, nullptr, n));  // :87
+    double* d_norm = sc.p + 2 * kHeatMaxDim * kHeatMaxDim;
+    NSB_CHECK(vec_dot(c, xu.p, xu.p, n, d_norm));                          // :89
+    int total_cg = 0;
+    for (int i = 1; i < m; ++i) {                                          // :95-98
+        NSB_CHECK(halo_exchange(c, K->halo, xu.p));
+        NSB_CHECK(spmv_plain(c, K, xu.p, b.q.p));                          // residual = diffusion * temperature
+        CgState hs;
+        NSB_CHECK(cg_solve_device(c, H, preH, b, true, cg_maxsteps, cg_tol, &hs, nullptr));   // heat_inverse * residual
+        total_cg += hs.it;
+        NSB_CHECK(vec_lincomb(c, xu.p, 1.0, xu.p, -dt, b.u.p, 0, nullptr, n));
+        NSB_CHECK(vec_lincomb(c, Q.p + (int64_t)i * n, 1.0, xu.p, 0, nullptr, 0, nullptr, n));
+    }
+    NSB_CHECK(gs_device(c, Q.p, n, m, 3));                                 // :100
+    BasisPtrs B;
+    for (int k = 0; k < kHeatMaxDim; ++k) B.q[k] = Q.p + (int64_t)(k < m ? k : 0) * n;
+    for (int col = 0; col < m; ++col) {                                    // :109-118
+        NSB_CHECK(vec_lincomb(c, xu.p, 1.0, Q.p + (int64_t)col * n, 0, nullptr, 0, nullptr, n));
+        NSB_CHECK(halo_exchange(c, K->halo, xu.p));
+        NSB_CHECK(spmv_plain(c, K, xu.p, r.p));
+        NSB_CHECK(multidot(c, B, m, r.p, n, sc.p + (int64_t)col * kHeatMaxDim));
+        NSB_CHECK(spmv_plain(c, M, xu.p, r.p));
+        NSB_CHECK(multidot(c, B, m, r.p, n, sc.p + (int64_t)(kHeatMaxDim + col) * kHeatMaxDim));
+    }
+    std::vector<double> h(2 * kHeatMaxDim * kHeatMaxDim + 16);
+    NSB_CUDA(cudaMemcpyAsync(h.data(), sc.p, sizeof(double) * h.size(), cudaMemcpyDeviceToHost, c.stream));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    // host: m x m projected system and the collocation step (heat.py:120-135, runge_kutta_method.py:26-59)
+    std::vector<double> Kh((size_t)m * m), Mh((size_t)m * m), evo((size_t)m * m);
+    for (int col = 0; col < m; ++col)
+        for (int row = 0; row < m; ++row) {
+            Kh[(size_t)row * m + col] = h[(size_t)col * kHeatMaxDim + row];
+            Mh[(size_t)row * m + col] = h[(size_t)(kHeatMaxDim + col) * kHeatMaxDim + row];
+        }
+    if (Khat_out) memcpy(Khat_out, Kh.data(), sizeof(double) * (size_t)m * m);
+    if (Mhat_out) memcpy(Mhat_out, Mh.data(), sizeof(double) * (size_t)m * m);
+    for (int col = 0; col < m; ++col) {                                    // evo = -Mh^-1 Kh, column by column
+        std::vector<double> A = Mh, rhs((size_t)m);
+        for (int row = 0; row < m; ++row) rhs[row] = -Kh[(size_t)row * m + col];
+        NSB_REQUIRE(dense_solve(A, rhs, m), "nsb_heat_step: projected mass matrix is singular");
+        for (int row = 0; row < m; ++row) evo[(size_t)row * m + col] = rhs[row];
+    }
+    const double norm0 = sqrt(h[2 * kHeatMaxDim * kHeatMaxDim]);
+    std::vector<double> y((size_t)m, 0.0), My((size_t)m, 0.0);
+    y[0] = norm0;                                                          // :131-133
+    for (int row = 0; row < m; ++row) My[row] = evo[(size_t)row * m] * norm0;
+    const int N = m * stages;
+    std::vector<double> coefm((size_t)N * N, 0.0), kk((size_t)N);
+    for (int si = 0; si < stages; ++si)
+        for (int sj = 0; sj < stages; ++sj)
+            for (int row = 0; row < m; ++row)
+                for (int col = 0; col < m; ++col)
+                    coefm[(size_t)(si * m + row) * N + (sj * m + col)] =
+                        ((si == sj && row == col) ? 1.0 : 0.0) - time_step * rk_a[si * stages + sj] * evo[(size_t)row * m + col];
+    for (int si = 0; si < stages; ++si)
+        for (int row = 0; row < m; ++row) kk[(size_t)si * m + row] = My[row];
+    NSB_REQUIRE(dense_solve(coefm, kk, N), "nsb_heat_step: collocation system is singular");
+    double nxt[kHeatMaxDim] = {0};
+    for (int row = 0; row < m; ++row) {
+        double s = 0.0;
+        for (int si = 0; si < stages; ++si) s += rk_b[si] * kk[(size_t)si * m + row];
+        nxt[row] = y[row] + time_step * s;
+    }
+    NSB_CUDA(cudaMemcpyAsync(coef.p, nxt, sizeof(double) * kHeatMaxDim, cudaMemcpyHostToDevice, c.stream));
+    k_lift<<<vec_grid(n, c.num_sms), kBlock, 0, c.stream>>>(B, coef.p, m, xu.p, n);   // :140-142
+    c.launches++;
+    NSB_CUDA(cudaGetLastError());
+    NSB_CHECK(copy_out(c, u, xu.p, n));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    if (cg_iterations) *cg_iterations = total_cg;
     return NSB_OK;
 }

@@ -49,7 +49,7 @@ extern thread_local char g_err[1024];
 // ---------------------------------------------------------------------------------------------
 constexpr int kBlock = 256;          // threads per block of the vector kernels
 constexpr int kMaxBlocks = 148 * 8;  // 148 SMs x 8 resident 256-thread blocks
-constexpr int kMaxRed = 4;           // doubles reduced per kernel at most
+constexpr int kMaxRed = 8;           // doubles reduced per kernel at most
 // SELL-LX SpMV (spmv.cuh, sell.cu): shared-memory doubles a chunk may stage (distinct columns + R row
 // sums; 36 KB per block), target nonzeros per chunk
 constexpr int kSellStage = 4600;
@@ -149,6 +149,9 @@ struct nsb_mat_s {
     nsb::DevBuf<unsigned short> sell_perm;    // nchunks * R: sorted position -> row inside the chunk
     nsb::DevBuf<int32_t> sell_uptr;           // nchunks + 1
     nsb::DevBuf<int32_t> sell_ucol;           // distinct columns, chunk by chunk, ascending
+    // the same lists as runs of consecutive columns (used when the mean run is >= 8): first column, position
+    int sell_nruns = 0;
+    nsb::DevBuf<int32_t> sell_rstart, sell_rpos, sell_rptr;   // nruns, nruns + 1, nchunks + 1
     nsb_halo_s* halo = nullptr;   // not owned
     // saddle composition bookkeeping (rows of the velocity block; 0 for a plain matrix)
     int64_t n_u = 0, n_p = 0;

@@ -12,8 +12,8 @@
 //   * inside a chunk the rows are sorted by length (sigma = R) and cut into slices of 32/T rows, T lanes
 //     per row; a slice is padded to its longest row and stored as pair-blocks of 32 lanes x 2 entries,
 //     so loads are 128-bit (values) / 32-bit (indices), fully coalesced, with no row pointers.
-// Traffic per SpMV: 10 B per stored nonzero (padding is 2-4 % on the P2/P1 blocks) + 4 B per distinct
-// column + 2 B per row (perm) + x once + y once.
+// Traffic per SpMV: 10 B per stored nonzero (padding is 2-8 % on the P2/P1 blocks) + 8 B per run of consecutive
+// distinct columns (or 4 B per distinct column when the runs are short) + 2 B per row (perm) + x once + y once.
 // R is the largest power of two whose staging buffers (distinct columns + R row sums) fit kSellStage
 // doubles: 4 resident blocks then use ~144 KB of shared memory and leave ~84 KB of L1 for the x gathers of
 // the staging phase (with 228 KB of shared memory in use the same kernel ran 20 % slower).  An operator
@@ -79,6 +79,37 @@ __global__ void k_sell_maxuniq(const int* __restrict__ uptr, int nchunks, int* _
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < nchunks; c += gridDim.x * blockDim.x)
         m = max(m, uptr[c + 1] - uptr[c]);
     atomicMax(out, m);
+}
+
+// ---- runs of consecutive columns in the distinct-column lists -------------------------------------------
+// FEM numberings make the distinct columns of a chunk a few long runs (whole mesh lines); storing
+// (first column, position) per run instead of 4 B per column removes most of the index traffic of the
+// staging phase and turns its gathers into contiguous copies.
+__global__ void k_sell_chunkflags(const int* __restrict__ uptr, int nchunks, int total, int* __restrict__ flag) {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < nchunks; c += gridDim.x * blockDim.x)
+        if (uptr[c] < total) flag[uptr[c]] = 1;
+}
+
+__global__ void k_sell_runheads(const int* __restrict__ ucol, int total, int* __restrict__ flag) {
+    for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x)
+        if (g == 0 || ucol[g] != ucol[g - 1] + 1) flag[g] = 1;   // benign race: every writer stores 1
+}
+
+__global__ void k_sell_runfill(const int* __restrict__ ucol, const int* __restrict__ flag, const int* __restrict__ ridx_incl,
+                               int total, int* __restrict__ rstart, int* __restrict__ rpos) {
+    for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x)
+        if (flag[g]) {
+            rstart[ridx_incl[g] - 1] = ucol[g];
+            rpos[ridx_incl[g] - 1] = g;
+        }
+}
+
+__global__ void k_sell_runptr(const int* __restrict__ uptr, const int* __restrict__ ridx_incl, int nchunks, int total, int nruns,
+                              int* __restrict__ rptr, int* __restrict__ rpos) {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c <= nchunks; c += gridDim.x * blockDim.x) {
+        rptr[c] = (c < nchunks && uptr[c] < total) ? ridx_incl[uptr[c]] - 1 : nruns;
+        if (c == nchunks) rpos[nruns] = total;
+    }
 }
 
 // ---- sorting the rows of every chunk by length ------------------------------------------------------
@@ -232,6 +263,36 @@ int build_sell(Context& c, nsb_mat_s* m) {
     if (!found) {
         m->sell_ucol.release();
         return NSB_OK;
+    }
+    // ---- runs of consecutive distinct columns
+    m->sell_nruns = 0;
+    if (total_uniq > 0 && !(getenv("NSB_SELL_RUNS") && atoi(getenv("NSB_SELL_RUNS")) == 0)) {
+        DevBuf<int> flag, ridx;
+        DevBuf<char> stmp;
+        NSB_CHECK(flag.alloc(total_uniq));
+        NSB_CHECK(ridx.alloc(total_uniq));
+        size_t sb = 0;
+        cub::DeviceScan::InclusiveSum(nullptr, sb, flag.p, ridx.p, total_uniq, c.stream);
+        NSB_CHECK(stmp.alloc((int64_t)sb + 16));
+        const int ug = vec_grid(total_uniq, c.num_sms);
+        NSB_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int) * (size_t)total_uniq, c.stream));
+        k_sell_chunkflags<<<(nchunks + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(m->sell_uptr.p, nchunks, total_uniq, flag.p);
+        k_sell_runheads<<<ug, kBlock, 0, c.stream>>>(m->sell_ucol.p, total_uniq, flag.p);
+        NSB_CUDA(cub::DeviceScan::InclusiveSum(stmp.p, sb, flag.p, ridx.p, total_uniq, c.stream));
+        int nruns = 0;
+        NSB_CUDA(cudaMemcpyAsync(&nruns, ridx.p + (total_uniq - 1), sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+        NSB_CUDA(cudaStreamSynchronize(c.stream));
+        if (debug) fprintf(stderr, "[sell] %d runs for %d distinct columns (mean run %.1f)\n", nruns, total_uniq, (double)total_uniq / nruns);
+        if ((int64_t)nruns * 8 <= (int64_t)total_uniq) {   // mean run >= 8 columns: descriptors beat the list
+            NSB_CHECK(m->sell_rstart.alloc(nruns));
+            NSB_CHECK(m->sell_rpos.alloc(nruns + 1));
+            NSB_CHECK(m->sell_rptr.alloc(nchunks + 1));
+            k_sell_runfill<<<ug, kBlock, 0, c.stream>>>(m->sell_ucol.p, flag.p, ridx.p, total_uniq, m->sell_rstart.p, m->sell_rpos.p);
+            k_sell_runptr<<<(nchunks + 1 + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(m->sell_uptr.p, ridx.p, nchunks, total_uniq,
+                                                                                         nruns, m->sell_rptr.p, m->sell_rpos.p);
+            NSB_CUDA(cudaStreamSynchronize(c.stream));
+            m->sell_nruns = nruns;
+        }
     }
     const int64_t R = 1LL << log2R;
     const int64_t nvr = (int64_t)nchunks * R;        // virtual rows (last chunk padded)

@@ -157,6 +157,10 @@ struct SellView {
     const unsigned short* __restrict__ perm;   // sorted position -> row inside the chunk
     const int* __restrict__ uptr;
     const int* __restrict__ ucol;
+    // runs of consecutive distinct columns (rptr == nullptr: use the ucol list)
+    const int* __restrict__ rptr;
+    const int* __restrict__ rstart;
+    const int* __restrict__ rpos;
 };
 
 __device__ __forceinline__ unsigned int ld_stream_b32(const void* p) {
@@ -186,6 +190,41 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
         const int nu = __ldg(S.uptr + chunk + 1) - u0;
         __syncthreads();   // previous chunk: gathers done with sx, epilogue done with sy
         for (int i = threadIdx.x; i <= S.nsl; i += kSellBlock) soff[i] = __ldg(S.off + (size_t)chunk * S.nsl + i);
+        if (S.rptr != nullptr) {
+            // contiguous copies: lane k of a warp holds the descriptor of the warp's k-th run, runs are then
+            // copied two at a time with up to 8 coalesced loads in flight per lane
+            const int r0 = __ldg(S.rptr + chunk), r1 = __ldg(S.rptr + chunk + 1);
+            for (int rb = r0 + warp; rb < r1; rb += 32 * kSellWarps) {
+                const int mine = rb + lane * kSellWarps;
+                const int cs_l = mine < r1 ? __ldg(S.rstart + mine) : 0;
+                const int p0_l = mine < r1 ? __ldg(S.rpos + mine) : 0;
+                const int p1_l = mine < r1 ? __ldg(S.rpos + mine + 1) : 0;
+                const int cnt = min(32, (r1 - rb + kSellWarps - 1) / kSellWarps);
+                for (int k = 0; k < cnt; k += 2) {
+                    int cs[2], p0[2], len[2];
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const int kk = min(k + q, 31);
+                        cs[q] = __shfl_sync(0xffffffffu, cs_l, kk);
+                        p0[q] = __shfl_sync(0xffffffffu, p0_l, kk) - u0;
+                        len[q] = (k + q < cnt) ? __shfl_sync(0xffffffffu, p1_l, kk) - u0 - p0[q] : 0;
+                    }
+                    const int longest = max(len[0], len[1]);
+                    for (int l = lane; l < longest; l += 128) {
+                        double v[2][4];
+#pragma unroll
+                        for (int q = 0; q < 2; ++q)
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) v[q][j] = (l + 32 * j < len[q]) ? __ldg(x + cs[q] + l + 32 * j) : 0.0;
+#pragma unroll
+                        for (int q = 0; q < 2; ++q)
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (l + 32 * j < len[q]) sx[p0[q] + l + 32 * j] = v[q][j];
+                    }
+                }
+            }
+        } else
         for (int i = threadIdx.x; i < nu; i += 4 * kSellBlock) {
             int c[4];
             double v[4];
@@ -247,7 +286,8 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
 
 inline SellView sell_view_of(const nsb_mat_s* m) {
     return SellView{m->rows, m->sell_R, m->sell_log2R, m->sell_nchunks, m->sell_R * m->sell_T / 32, m->sell_cap,
-                    m->sell_vals.p, m->sell_lcol.p, m->sell_off.p, m->sell_perm.p, m->sell_uptr.p, m->sell_ucol.p};
+                    m->sell_vals.p, m->sell_lcol.p, m->sell_off.p, m->sell_perm.p, m->sell_uptr.p, m->sell_ucol.p,
+                    m->sell_nruns > 0 ? m->sell_rptr.p : nullptr, m->sell_rstart.p, m->sell_rpos.p};
 }
 
 inline size_t sell_smem_bytes(const nsb_mat_s* m) {

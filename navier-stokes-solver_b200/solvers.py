@@ -293,6 +293,35 @@ def orthonormalize(basis, tries=3):
 
 
 # ------------------------------------------------------------------------------------------------
+def heat_large_step(diffusion, mass, heat, pre_heat, temperature, time_step, weights, subspace_dimension=5,
+                    cg_tol=1e-12, cg_maxsteps=2000):
+    """One pass of the time-loop body of heat.py:81-146 on the device: Krylov-like basis from m-1 implicit Euler
+    sub-steps (:95-98), orthonormalize (:100), projected m x m matrices (:109-118), Gauss collocation step of the
+    projected system (:135) and the lift (:140-142).  ``diffusion`` / ``mass`` / ``heat`` are device SparseMatrix
+    (diffusion.mat, mass.mat, heat.mat = M + dt K); the direct ``heat.mat.Inverse(freedofs)`` of heat.py:72 is
+    replaced by Jacobi-CG with ``pre_heat`` (zero on constrained dofs) to ``cg_tol``.  ``temperature`` is updated
+    in place and returned; diagnostics in ``last_info``."""
+    for m_ in (diffusion, mass, heat):
+        if not isinstance(m_, SparseMatrix):
+            raise TypeError("heat_large_step needs device SparseMatrix operators")
+    ctx = diffusion.ctx
+    n = diffusion._halo.n_owned if diffusion._halo is not None else diffusion.height
+    pre_h, keep = _pre_handle(pre_heat, n)
+    p_u, keep_u = _flat(temperature, n, "temperature")
+    m = int(subspace_dimension)
+    a = np.ascontiguousarray(weights.a, dtype=np.float64)
+    b = np.ascontiguousarray(weights.b, dtype=np.float64)
+    Kh, Mh = np.zeros((m, m)), np.zeros((m, m))
+    its = C.c_int()
+    _lib.check(ctx._lib.nsb_heat_step(ctx.h, diffusion.h, mass.h, heat.h, pre_h, p_u, float(time_step), m, a.shape[0],
+                                      a.ctypes.data, b.ctypes.data, float(cg_tol), int(cg_maxsteps), C.byref(its),
+                                      Kh.ctypes.data, Mh.ctypes.data), "nsb_heat_step")
+    last_info.clear()
+    last_info.update(solver="heat_large_step", cg_iterations=its.value, subspace_diffusion=Kh, subspace_mass=Mh)
+    return temperature
+
+
+# ------------------------------------------------------------------------------------------------
 # Gauss collocation on the projected (m x m, m = 5) system: host-side dense algebra, as in the
 # reference (runge_kutta_method.py; SURVEY.md a12: "negligible; stays on host").
 def _lagrange(c, n, x):

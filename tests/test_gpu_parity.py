@@ -407,3 +407,52 @@ def test_launch_counter_counts_kernels(nsb, dev):
     n0 = ctx.launch_count()
     quiet(nsb.CGSolve, A, np.ones(c.n_u) * c.free_u, pA, None, 1e-8, 50)
     assert ctx.launch_count() - n0 >= 3
+
+
+def _heat_case(cells=(10, 10)):
+    """2D heat problem of heat.py on the unit square: P2 mass / stiffness, zero Dirichlet boundary, initial
+    temperature = the analytic sine series of heat.py:21-27 at t = 0."""
+    import navier_stokes_solver_b200.synthetic as syn
+    S = syn.assemble_stokes(cells, (1.0, 1.0), with_mass2=True)
+    K, M = S.extras["K2"].to_scipy(), S.extras["M2"].to_scipy()
+    nx, ny = 2 * cells[0] + 1, 2 * cells[1] + 1
+    ix, iy = np.divmod(np.arange(nx * ny), ny)
+    free = (ix > 0) & (ix < nx - 1) & (iy > 0) & (iy < ny - 1)
+    x, y = ix / (nx - 1), iy / (ny - 1)
+    kl = [(1, 1), (2, 1), (1, 3), (3, 3), (2, 3), (4, 5), (5, 2)]
+    u0 = sum(2 * np.sin(k * np.pi * x) * np.sin(l * np.pi * y) for k, l in kl) * free
+    return K, M, free, u0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("time_step", [1e-2, 1e-3])
+def test_heat_large_step_matches_oracle(nsb, time_step):
+    """heat.py:81-146 time-loop body: device step against the oracle restatement with the same Jacobi-CG solve."""
+    from oracle import krylov_oracle as ko
+    K, M, free, u0 = _heat_case()
+    m = 5
+    dt = time_step / m
+    H = (M + dt * K).tocsr()                                          # heat.py:52
+    dH = np.where(free, 1.0 / H.diagonal(), 0.0)
+    w_ref = ko.RungeKuttaWeights(10)
+
+    def heat_solve(r):
+        x, _, _ = ko.pcg(H, r, pre=dH, tol=1e-13, maxsteps=2000)
+        return x
+
+    ref = ko.heat_large_step(K, M, heat_solve, u0, time_step, w_ref, m)
+    dK, dM_, dHm = nsb.SparseMatrix.from_scipy(K), nsb.SparseMatrix.from_scipy(M), nsb.SparseMatrix.from_scipy(H)
+    pre = nsb.DiagonalPreconditioner.from_diagonal(dH)
+    w = nsb.ImplicitRungeKuttaMethodWeights(10)
+    u = u0.copy()
+    out = nsb.heat_large_step(dK, dM_, dHm, pre, u, time_step, w, m, cg_tol=1e-13, cg_maxsteps=2000)
+    assert out is u
+    assert relerr(u, ref) < 1e-8                                      # north-star solution tolerance
+    info = nsb.solvers.last_info
+    assert info["cg_iterations"] > 0
+    # projected mass matrix of an M-orthogonal... the basis is l2-orthonormal: Mh is SPD, Kh symmetric
+    np.testing.assert_allclose(info["subspace_mass"], info["subspace_mass"].T, rtol=0, atol=1e-9 * np.abs(info["subspace_mass"]).max())
+    # two consecutive steps stay on the oracle's trajectory
+    ref2 = ko.heat_large_step(K, M, heat_solve, ref, time_step, w_ref, m)
+    nsb.heat_large_step(dK, dM_, dHm, pre, u, time_step, w, m, cg_tol=1e-13, cg_maxsteps=2000)
+    assert relerr(u, ref2) < 1e-7
