@@ -91,9 +91,10 @@ NSB_API int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz);
  * length inside chunks, sliced-ELL pair-blocks, x staged in shared memory, 16-bit chunk-local column indices)
  * is active, else the CSR-vector kernel runs.  total_distinct = sum over chunks of distinct columns (4 B each
  * of extra index traffic per SpMV); stored_nnz = nonzeros including slice padding; lanes_per_row = lanes that
- * share a row in the active kernel. */
+ * share a row in the active kernel; column_runs > 0 when the distinct-column lists are stored as that many runs
+ * of consecutive columns (8 B per run instead of 4 B per column). */
 NSB_API int nsb_mat_format(nsb_mat m, int* rows_per_chunk, int* chunks, int* max_distinct, int64_t* total_distinct,
-                           int* lanes_per_row, int64_t* stored_nnz);
+                           int* lanes_per_row, int64_t* stored_nnz, int64_t* column_runs);
 /* main diagonal of a square (or owned-square) operator, length rows */
 NSB_API int nsb_mat_diagonal(nsb_ctx ctx, nsb_mat m, double* out);
 /* y = M x   (the `mat * vec` primitive, e.g. minres.py:97).  x has `cols`, y has `rows` entries. */

@@ -53,6 +53,7 @@ constexpr int kMaxRed = 8;           // doubles reduced per kernel at most
 // SELL-LX SpMV (spmv.cuh, sell.cu): shared-memory doubles a chunk may stage (distinct columns + R row
 // sums; 36 KB per block), target nonzeros per chunk
 constexpr int kSellStage = 4600;
+constexpr int kSellStageMax = 7300;   // relaxed budget for chunks of long rows (sell.cu)
 constexpr double kSellTargetNnz = 24000.0;
 
 inline int vec_grid(int64_t n, int num_sms) {

@@ -311,7 +311,7 @@ int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz) {
 }
 
 int nsb_mat_format(nsb_mat m, int* rows_per_chunk, int* chunks, int* max_distinct, int64_t* total_distinct,
-                   int* lanes_per_row, int64_t* stored_nnz) {
+                   int* lanes_per_row, int64_t* stored_nnz, int64_t* column_runs) {
     NSB_REQUIRE(m, "nsb_mat_format: NULL matrix");
     if (rows_per_chunk) *rows_per_chunk = m->sell_R;
     if (chunks) *chunks = m->sell_nchunks;
@@ -319,6 +319,7 @@ int nsb_mat_format(nsb_mat m, int* rows_per_chunk, int* chunks, int* max_distinc
     if (total_distinct) *total_distinct = m->sell_total_uniq;
     if (lanes_per_row) *lanes_per_row = m->sell_R > 0 ? m->sell_T : m->threads_per_row;
     if (stored_nnz) *stored_nnz = m->sell_R > 0 ? m->sell_stored : m->nnz;
+    if (column_runs) *column_runs = m->sell_R > 0 ? m->sell_nruns : 0;
     return NSB_OK;
 }
 

@@ -203,6 +203,8 @@ int build_sell(Context& c, nsb_mat_s* m) {
     if (log2R < minlog) log2R = minlog;
     CsrView A = view_of(m);
     const int vg = vec_grid(nnz, c.num_sms);
+    const int64_t stage_cap = getenv("NSB_SELL_STAGE") ? atoll(getenv("NSB_SELL_STAGE")) : kSellStage;
+    const int64_t stage_max = stage_cap > kSellStageMax ? stage_cap : kSellStageMax;
 
     // ---- phase A: chunk-local column numbering (largest R whose chunks fit the staging buffer)
     DevBuf<unsigned short> lcol_csr;
@@ -245,7 +247,10 @@ int build_sell(Context& c, nsb_mat_s* m) {
             if (debug)
                 fprintf(stderr, "[sell] rows=%lld nnz=%lld T=%d log2R=%d nchunks=%d max_distinct=%d total=%d\n",
                         (long long)rows, (long long)nnz, T, log2R, nchunks, h[0], h[1]);
-            if (h[0] + R > kSellStage) continue;  // staging buffers (x + row sums) over budget: halve the chunk
+            // staging buffers (x + row sums) over budget: halve the chunk.  Chunks with fewer than two slices per
+            // warp lose more to imbalance than to the larger footprint, so they may use the relaxed budget.
+            const bool small = log2R <= ilog2((int64_t)rps * kSellWarps * 2);
+            if (h[0] + R > (small ? stage_max : stage_cap)) continue;
             NSB_CHECK(lcol_csr.alloc(nnz));
             NSB_CHECK(m->sell_ucol.alloc(h[1] > 0 ? h[1] : 1));
             k_sell_localcols<<<vg, kBlock, 0, c.stream>>>(k1.p, p1.p, head.p, gidx.p, uptr.p, lcol_csr.p, m->sell_ucol.p, nnz);

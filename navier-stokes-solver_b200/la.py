@@ -324,13 +324,13 @@ class SparseMatrix(BaseMatrix):
 
     def format(self):
         """Which SpMV kernel this operator runs: dict(rows_per_chunk, chunks, max_distinct, total_distinct,
-        lanes_per_row, stored_nnz); rows_per_chunk == 0 means the plain CSR-vector kernel, > 0 the SELL-LX kernel."""
+        lanes_per_row, stored_nnz, column_runs); rows_per_chunk == 0 means the plain CSR-vector kernel, > 0 the SELL-LX kernel."""
         a, b, c_, t = C.c_int(), C.c_int(), C.c_int(), C.c_int()
-        d, e = C.c_int64(), C.c_int64()
+        d, e, f = C.c_int64(), C.c_int64(), C.c_int64()
         _lib.check(self.ctx._lib.nsb_mat_format(self.h, C.byref(a), C.byref(b), C.byref(c_), C.byref(d), C.byref(t),
-                                                C.byref(e)), "nsb_mat_format")
+                                                C.byref(e), C.byref(f)), "nsb_mat_format")
         return dict(rows_per_chunk=a.value, chunks=b.value, max_distinct=c_.value, total_distinct=d.value,
-                    lanes_per_row=t.value, stored_nnz=e.value)
+                    lanes_per_row=t.value, stored_nnz=e.value, column_runs=f.value)
 
     def diagonal(self):
         out = np.empty(self.height)

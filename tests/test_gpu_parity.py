@@ -108,11 +108,13 @@ def test_spmv_ragged_and_empty_rows(nsb):
     np.testing.assert_array_equal((Z * np.ones(4)).NumPy(), np.zeros(5))
 
 
+@pytest.mark.parametrize("runs", ["1", "0"])
 @pytest.mark.parametrize("log2r", [None, 3, 5, 7])
-def test_spmv_sell_format_matches_scipy(nsb, cases, monkeypatch, log2r):
+def test_spmv_sell_format_matches_scipy(nsb, cases, monkeypatch, log2r, runs):
     """The SELL-LX kernel (sorted sliced-ELL, x staged in shared memory) forced on the small cases."""
     import scipy.sparse as sp
     monkeypatch.setenv("NSB_SELL_MIN_NNZ", "0")
+    monkeypatch.setenv("NSB_SELL_RUNS", runs)      # distinct columns as runs of consecutive columns / as a list
     if log2r is not None:
         monkeypatch.setenv("NSB_SELL_LOG2R", str(log2r))
     c = cases("chan3d")
@@ -122,6 +124,10 @@ def test_spmv_sell_format_matches_scipy(nsb, cases, monkeypatch, log2r):
     BT = B.T
     for M in (A, B, BT):
         assert M.format()["rows_per_chunk"] > 0
+        if runs == "0":
+            assert M.format()["column_runs"] == 0
+    if runs == "1" and log2r in (None, 7):
+        assert A.format()["column_runs"] > 0          # the lattice numbering gives long runs
     np.testing.assert_allclose((A * xu).NumPy(), c.A @ xu, rtol=0, atol=1e-12)
     np.testing.assert_allclose((B * xu).NumPy(), c.B @ xu, rtol=0, atol=1e-12)
     np.testing.assert_allclose((BT * xp).NumPy(), c.BT @ xp, rtol=0, atol=1e-12)
