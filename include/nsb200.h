@@ -72,7 +72,8 @@ NSB_API int nsb_ctx_sync(nsb_ctx ctx);
 NSB_API void* nsb_ctx_stream(nsb_ctx ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches claim) */
 NSB_API int64_t nsb_ctx_launch_count(nsb_ctx ctx);
-/* capture the per-iteration kernel sequence in CUDA graphs (default on for single-GPU contexts) */
+/* capture the per-iteration kernel sequence in CUDA graphs (default on for single-GPU contexts and for
+ * row-partitioned contexts whose exchanges run over NVLink peer memory; NSB_P2P=0 forces the NCCL path) */
 NSB_API int nsb_ctx_set_graphs(nsb_ctx ctx, int enabled);
 
 /* ---- operators: replaces NGSolve SparseMatrix / BilinearForm.mat (run.py:106,

@@ -1,12 +1,12 @@
 // bpcg.cu -- Bramble-Pasciak CG, device-resident engine for both reference variants:
 //   solvers/bramblepasciak_new.py:24-253 (mode 2) and bramble_pasciak_cg.py:65-148 (mode 1; same iterates,
 //   SURVEY.md 8(c)(iii)).  The iteration is v2's (one A apply per step, A*s0 and A*w0 by recurrence):
-//   B1  SpMV B^T s1, row epilogue:  As0 = beta As0 + z0 ; tmp0 = As0 + B^T s1 ; tmp1 = k dA tmp0 ;
-//                                   tmp4 = tmp1 - s0                                   (:205-209,:212)
+//   B1  SpMV B^T s1, row epilogue:  s0 = beta s0 + w0 (:240-241 of the previous pass) ; As0 = beta As0 + z0 ;
+//                                   tmp0 = As0 + B^T s1 ; tmp1 = k dA tmp0 ; tmp4 = tmp1 - s0   (:205-209,:212)
 //   B2  SpMV A tmp1 -> tmp2,        fused  sum s0 (tmp2 - tmp0)                        (:210,:218,:222)
 //   B3  SpMV B tmp4 -> tmp3,        fused  sum s1 tmp3            -> alpha             (:213,:219,:222,:226)
 //   B4  u += a s ; d -= a v ; w0 -= a tmp1 ; w1 -= a dM tmp3 ; z0 -= a tmp2,  fused <w,d> -> beta, err, exit (:228-247)
-//   B5  s = beta s + w                                                                 (:240-241)
+//   B5  s1 = beta s1 + w1  (pressure part of :240-241; n_p entries)
 // z_old of :215 is folded away: beta*As0 + z_old - alpha*tmp2 == beta*As0 + z0(after :238).
 // Traffic beyond the three SpMVs: 8*(24 n_u + 13 n_p) bytes per iteration.
 // Only diagonal preA / preM are fused here (the reference's BDDC / AMG live in NGSolve: BASELINE.md 4).
@@ -67,7 +67,8 @@ struct BpcgB1Op {
     double* __restrict__ As0;
     const double* __restrict__ z0;
     const double* __restrict__ dA;
-    const double* __restrict__ s0;
+    double* __restrict__ s0;
+    const double* __restrict__ w0;
     double* __restrict__ tmp0;
     double* __restrict__ tmp1;
     double* __restrict__ tmp4;
@@ -76,10 +77,12 @@ struct BpcgB1Op {
         const double as0 = S->beta * As0[i] + z0[i];
         const double t0 = as0 + ax;
         const double t1 = S->k * (dA[i] * t0);
+        const double sn = S->beta * s0[i] + w0[i];   // :240-241 of the previous pass, velocity part (s0 = w0 before
+        s0[i] = sn;                                  // the first pass and beta = 0 then, so this is the identity)
         As0[i] = as0;
         tmp0[i] = t0;
         tmp1[i] = t1;
-        tmp4[i] = t1 - s0[i];
+        tmp4[i] = t1 - sn;
     }
     __device__ void finish(const double (&)[1]) const {}
 };
@@ -158,14 +161,12 @@ __global__ void __launch_bounds__(kBlock) k_bpcg_b4(BpcgState* S, BpcgVecs V, do
     }
 }
 
+// s1 = beta s1 + w1 (:240-241, pressure part; the velocity part rides in B1's epilogue of the next pass)
 __global__ void __launch_bounds__(kBlock) k_bpcg_b5(const BpcgState* S, BpcgVecs V) {
     if (S->stop) return;
     const double b = S->beta;
-    const int64_t n = V.n_u + V.n_p;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        if (i < V.n_u) V.s0[i] = b * V.s0[i] + V.w0[i];     // :240-241
-        else V.s1[i - V.n_u] = b * V.s1[i - V.n_u] + V.w1[i - V.n_u];
-    }
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < V.n_p; j += (int64_t)gridDim.x * blockDim.x)
+        V.s1[j] = b * V.s1[j] + V.w1[j];
 }
 
 __global__ void k_bpcg_init_scalar(BpcgState* S, double k, double wdn_u, const double* wdn_dev, int maxsteps, double tol,
@@ -224,12 +225,12 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
 
     DevBuf<double> u0, u1, d0, d1, w0, w1, s0, s1, z0, As0, tmp0, tmp1, tmp2, tmp3, tmp4, df, dg, fnew, gnew, hist;
     DevBuf<BpcgState> st;
-    for (DevBuf<double>* b : {&u0, &s0, &tmp0, &tmp1, &tmp4}) NSB_CHECK(b->alloc(nxu));
-    for (DevBuf<double>* b : {&d0, &w0, &z0, &As0, &tmp2, &df, &fnew}) NSB_CHECK(b->alloc(n_u));
-    for (DevBuf<double>* b : {&u1, &s1}) NSB_CHECK(b->alloc(nxp));
-    for (DevBuf<double>* b : {&d1, &w1, &tmp3, &dg, &gnew}) NSB_CHECK(b->alloc(n_p > 0 ? n_p : 1));
-    NSB_CHECK(hist.alloc(maxsteps + 2));
-    NSB_CHECK(st.alloc(1));
+    for (DevBuf<double>* b : {&u0, &s0, &tmp0, &tmp1, &tmp4}) NSB_CHECK(b->allocs(c, nxu));
+    for (DevBuf<double>* b : {&d0, &w0, &z0, &As0, &tmp2, &df, &fnew}) NSB_CHECK(b->allocs(c, n_u));
+    for (DevBuf<double>* b : {&u1, &s1}) NSB_CHECK(b->allocs(c, nxp));
+    for (DevBuf<double>* b : {&d1, &w1, &tmp3, &dg, &gnew}) NSB_CHECK(b->allocs(c, n_p > 0 ? n_p : 1));
+    NSB_CHECK(hist.allocs(c, maxsteps + 2));
+    NSB_CHECK(st.allocs(c, 1));
     BpcgState* S = st.p;
 
     // ---- set-up, solvers/bramblepasciak_new.py:124-189 (not condensed)
@@ -280,7 +281,7 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
     const int vg = vec_grid(n_u + n_p, c.num_sms);
     auto launch_iteration = [&]() -> int {
         NSB_CHECK(halo_exchange(c, BT->halo, s1.p));
-        NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, tmp0.p, tmp1.p, tmp4.p}));
+        NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p}));
         // tmp1 and tmp4 travel in the velocity halo
         NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
         NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
@@ -298,7 +299,7 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
             k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;
         }
-        k_bpcg_b5<<<vg, kBlock, 0, c.stream>>>(S, V);
+        k_bpcg_b5<<<vec_grid(n_p > 0 ? n_p : 1, c.num_sms), kBlock, 0, c.stream>>>(S, V);
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;

@@ -329,18 +329,18 @@ __global__ void __launch_bounds__(kBlock) k_gs_scale(double* __restrict__ bj, co
 
 using namespace nsb;
 
-static int cg_alloc(CgBuffers& b, nsb_mat A, int maxsteps, bool lanczos) {
+static int cg_alloc(Context& c, CgBuffers& b, nsb_mat A, int maxsteps, bool lanczos) {
     const int64_t n = A->rows, nx = A->cols;
-    NSB_CHECK(b.u.alloc(nx));
-    NSB_CHECK(b.s.alloc(nx));
-    NSB_CHECK(b.d.alloc(n));
-    NSB_CHECK(b.w.alloc(n));
-    NSB_CHECK(b.q.alloc(n));
-    NSB_CHECK(b.hist.alloc(maxsteps + 2));
-    NSB_CHECK(b.st.alloc(1));
+    NSB_CHECK(b.u.allocs(c, nx));
+    NSB_CHECK(b.s.allocs(c, nx));
+    NSB_CHECK(b.d.allocs(c, n));
+    NSB_CHECK(b.w.allocs(c, n));
+    NSB_CHECK(b.q.allocs(c, n));
+    NSB_CHECK(b.hist.allocs(c, maxsteps + 2));
+    NSB_CHECK(b.st.allocs(c, 1));
     if (lanczos) {
-        NSB_CHECK(b.alphas.alloc(maxsteps + 2));
-        NSB_CHECK(b.betas.alloc(maxsteps + 2));
+        NSB_CHECK(b.alphas.allocs(c, maxsteps + 2));
+        NSB_CHECK(b.betas.allocs(c, maxsteps + 2));
     }
     return NSB_OK;
 }
@@ -369,7 +369,7 @@ extern "C" int nsb_cg(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* rhs, do
     const int64_t n = A->rows;
     if (pre) NSB_REQUIRE(pre->n == n, "nsb_cg: preconditioner size mismatch");
     CgBuffers b;
-    NSB_CHECK(cg_alloc(b, A, maxsteps, false));
+    NSB_CHECK(cg_alloc(c, b, A, maxsteps, false));
     NSB_CHECK(copy_in(c, b.q.p, rhs, n));
     if (!initialize) NSB_CHECK(copy_in(c, b.u.p, sol, n));
     CgState hs;
@@ -393,7 +393,7 @@ extern "C" int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const doubl
     const int64_t n = A->rows;
     if (pre) NSB_REQUIRE(pre->n == n, "nsb_lanczos_eigs: preconditioner size mismatch");
     CgBuffers b;
-    NSB_CHECK(cg_alloc(b, A, maxsteps, true));
+    NSB_CHECK(cg_alloc(c, b, A, maxsteps, true));
     if (start) NSB_CHECK(copy_in(c, b.d.p, start, n));
     else {
         k_lanczos_start<<<vec_grid(n, c.num_sms), kBlock, 0, c.stream>>>(b.d.p, n);
@@ -417,7 +417,7 @@ extern "C" int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const doubl
 // modified Gram-Schmidt on m device-resident vectors of length n (stride n), orthonormalization.py:8-13
 static int gs_device(Context& c, double* Q, int64_t n, int m, int tries) {
     DevBuf<double> sc;
-    NSB_CHECK(sc.alloc(2));
+    NSB_CHECK(sc.allocs(c, 2));
     const int vg = vec_grid(n, c.num_sms);
     for (int t = 0; t < tries; ++t) {                                   // :8
         for (int j = 0; j < m; ++j) {                                   // :9
@@ -447,7 +447,7 @@ extern "C" int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, 
     DevBuf<double> own;
     double* Q = basis;
     if (!on_dev) {
-        NSB_CHECK(own.alloc(n * m));
+        NSB_CHECK(own.allocs(c, n * m));
         NSB_CHECK(copy_in(c, own.p, basis, n * m));
         Q = own.p;
     }
@@ -552,13 +552,13 @@ extern "C" int nsb_heat_step(nsb_ctx ctx, nsb_mat K, nsb_mat M, nsb_mat H, nsb_p
     if (preH) NSB_REQUIRE(preH->n == n, "nsb_heat_step: preconditioner size mismatch");
     const double dt = time_step / m;                                      // heat.py:75
     DevBuf<double> Q, xu, r, sc, coef;
-    NSB_CHECK(Q.alloc((int64_t)m * n));
-    NSB_CHECK(xu.alloc(nx));                                               // temperature with halo room
-    NSB_CHECK(r.alloc(nx));
-    NSB_CHECK(sc.alloc(2 * kHeatMaxDim * kHeatMaxDim + 16));
-    NSB_CHECK(coef.alloc(kHeatMaxDim));
+    NSB_CHECK(Q.allocs(c, (int64_t)m * n));
+    NSB_CHECK(xu.allocs(c, nx));                                               // temperature with halo room
+    NSB_CHECK(r.allocs(c, nx));
+    NSB_CHECK(sc.allocs(c, 2 * kHeatMaxDim * kHeatMaxDim + 16));
+    NSB_CHECK(coef.allocs(c, kHeatMaxDim));
     CgBuffers b;
-    NSB_CHECK(cg_alloc(b, H, cg_maxsteps, false));
+    NSB_CHECK(cg_alloc(c, b, H, cg_maxsteps, false));
     NSB_CHECK(copy_in(c, xu.p, u, n));
     NSB_CHECK(vec_lincomb(c, Q.p, 1.0, xu.p, 0, nullptr, 0, nullptr, n));  // :87
     double* d_norm = sc.p + 2 * kHeatMaxDim * kHeatMaxDim;

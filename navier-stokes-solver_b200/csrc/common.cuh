@@ -66,7 +66,9 @@ inline int vec_grid(int64_t n, int num_sms) {
 // ---------------------------------------------------------------------------------------------
 // context
 // ---------------------------------------------------------------------------------------------
-struct NcclApi;  // dist.cu
+struct NcclApi;    // dist.cu
+struct P2PReduce;  // p2p.cu
+struct P2PHalo;    // p2p.cu
 
 struct Context {
     int device = 0;
@@ -85,21 +87,30 @@ struct Context {
     int rank = 0, nranks = 1;
     void* nccl_comm = nullptr;
     NcclApi* nccl = nullptr;
+    P2PReduce* p2p = nullptr;   // peer-memory scalar all-reduce (p2p.cu); null: NCCL all-reduce
 };
 
-// device buffer with RAII (host-side owner)
+// device buffer with RAII (host-side owner).  alloc(): cudaMalloc, for long-lived storage (operators, IPC
+// blocks).  allocs(): stream-ordered allocation from the context's memory pool, for the work vectors of a
+// solve -- a solve allocates ~20 vectors and cudaMalloc/cudaFree of 150 MB blocks cost ~30 ms per call.
 template <typename T>
 struct DevBuf {
     T* p = nullptr;
     int64_t n = 0;
+    cudaStream_t pool_stream = nullptr;
+    bool pooled = false;
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
     ~DevBuf() { release(); }
     void release() {
-        if (p) cudaFree(p);
+        if (p) {
+            if (pooled) cudaFreeAsync(p, pool_stream);
+            else cudaFree(p);
+        }
         p = nullptr;
         n = 0;
+        pooled = false;
     }
     int alloc(int64_t count) {
         release();
@@ -111,6 +122,20 @@ struct DevBuf {
             set_error("cudaMalloc(%lld bytes) failed: %s", (long long)(sizeof(T) * (size_t)count), cudaGetErrorString(e));
             return NSB_ERR_CUDA;
         }
+        return NSB_OK;
+    }
+    int allocs(Context& c, int64_t count) {
+        release();
+        n = count;
+        if (count <= 0) return NSB_OK;
+        cudaError_t e = cudaMallocAsync((void**)&p, sizeof(T) * (size_t)count, c.stream);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            set_error("cudaMallocAsync(%lld bytes) failed: %s", (long long)(sizeof(T) * (size_t)count), cudaGetErrorString(e));
+            return NSB_ERR_CUDA;
+        }
+        pooled = true;
+        pool_stream = c.stream;
         return NSB_OK;
     }
 };
@@ -132,6 +157,8 @@ struct nsb_halo_s {
     int64_t n_send = 0;
     nsb::DevBuf<int32_t> send_idx;  // owned entries to ship, neighbour by neighbour
     nsb::DevBuf<double> send_buf;
+    nsb::P2PHalo* p2p = nullptr;    // peer-memory push exchange (p2p.cu); null: pack + NCCL send/recv
+    ~nsb_halo_s();
 };
 
 struct nsb_mat_s {
@@ -247,6 +274,14 @@ int vec_diagmul(Context& c, double* y, double s, const double* d, const double* 
 int vec_dot(Context& c, const double* x, const double* y, int64_t n, double* out_dev);          // *out_dev = <x,y> (+ allreduce when distributed)
 int allreduce_sum(Context& c, double* dev, int count);                       // no-op for nranks == 1
 int halo_exchange(Context& c, nsb_halo_s* h, double* x);                     // fills x[n_owned .. n_owned+n_halo)
+// peer-memory (NVLink) paths, p2p.cu
+int p2p_reduce_init(Context& c);                                              // collective; leaves c.p2p null when IPC is unavailable
+void p2p_reduce_destroy(Context& c);
+int p2p_allreduce(Context& c, double* dev, int count);
+int p2p_halo_init(Context& c, nsb_halo_s* h);                                 // collective; leaves h->p2p null on failure
+void p2p_halo_destroy(nsb_halo_s* h);
+int p2p_halo_exchange(Context& c, nsb_halo_s* h, double* x);
+int nccl_allgather_bytes(Context& c, const void* send_dev, void* recv_dev, size_t bytes_per_rank);   // dist.cu
 
 int build_sell(Context& c, nsb_mat_s* m);   // sell.cu
 

@@ -43,6 +43,12 @@ int ctx_init(Context& c, int device) {
     NSB_CUDA(cudaGetDeviceProperties(&prop, device));
     c.num_sms = prop.multiProcessorCount;
     NSB_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    {   // keep freed work vectors in the device's default pool between solves
+        cudaMemPool_t pool;
+        NSB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        unsigned long long keep = ~0ull;
+        NSB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     c.max_grid = c.num_sms * 8 > kMaxBlocks ? c.num_sms * 8 : kMaxBlocks;
     NSB_CUDA(cudaMalloc((void**)&c.partials, sizeof(double) * kMaxRed * (size_t)c.max_grid));
     NSB_CUDA(cudaMalloc((void**)&c.ticket, sizeof(unsigned int)));
@@ -96,7 +102,9 @@ int nsb_ctx_create_dist(int device, int rank, int nranks, const char unique_id[1
             *out = nullptr;
             return r;
         }
-        (*out)->c.use_graphs = false;
+        // CUDA graphs stay on when both exchange steps run over peer memory (no host-side communication call
+        // inside the iteration); with the NCCL fallback the iteration is launched kernel by kernel
+        (*out)->c.use_graphs = (*out)->c.p2p != nullptr;
     }
     return NSB_OK;
 }
@@ -128,7 +136,7 @@ int64_t nsb_ctx_launch_count(nsb_ctx ctx) { return ctx ? ctx->c.launches : 0; }
 
 int nsb_ctx_set_graphs(nsb_ctx ctx, int enabled) {
     NSB_REQUIRE(ctx, "nsb_ctx_set_graphs: NULL context");
-    ctx->c.use_graphs = enabled != 0 && ctx->c.nranks == 1;
+    ctx->c.use_graphs = enabled != 0 && (ctx->c.nranks == 1 || ctx->c.p2p != nullptr);
     return NSB_OK;
 }
 

@@ -341,8 +341,8 @@ int nsb_spmv(nsb_ctx ctx, nsb_mat m, const double* x, double* y) {
     NSB_CUDA(cudaSetDevice(c.device));
     const int64_t n_in = m->halo ? m->halo->n_owned : m->cols;
     DevBuf<double> dx, dy;
-    NSB_CHECK(dx.alloc(m->cols));
-    NSB_CHECK(dy.alloc(m->rows));
+    NSB_CHECK(dx.allocs(c, m->cols));
+    NSB_CHECK(dy.allocs(c, m->rows));
     NSB_CHECK(copy_in(c, dx.p, x, n_in));
     NSB_CHECK(halo_exchange(c, m->halo, dx.p));
     NSB_CHECK(spmv_plain(c, m, dx.p, dy.p));
@@ -356,8 +356,8 @@ int nsb_spmv_bench(nsb_ctx ctx, nsb_mat m, int warmup, int reps, double* ms_per_
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
     DevBuf<double> dx, dy;
-    NSB_CHECK(dx.alloc(m->cols));
-    NSB_CHECK(dy.alloc(m->rows));
+    NSB_CHECK(dx.allocs(c, m->cols));
+    NSB_CHECK(dy.allocs(c, m->rows));
     // x ~ deterministic pattern in (-1, 1)
     NSB_CHECK(vec_set(c, dx.p, 0.5, m->cols));
     cudaEvent_t e0, e1;
@@ -462,8 +462,8 @@ int nsb_pre_apply(nsb_ctx ctx, nsb_pre p, const double* x, double* y) {
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
     DevBuf<double> dx, dy;
-    NSB_CHECK(dx.alloc(p->n));
-    NSB_CHECK(dy.alloc(p->n));
+    NSB_CHECK(dx.allocs(c, p->n));
+    NSB_CHECK(dy.allocs(c, p->n));
     NSB_CHECK(copy_in(c, dx.p, x, p->n));
     NSB_CHECK(vec_diagmul(c, dy.p, 1.0, p->d.p, dx.p, p->n));
     NSB_CHECK(copy_out(c, y, dy.p, p->n));

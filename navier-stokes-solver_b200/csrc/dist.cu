@@ -22,6 +22,7 @@ struct NcclApi {
     int (*CommInitRank)(NcclComm*, int, NcclUniqueId, int) = nullptr;
     int (*CommDestroy)(NcclComm) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, NcclComm, cudaStream_t) = nullptr;
     int (*Send)(const void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
     int (*Recv)(void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
@@ -51,6 +52,7 @@ static int load_nccl() {
     LOAD(CommInitRank, "ncclCommInitRank");
     LOAD(CommDestroy, "ncclCommDestroy");
     LOAD(AllReduce, "ncclAllReduce");
+    LOAD(AllGather, "ncclAllGather");
     LOAD(Send, "ncclSend");
     LOAD(Recv, "ncclRecv");
     LOAD(GroupStart, "ncclGroupStart");
@@ -80,16 +82,26 @@ int dist_init(Context& c, int rank, int nranks, const char* uid) {
     c.nccl = &g_nccl;
     c.rank = rank;
     c.nranks = nranks;
+    const char* env = getenv("NSB_P2P");
+    if (!(env && atoi(env) == 0)) NSB_CHECK(p2p_reduce_init(c));   // peer-memory scalar all-reduce when IPC works
+    return NSB_OK;
+}
+
+int nccl_allgather_bytes(Context& c, const void* send_dev, void* recv_dev, size_t bytes_per_rank) {
+    NSB_NCCL(c.nccl->AllGather(send_dev, recv_dev, bytes_per_rank, 0 /* ncclInt8 */, (NcclComm)c.nccl_comm, c.stream));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
     return NSB_OK;
 }
 
 void dist_destroy(Context& c) {
+    p2p_reduce_destroy(c);
     if (c.nccl_comm && c.nccl) c.nccl->CommDestroy((NcclComm)c.nccl_comm);
     c.nccl_comm = nullptr;
 }
 
 int allreduce_sum(Context& c, double* dev, int count) {
     if (c.nranks <= 1) return NSB_OK;
+    if (c.p2p && count <= 8) return p2p_allreduce(c, dev, count);
     NSB_NCCL(c.nccl->AllReduce(dev, dev, (size_t)count, kNcclFloat64, kNcclSum, (NcclComm)c.nccl_comm, c.stream));
     return NSB_OK;
 }
@@ -102,6 +114,7 @@ __global__ void __launch_bounds__(kBlock) k_pack(double* __restrict__ buf, const
 
 int halo_exchange(Context& c, nsb_halo_s* h, double* x) {
     if (!h || c.nranks <= 1) return NSB_OK;
+    if (h->p2p) return p2p_halo_exchange(c, h, x);
     if (h->n_send > 0) {
         k_pack<<<vec_grid(h->n_send, c.num_sms), kBlock, 0, c.stream>>>(h->send_buf.p, x, h->send_idx.p, h->n_send);
         c.launches++;
@@ -124,6 +137,8 @@ int halo_exchange(Context& c, nsb_halo_s* h, double* x) {
 }
 
 }  // namespace nsb
+
+nsb_halo_s::~nsb_halo_s() { nsb::p2p_halo_destroy(this); }
 
 using namespace nsb;
 
@@ -169,6 +184,7 @@ int nsb_halo_create(nsb_ctx ctx, int64_t n_owned, int64_t n_halo, int n_neighbor
             r = NSB_ERR_CUDA;
         }
     }
+    if (r == NSB_OK && ctx->c.nranks > 1 && ctx->c.p2p) r = p2p_halo_init(ctx->c, h);   // collective
     if (r != NSB_OK) {
         delete h;
         return r;

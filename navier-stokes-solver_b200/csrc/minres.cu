@@ -227,14 +227,14 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
 
     DevBuf<double> u, t, v[3], w[3], z[2], hist, drhs;
     DevBuf<MinresState> st;
-    NSB_CHECK(u.alloc(nx));
-    NSB_CHECK(t.alloc(n));
-    NSB_CHECK(drhs.alloc(n));
-    for (auto& b : v) NSB_CHECK(b.alloc(n));
-    for (auto& b : w) NSB_CHECK(b.alloc(n));
-    for (auto& b : z) NSB_CHECK(b.alloc(nx));
-    NSB_CHECK(hist.alloc(maxsteps + 2));
-    NSB_CHECK(st.alloc(1));
+    NSB_CHECK(u.allocs(c, nx));
+    NSB_CHECK(t.allocs(c, n));
+    NSB_CHECK(drhs.allocs(c, n));
+    for (auto& b : v) NSB_CHECK(b.allocs(c, n));
+    for (auto& b : w) NSB_CHECK(b.allocs(c, n));
+    for (auto& b : z) NSB_CHECK(b.allocs(c, nx));
+    NSB_CHECK(hist.allocs(c, maxsteps + 2));
+    NSB_CHECK(st.allocs(c, 1));
     MinresState* S = st.p;
     const int vg = vec_grid(n, c.num_sms);
 
