@@ -53,6 +53,7 @@ typedef struct nsb_ctx_s* nsb_ctx;
 typedef struct nsb_mat_s* nsb_mat;
 typedef struct nsb_pre_s* nsb_pre;
 typedef struct nsb_halo_s* nsb_halo;
+typedef struct nsb_cond_s* nsb_cond;
 
 /* ---- library / context ------------------------------------------------------------------- */
 NSB_API int nsb_version(void);
@@ -141,6 +142,23 @@ NSB_API int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs, d
 NSB_API int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre preA, nsb_pre preM, double k_scale,
              const double* f, const double* g, double* sol, int maxsteps, double tol, int initialize, int rel_err,
              int mode, double* history, int* updates, double* seconds, int* status);
+
+/* Statically condensed velocity operator of BramblePasciakCG (blfA.condense == True, bramblepasciak_new.py:8-21,84-103):
+ *   matA = (I - HT)(A + inner_matrix)(I - H)     with A = blfA.mat (the condensed matrix), H = blfA.harmonic_extension,
+ *   HT = blfA.harmonic_extension_trans, inner_solve = blfA.inner_solve, inner_matrix = blfA.inner_matrix, all exported as
+ *   CSR of the full velocity size.  The handle borrows the five operators (they must outlive it).  Single GPU. */
+NSB_API int nsb_cond_create(nsb_ctx ctx, nsb_mat A, nsb_mat H, nsb_mat HT, nsb_mat inner_solve, nsb_mat inner_matrix, nsb_cond* out);
+NSB_API int nsb_cond_destroy(nsb_cond k);
+/* y = matA x  (myAmatrix.Mult, bramblepasciak_new.py:90-91) */
+NSB_API int nsb_cond_apply(nsb_ctx ctx, nsb_cond k, const double* x, double* y);
+/* BramblePasciakCG with blfA.condense == True: matA as above, and every application of the A-preconditioner goes through
+ * harmonic_extension(f, blfA, k * preA_unscaled) (bramblepasciak_new.py:8-21).  Same outputs as nsb_bpcg mode 2. */
+NSB_API int nsb_bpcg_condensed(nsb_ctx ctx, nsb_cond cond, nsb_mat B, nsb_mat BT, nsb_pre preA, nsb_pre preM, double k_scale,
+                               const double* f, const double* g, double* sol, int maxsteps, double tol, int initialize,
+                               int rel_err, double* history, int* updates, double* seconds, int* status);
+/* EigenValues_Preconditioner(mat=matA, pre=preA_unscaled) with the condensed matA (bramblepasciak_new.py:104-115) */
+NSB_API int nsb_lanczos_eigs_condensed(nsb_ctx ctx, nsb_cond cond, nsb_pre pre, const double* start, int maxsteps, double tol,
+                                       double* lam_min, double* lam_max, int* steps);
 
 /* Preconditioned CG with NGSolve CGSolver's stopping rule sqrt<Cr,r> <= tol * initial
  * (CGSolver(mstar, pre, precision=1e-4) NavierStokesSIMPLE_iterative.py:93,128; stands in for the direct

@@ -4,7 +4,7 @@ orthonormalization.py) behind the same call signatures.  Compute lives in libnsb
 sm_100a CUDA behind the C ABI of include/nsb200.h); this package is the host-side mirror of the
 reference's operator/vector protocol."""
 from . import _lib, la, solvers  # noqa: F401
-from .la import (BaseVector, BlockMatrix, BlockVector, Context, DiagonalPreconditioner, IdentityMatrix,  # noqa: F401
+from .la import (BaseVector, BlockMatrix, BlockVector, CondensedOperator, Context, DiagonalPreconditioner, IdentityMatrix,  # noqa: F401
                  InnerProduct, Norm, Preconditioner, SparseMatrix, default_context, set_default_context)
 from .solvers import (BramblePasciakCG, CGSolve, CGSolver, EigenValues_Preconditioner, MinRes,  # noqa: F401
                       ImplicitRungeKuttaMethodWeights, bramble_pasciak_cg, heat_large_step,

@@ -12,7 +12,7 @@
 // Only diagonal preA / preM are fused here (the reference's BDDC / AMG live in NGSolve: BASELINE.md 4).
 #include <math.h>
 
-#include "spmv.cuh"
+#include "cond.cuh"
 
 namespace nsb {
 
@@ -83,6 +83,24 @@ struct BpcgB1Op {
         tmp0[i] = t0;
         tmp1[i] = t1;
         tmp4[i] = t1 - sn;
+    }
+    __device__ void finish(const double (&)[1]) const {}
+};
+
+// condensed variant of B1: the preconditioner is a chain of SpMVs (cond_apply_pre), so tmp1 / tmp4 are not formed here
+struct BpcgB1cOp {
+    BpcgState* S;
+    double* __restrict__ As0;
+    const double* __restrict__ z0;
+    double* __restrict__ s0;
+    const double* __restrict__ w0;
+    double* __restrict__ tmp0;
+    __device__ bool skip() const { return S->stop != 0; }
+    __device__ void row(int64_t i, double ax, double (&)[1]) const {
+        s0[i] = S->beta * s0[i] + w0[i];             // :240-241 of the previous pass
+        const double as0 = S->beta * As0[i] + z0[i]; // :205
+        As0[i] = as0;
+        tmp0[i] = as0 + ax;                          // :207
     }
     __device__ void finish(const double (&)[1]) const {}
 };
@@ -204,9 +222,9 @@ static int apply(Context& c, nsb_mat_s* m, double* x, double* y) {
 
 using namespace nsb;
 
-extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre preA, nsb_pre preM, double k_scale,
-                        const double* f, const double* g, double* sol, int maxsteps, double tol, int initialize,
-                        int rel_err, int mode, double* history, int* updates, double* seconds, int* status) {
+static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat BT, nsb_pre preA, nsb_pre preM, double k_scale,
+                     const double* f, const double* g, double* sol, int maxsteps, double tol, int initialize,
+                     int rel_err, int mode, double* history, int* updates, double* seconds, int* status) {
     NSB_REQUIRE(ctx && A && B && BT && preA && f && g && sol && history, "nsb_bpcg: NULL argument");
     NSB_REQUIRE(mode == 1 || mode == 2, "nsb_bpcg: mode must be 1 or 2");
     NSB_REQUIRE(isfinite(k_scale) && k_scale > 0.0, "nsb_bpcg: k_scale must be positive and finite");
@@ -222,6 +240,21 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
     const bool fused = c.nranks == 1;
     const double* dA = preA->d.p;
     const double* dM = preM ? preM->d.p : nullptr;
+    if (K) NSB_REQUIRE(c.nranks == 1 && mode == 2, "nsb_bpcg_condensed: single-GPU, v2 semantics only");
+    DevBuf<double> cr, cy;   // scratch of the condensed preconditioner chain
+    if (K) {
+        NSB_CHECK(cr.allocs(c, n_u));
+        NSB_CHECK(cy.allocs(c, n_u));
+    }
+    // matA x -> y and preA x -> y (k * preA_unscaled, extended harmonically when condensed: :8-21,:84-103,:122)
+    auto applyA = [&](double* x, double* y) -> int {
+        if (K) return cond_apply_A<0>(c, K, x, PlainRowOp{y});
+        return apply(c, A, x, y);
+    };
+    auto applyPre = [&](const double* x, double* y) -> int {
+        if (K) return cond_apply_pre(c, K, x, dA, k_scale, cr.p, cy.p, y);
+        return vec_diagmul(c, y, k_scale, dA, x, n_u);
+    };
 
     DevBuf<double> u0, u1, d0, d1, w0, w1, s0, s1, z0, As0, tmp0, tmp1, tmp2, tmp3, tmp4, df, dg, fnew, gnew, hist;
     DevBuf<BpcgState> st;
@@ -236,9 +269,8 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
     // ---- set-up, solvers/bramblepasciak_new.py:124-189 (not condensed)
     NSB_CHECK(copy_in(c, df.p, f, n_u));
     NSB_CHECK(copy_in(c, dg.p, g, n_p));
-    NSB_CHECK(vec_diagmul(c, tmp0.p, 1.0, dA, df.p, n_u));                       // preA_unscaled f
-    NSB_CHECK(vec_lincomb(c, tmp0.p, k_scale, tmp0.p, 0, nullptr, 0, nullptr, n_u));   // k * (.)   :122,:129
-    NSB_CHECK(apply(c, A, tmp0.p, fnew.p));
+    NSB_CHECK(applyPre(df.p, tmp0.p));                                            // :122,:128-129
+    NSB_CHECK(applyA(tmp0.p, fnew.p));
     NSB_CHECK(vec_lincomb(c, fnew.p, 1.0, fnew.p, -1.0, df.p, 0, nullptr, n_u));  // :130
     NSB_CHECK(apply(c, B, tmp0.p, gnew.p));
     NSB_CHECK(vec_lincomb(c, gnew.p, 1.0, gnew.p, -1.0, dg.p, 0, nullptr, n_p));  // :133  (== tmp5, :177)
@@ -250,12 +282,11 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
         NSB_CHECK(copy_in(c, u0.p, sol, n_u));
         NSB_CHECK(copy_in(c, u1.p, sol + n_u, n_p));
     }
-    NSB_CHECK(apply(c, A, u0.p, tmp0.p));                                          // :160
+    NSB_CHECK(applyA(u0.p, tmp0.p));                                               // :160
     NSB_CHECK(apply(c, BT, u1.p, tmp2.p));
     NSB_CHECK(vec_lincomb(c, tmp0.p, 1.0, tmp0.p, 1.0, tmp2.p, 0, nullptr, n_u));
-    NSB_CHECK(vec_diagmul(c, tmp1.p, 1.0, dA, tmp0.p, n_u));                       // :162
-    NSB_CHECK(vec_lincomb(c, tmp1.p, k_scale, tmp1.p, 0, nullptr, 0, nullptr, n_u));
-    NSB_CHECK(apply(c, A, tmp1.p, tmp2.p));                                        // :163
+    NSB_CHECK(applyPre(tmp0.p, tmp1.p));                                           // :162
+    NSB_CHECK(applyA(tmp1.p, tmp2.p));                                             // :163
     NSB_CHECK(vec_lincomb(c, tmp4.p, 1.0, tmp1.p, -1.0, u0.p, 0, nullptr, n_u));   // :165
     NSB_CHECK(apply(c, B, tmp4.p, tmp3.p));                                        // :166
     NSB_CHECK(vec_lincomb(c, d0.p, 1.0, fnew.p, -1.0, tmp2.p, 1.0, tmp0.p, n_u)); // :169
@@ -269,7 +300,7 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
     c.launches++;
     NSB_CHECK(vec_lincomb(c, s0.p, 1.0, w0.p, 0, nullptr, 0, nullptr, n_u));      // :189
     NSB_CHECK(vec_lincomb(c, s1.p, 1.0, w1.p, 0, nullptr, 0, nullptr, n_p));
-    NSB_CHECK(apply(c, A, s0.p, As0.p));                                           // :202
+    NSB_CHECK(applyA(s0.p, As0.p));                                                // :202
     NSB_CHECK(vec_lincomb(c, z0.p, 1.0, As0.p, 0, nullptr, 0, nullptr, n_u));     // :203
 
     cudaEvent_t e0, e1;
@@ -281,10 +312,17 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
     const int vg = vec_grid(n_u + n_p, c.num_sms);
     auto launch_iteration = [&]() -> int {
         NSB_CHECK(halo_exchange(c, BT->halo, s1.p));
-        NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p}));
-        // tmp1 and tmp4 travel in the velocity halo
-        NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
-        NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
+        if (K) {
+            NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1cOp{S, As0.p, z0.p, s0.p, w0.p, tmp0.p}));
+            NSB_CHECK(applyPre(tmp0.p, tmp1.p));                                                   // :209
+            NSB_CHECK(vec_lincomb(c, tmp4.p, 1.0, tmp1.p, -1.0, s0.p, 0, nullptr, n_u));           // :212
+            NSB_CHECK((cond_apply_A<1>(c, K, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused})));   // :210,:218,:222
+        } else {
+            NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p}));
+            // tmp1 and tmp4 travel in the velocity halo
+            NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
+            NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
+        }
         NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
         NSB_CHECK(spmv_launch<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, fused}));
         if (!fused) {
@@ -363,4 +401,63 @@ extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre p
     if (seconds) *seconds = (double)ms * 1e-3;
     if (status) *status = hs.status;
     return NSB_OK;
+}
+
+extern "C" int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre preA, nsb_pre preM, double k_scale,
+                        const double* f, const double* g, double* sol, int maxsteps, double tol, int initialize,
+                        int rel_err, int mode, double* history, int* updates, double* seconds, int* status) {
+    return bpcg_core(ctx, A, nullptr, B, BT, preA, preM, k_scale, f, g, sol, maxsteps, tol, initialize, rel_err, mode, history,
+                     updates, seconds, status);
+}
+
+extern "C" int nsb_cond_create(nsb_ctx ctx, nsb_mat A, nsb_mat H, nsb_mat HT, nsb_mat inner_solve, nsb_mat inner_matrix,
+                               nsb_cond* out) {
+    NSB_REQUIRE(ctx && A && H && HT && inner_solve && inner_matrix && out, "nsb_cond_create: NULL argument");
+    const int64_t n = A->rows;
+    for (nsb_mat m : {A, H, HT, inner_solve, inner_matrix})
+        NSB_REQUIRE(m->rows == n && m->cols == n && m->halo == nullptr,
+                    "nsb_cond_create: all five operators must be square of the same size and not row-partitioned");
+    nsb_cond_s* K = new nsb_cond_s();
+    K->ctx = &ctx->c;
+    K->A = A;
+    K->H = H;
+    K->HT = HT;
+    K->inner_solve = inner_solve;
+    K->inner_matrix = inner_matrix;
+    K->n = n;
+    int r = K->t.alloc(n);
+    if (r == NSB_OK) r = K->q.alloc(n);
+    if (r != NSB_OK) {
+        delete K;
+        return r;
+    }
+    *out = K;
+    return NSB_OK;
+}
+
+extern "C" int nsb_cond_destroy(nsb_cond k) {
+    delete k;
+    return NSB_OK;
+}
+
+extern "C" int nsb_cond_apply(nsb_ctx ctx, nsb_cond k, const double* x, double* y) {
+    NSB_REQUIRE(ctx && k && x && y, "nsb_cond_apply: NULL argument");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    DevBuf<double> dx, dy;
+    NSB_CHECK(dx.allocs(c, k->n));
+    NSB_CHECK(dy.allocs(c, k->n));
+    NSB_CHECK(copy_in(c, dx.p, x, k->n));
+    NSB_CHECK(cond_apply_A<0>(c, k, dx.p, PlainRowOp{dy.p}));
+    NSB_CHECK(copy_out(c, y, dy.p, k->n));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    return NSB_OK;
+}
+
+extern "C" int nsb_bpcg_condensed(nsb_ctx ctx, nsb_cond cond, nsb_mat B, nsb_mat BT, nsb_pre preA, nsb_pre preM, double k_scale,
+                                  const double* f, const double* g, double* sol, int maxsteps, double tol, int initialize,
+                                  int rel_err, double* history, int* updates, double* seconds, int* status) {
+    NSB_REQUIRE(cond, "nsb_bpcg_condensed: NULL operator");
+    return bpcg_core(ctx, cond->A, cond, B, BT, preA, preM, k_scale, f, g, sol, maxsteps, tol, initialize, rel_err, 2, history,
+                     updates, seconds, status);
 }

@@ -9,7 +9,7 @@
 
 #include <algorithm>
 
-#include "spmv.cuh"
+#include "cond.cuh"
 
 namespace nsb {
 
@@ -132,7 +132,7 @@ struct CgBuffers {
 
 static int cg_run(Context& c, nsb_mat_s* A, const double* dinv, CgBuffers& b, bool want_u, int maxsteps, double tol,
                   bool lanczos, int chunk, bool (*host_check)(void*, const CgState&), void* check_arg, CgState* out_state,
-                  float* out_ms) {
+                  float* out_ms, nsb_cond_s* K = nullptr) {
     const int64_t n = A->rows;
     const bool fused = c.nranks == 1;
     CgState* S = b.st.p;
@@ -153,7 +153,8 @@ static int cg_run(Context& c, nsb_mat_s* A, const double* dinv, CgBuffers& b, bo
     NSB_CUDA(cudaEventRecord(e0, c.stream));
     auto launch_iteration = [&]() -> int {
         NSB_CHECK(halo_exchange(c, A->halo, b.s.p));
-        NSB_CHECK(spmv_launch<1>(c, A, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused}));
+        if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused})));
+        else NSB_CHECK(spmv_launch<1>(c, A, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused}));
         if (!fused) {
             NSB_CHECK(allreduce_sum(c, &S->red[0], 1));
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist, alphas, betas);
@@ -384,8 +385,8 @@ extern "C" int nsb_cg(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* rhs, do
     return NSB_OK;
 }
 
-extern "C" int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* start, int maxsteps, double tol,
-                                double* lam_min, double* lam_max, int* steps) {
+static int lanczos_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_pre pre, const double* start, int maxsteps, double tol,
+                        double* lam_min, double* lam_max, int* steps) {
     NSB_REQUIRE(ctx && A && lam_min, "nsb_lanczos_eigs: NULL argument");
     NSB_REQUIRE(maxsteps > 0, "nsb_lanczos_eigs: maxsteps must be positive");
     Context& c = ctx->c;
@@ -405,7 +406,7 @@ extern "C" int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const doubl
     L.tol = tol;
     CgState hs;
     float ms = 0.f;
-    NSB_CHECK(cg_run(c, A, pre ? pre->d.p : nullptr, b, false, maxsteps, 0.0, true, 8, lanczos_host_check, &L, &hs, &ms));
+    NSB_CHECK(cg_run(c, A, pre ? pre->d.p : nullptr, b, false, maxsteps, 0.0, true, 8, lanczos_host_check, &L, &hs, &ms, K));
     if (!L.converged) lanczos_host_check(&L, hs);  // fold whatever the last chunk produced
     NSB_REQUIRE(L.steps > 0, "nsb_lanczos_eigs: Lanczos produced no step (zero start residual?)");
     *lam_min = L.lam_min;
@@ -436,6 +437,17 @@ static int gs_device(Context& c, double* Q, int64_t n, int m, int tries) {
         }
     }
     return NSB_OK;
+}
+
+extern "C" int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* start, int maxsteps, double tol,
+                                double* lam_min, double* lam_max, int* steps) {
+    return lanczos_core(ctx, A, nullptr, pre, start, maxsteps, tol, lam_min, lam_max, steps);
+}
+
+extern "C" int nsb_lanczos_eigs_condensed(nsb_ctx ctx, nsb_cond cond, nsb_pre pre, const double* start, int maxsteps,
+                                          double tol, double* lam_min, double* lam_max, int* steps) {
+    NSB_REQUIRE(cond, "nsb_lanczos_eigs_condensed: NULL operator");
+    return lanczos_core(ctx, cond->A, cond, pre, start, maxsteps, tol, lam_min, lam_max, steps);
 }
 
 extern "C" int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int tries) {

@@ -370,6 +370,53 @@ class SparseMatrix(BaseMatrix):
             pass
 
 
+class CondensedOperator(BaseMatrix):
+    """matA = (I - HT)(A + inner_matrix)(I - H) of a statically condensed BilinearForm
+    (myAmatrix, solvers/bramblepasciak_new.py:84-103).  Holds references to the five device matrices."""
+
+    def __init__(self, mat, harmonic_extension, harmonic_extension_trans, inner_solve, inner_matrix):
+        parts = (mat, harmonic_extension, harmonic_extension_trans, inner_solve, inner_matrix)
+        for m in parts:
+            if not isinstance(m, SparseMatrix):
+                raise TypeError("CondensedOperator needs device SparseMatrix parts (export the element matrices as CSR); "
+                                "got %r" % (type(m),))
+        self.parts = parts
+        self.ctx = mat.ctx
+        h = C.c_void_p()
+        _lib.check(self.ctx._lib.nsb_cond_create(self.ctx.h, *[m.h for m in parts], C.byref(h)), "nsb_cond_create")
+        self.h = h
+
+    @classmethod
+    def from_bilinear_form(cls, blfA):
+        """From an object with the attributes of a condensed NGSolve BilinearForm (``.mat``, ``.harmonic_extension``,
+        ``.harmonic_extension_trans``, ``.inner_solve``, ``.inner_matrix``) holding device matrices."""
+        return cls(blfA.mat, blfA.harmonic_extension, blfA.harmonic_extension_trans, blfA.inner_solve, blfA.inner_matrix)
+
+    @property
+    def height(self):
+        return self.parts[0].height
+
+    @property
+    def width(self):
+        return self.parts[0].width
+
+    def __mul__(self, v):
+        px, nx, keep = buffer_of(v)
+        if nx != self.width:
+            raise ValueError("vector length %d != %d" % (nx, self.width))
+        out = keep.new_empty(self.height) if _is_torch(keep) else np.empty(self.height)
+        py, _, _ = buffer_of(out)
+        _lib.check(self.ctx._lib.nsb_cond_apply(self.ctx.h, self.h, px, py), "nsb_cond_apply")
+        return BaseVector(out)
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None) and self.ctx.h:
+                self.ctx._lib.nsb_cond_destroy(self.h)
+        except Exception:
+            pass
+
+
 class HaloPlan:
     """Device copy of a partition.Plan (send lists, receive counts) -- SURVEY.md 8(e)."""
 

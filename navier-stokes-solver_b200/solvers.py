@@ -17,7 +17,7 @@ import math
 import numpy as np
 
 from . import _lib
-from .la import (BaseVector, BlockMatrix, BlockVector, DiagonalPreconditioner, SparseMatrix, _is_torch,
+from .la import (BaseVector, BlockMatrix, BlockVector, CondensedOperator, DiagonalPreconditioner, SparseMatrix, _is_torch,
                  buffer_of, default_context)
 
 last_info = {}   # diagnostics of the most recent solve (status, seconds, iterations)
@@ -104,24 +104,25 @@ def EigenValues_Preconditioner(mat, pre, tol=1e-10, maxsteps=2000, start=None):
     """[lambda_min, lambda_max] of pre*mat by device CG-Lanczos; stands where NGSolve's
     EigenValues_Preconditioner stands (bramble_pasciak_cg.py:70, solvers/bramblepasciak_new.py:115).
     The reference only uses min() and max() of the returned list."""
-    if not isinstance(mat, SparseMatrix):
-        raise TypeError("EigenValues_Preconditioner needs a device SparseMatrix")
+    if not isinstance(mat, (SparseMatrix, CondensedOperator)):
+        raise TypeError("EigenValues_Preconditioner needs a device SparseMatrix or CondensedOperator")
     ctx = mat.ctx
-    n = mat._halo.n_owned if mat._halo is not None else mat.height
+    n = mat._halo.n_owned if getattr(mat, "_halo", None) is not None else mat.height
     pre_h, keep = _pre_handle(pre, n)
     lmin, lmax, steps = C.c_double(), C.c_double(), C.c_int()
     p_start = None
     if start is not None:
         p_start, keep2 = _flat(start, n, "start")
-    _lib.check(ctx._lib.nsb_lanczos_eigs(ctx.h, mat.h, pre_h, p_start, int(maxsteps), float(tol), C.byref(lmin),
-                                         C.byref(lmax), C.byref(steps)), "nsb_lanczos_eigs")
+    fn = ctx._lib.nsb_lanczos_eigs_condensed if isinstance(mat, CondensedOperator) else ctx._lib.nsb_lanczos_eigs
+    _lib.check(fn(ctx.h, mat.h, pre_h, p_start, int(maxsteps), float(tol), C.byref(lmin), C.byref(lmax), C.byref(steps)),
+               "nsb_lanczos_eigs")
     last_info.clear()
     last_info.update(solver="lanczos", iterations=steps.value)
     return [lmin.value, lmax.value]
 
 
 def _bpcg_engine(A, B, preA, preM, f, g, sol_flat, n_u, n_p, k, tol, maxsteps, initialize, rel_err, mode):
-    if not (isinstance(A, SparseMatrix) and isinstance(B, SparseMatrix)):
+    if not (isinstance(A, (SparseMatrix, CondensedOperator)) and isinstance(B, SparseMatrix)):
         raise TypeError("Bramble-Pasciak CG needs device SparseMatrix blocks (got %r, %r)" % (type(A), type(B)))
     ctx = A.ctx
     BT = B.CreateTranspose()                                             # bramblepasciak_new.py:198
@@ -134,9 +135,16 @@ def _bpcg_engine(A, B, preA, preM, f, g, sol_flat, n_u, n_p, k, tol, maxsteps, i
     p_sol, k5 = _flat(sol_flat, n_u + n_p, "sol")
     hist = np.zeros(int(maxsteps) + 2)
     upd, secs, status = C.c_int(), C.c_double(), C.c_int()
-    _lib.check(ctx._lib.nsb_bpcg(ctx.h, A.h, B.h, BT.h, preA_h, preM_h, float(k), p_f, p_g, p_sol, int(maxsteps), float(tol),
-                                 int(bool(initialize)), int(bool(rel_err)), int(mode), hist.ctypes.data, C.byref(upd),
-                                 C.byref(secs), C.byref(status)), "nsb_bpcg")
+    if isinstance(A, CondensedOperator):
+        if mode != 2:
+            raise NotImplementedError("static condensation exists only in BramblePasciakCG (bramblepasciak_new.py)")
+        _lib.check(ctx._lib.nsb_bpcg_condensed(ctx.h, A.h, B.h, BT.h, preA_h, preM_h, float(k), p_f, p_g, p_sol, int(maxsteps),
+                                               float(tol), int(bool(initialize)), int(bool(rel_err)), hist.ctypes.data,
+                                               C.byref(upd), C.byref(secs), C.byref(status)), "nsb_bpcg_condensed")
+    else:
+        _lib.check(ctx._lib.nsb_bpcg(ctx.h, A.h, B.h, BT.h, preA_h, preM_h, float(k), p_f, p_g, p_sol, int(maxsteps), float(tol),
+                                     int(bool(initialize)), int(bool(rel_err)), int(mode), hist.ctypes.data, C.byref(upd),
+                                     C.byref(secs), C.byref(status)), "nsb_bpcg")
     last_info.clear()
     last_info.update(solver="bpcg", updates=upd.value, seconds=secs.value, status=_lib.STATUS_NAMES[status.value], k=k,
                      history=hist[:upd.value + 1].copy(), err0=float(hist[0]))
@@ -188,11 +196,12 @@ def BramblePasciakCG(blfA, blfB, matC, f, g, preA_unscaled, preM, sol=None, tol=
     objects with ``.mat`` (device SparseMatrix) and ``.condense`` like NGSolve BilinearForms, or the
     matrices themselves.  ``matC`` is accepted and unused, as in the reference.  The residual history
     the reference prints (:245) is also kept in ``solvers.last_info['history']``."""
-    matA = getattr(blfA, "mat", blfA)
     matB = getattr(blfB, "mat", blfB)
     if getattr(blfA, "condense", False):
-        raise NotImplementedError("static condensation (blfA.condense=True, bramblepasciak_new.py:8-21,84-103) is not "
-                                  "built yet; export the uncondensed form")
+        # matA = (I - HT)(A + inner_matrix)(I - H), preconditioner through harmonic_extension (:8-21, :84-106)
+        matA = blfA if isinstance(blfA, CondensedOperator) else CondensedOperator.from_bilinear_form(blfA)
+    else:
+        matA = getattr(blfA, "mat", blfA)
     n_u, n_p = matA.height, matB.height
     if lam_min is None:
         lams = EigenValues_Preconditioner(matA, preA_unscaled, tol=1e-3)  # :115

@@ -75,3 +75,38 @@ class Case:
 
 def load_golden(name):
     return np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+
+
+def synthetic_condensation(A, free):
+    """Static condensation of an independent set I of free dofs (A_II diagonal), laid out like a condensed NGSolve
+    BilinearForm (solvers/bramblepasciak_new.py:8-21,84-103): returns dict(mat=S embedded, H, HT, inner_solve,
+    inner_matrix, interior mask) with (I - HT)(S + inner_matrix)(I - H) == A."""
+    import scipy.sparse as sp
+    A = A.tocsr()
+    n = A.shape[0]
+    interior = np.zeros(n, dtype=bool)
+    blocked = ~np.asarray(free, dtype=bool)
+    indptr, indices = A.indptr, A.indices
+    for i in range(n):
+        if blocked[i]:
+            continue
+        nb = indices[indptr[i]:indptr[i + 1]]
+        if interior[nb].any():
+            continue
+        interior[i] = True
+        blocked[nb] = True          # neighbours stay on the interface
+        blocked[i] = True
+    d = A.diagonal()
+    PI = sp.diags(interior.astype(float))
+    PG = sp.diags((~interior).astype(float))
+    Dinv = sp.diags(np.where(interior, 1.0 / np.where(d != 0, d, 1.0), 0.0))
+    A_IG = PI @ A @ PG
+    A_GI = PG @ A @ PI
+    H = (-(Dinv @ A_IG)).tocsr()
+    S = (PG @ A @ PG - A_GI @ Dinv @ A_IG).tocsr()
+    inner_matrix = sp.diags(np.where(interior, d, 0.0)).tocsr()
+    out = dict(mat=S, H=H, HT=H.T.tocsr(), inner_solve=Dinv.tocsr(), inner_matrix=inner_matrix, interior=interior)
+    for k in ("mat", "H", "HT", "inner_solve", "inner_matrix"):
+        out[k].eliminate_zeros()
+        out[k].sort_indices()
+    return out

@@ -462,3 +462,48 @@ def test_heat_large_step_matches_oracle(nsb, time_step):
     ref2 = ko.heat_large_step(K, M, heat_solve, ref, time_step, w_ref, m)
     nsb.heat_large_step(dK, dM_, dHm, pre, u, time_step, w, m, cg_tol=1e-13, cg_maxsteps=2000)
     assert relerr(u, ref2) < 1e-7
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mesh", ["chan2d", "chan3d"])
+def test_bpcg_static_condensation_matches_oracle(nsb, cases, mesh):
+    """BramblePasciakCG with blfA.condense = True (bramblepasciak_new.py:8-21,84-103): matA = (I-HT)(A+Ain)(I-H) and the
+    harmonically extended preconditioner on the device against the oracle's condensed path, same injected lambda."""
+    from oracle import krylov_oracle as ko
+    from oracle.cases import synthetic_condensation
+    c = cases(mesh)
+    cd = synthetic_condensation(c.A, c.free_u)
+    dS = cd["mat"].diagonal()
+    dAc = np.where(c.free_u & ~cd["interior"] & (dS != 0), 1.0 / np.where(dS != 0, dS, 1.0), 0.0)
+
+    class Blf:
+        condense = True
+    blf = Blf()
+    for k in ("mat", "H", "HT", "inner_solve", "inner_matrix"):
+        setattr(blf, {"H": "harmonic_extension", "HT": "harmonic_extension_trans"}.get(k, k), nsb.SparseMatrix.from_scipy(cd[k]))
+    matA = nsb.CondensedOperator.from_bilinear_form(blf)
+    x = np.random.default_rng(4).uniform(-1, 1, c.n_u)
+    ref = c.A @ x
+    np.testing.assert_allclose((matA * x).NumPy(), ref, rtol=0, atol=1e-11 * np.abs(ref).max())   # myAmatrix.Mult
+    pA, pM = nsb.DiagonalPreconditioner.from_diagonal(dAc), nsb.DiagonalPreconditioner.from_diagonal(c.dM)
+    B = nsb.SparseMatrix.from_scipy(c.B)
+    # EigenValues_Preconditioner(mat=matA, pre=preA_unscaled) on the device vs the dense value on the interface dofs
+    g_ = dAc > 0
+    Sg = cd["mat"][g_][:, g_].toarray()
+    lam_dense = float(np.linalg.eigvalsh(np.sqrt(dAc[g_])[:, None] * Sg * np.sqrt(dAc[g_])[None, :])[0])
+    lam_dev = min(nsb.EigenValues_Preconditioner(matA, pA, tol=1e-9, maxsteps=3000))
+    assert abs(lam_dev - lam_dense) < 1e-5 * lam_dense
+    lam = 0.9 * lam_dense
+    cond = dict(H=cd["H"], HT=cd["HT"], inner_solve=cd["inner_solve"], inner_matrix=cd["inner_matrix"])
+    sol_ref = c.start()
+    _, h_ref, info = ko.bramble_pasciak_cg_v2(cd["mat"], c.B, c.f, c.g, dAc, c.dM, sol=sol_ref, tol=1e-10, maxsteps=20000,
+                                              initialize=False, lam_min=lam, BT=c.BT, cond=cond)
+    sol = c.start()
+    ret = quiet(nsb.BramblePasciakCG, matA if mesh == "chan2d" else blf, B, None, c.f, c.g, pA, pM, sol, tol=1e-10,
+                maxsteps=20000, initialize=False, lam_min=lam)
+    it = ret[0][0]
+    assert abs(it - info["it"]) <= 1
+    h = nsb.solvers.last_info["history"]
+    m = min(50, len(h), len(h_ref))
+    np.testing.assert_allclose(h[:m], np.array(h_ref[:m]), rtol=HIST_RTOL)
+    assert relerr(sol, sol_ref) < 1e-7

@@ -196,3 +196,33 @@ def test_c_oracle_spmv_and_threads(cases):
     x = np.random.default_rng(0).uniform(-1, 1, c.n_u)
     np.testing.assert_allclose(cbuild.spmv(c.A, x), c.A @ x, rtol=0, atol=1e-13)
     assert cbuild.num_threads() >= 1
+
+
+def test_condensed_operator_identity_and_oracle_path(cases):
+    """(I - HT)(S + inner_matrix)(I - H) == A for the synthetic condensation, and the oracle's condensed
+    BramblePasciakCG (bramblepasciak_new.py:8-21,84-103) converges to the uncondensed solution."""
+    from oracle.cases import synthetic_condensation
+    c = cases("chan2d")
+    cd = synthetic_condensation(c.A, c.free_u)
+    assert cd["interior"].sum() > 0.1 * c.n_u
+    x = np.random.default_rng(1).uniform(-1, 1, c.n_u)
+    y = x - cd["H"] @ x
+    y = cd["mat"] @ y + cd["inner_matrix"] @ y
+    y = y - cd["HT"] @ y
+    np.testing.assert_allclose(y, c.A @ x, rtol=0, atol=1e-11 * np.abs(c.A @ x).max())
+    dS = cd["mat"].diagonal()
+    dAc = np.where(c.free_u & ~cd["interior"] & (dS != 0), 1.0 / np.where(dS != 0, dS, 1.0), 0.0)
+    cond = dict(H=cd["H"], HT=cd["HT"], inner_solve=cd["inner_solve"], inner_matrix=cd["inner_matrix"])
+    # scale factor from lambda_min(preA_unscaled * matA) (:115): preA_unscaled lives on the interface dofs, where
+    # matA acts as the Schur complement S
+    g_ = dAc > 0
+    Sg = cd["mat"][g_][:, g_].toarray()
+    lam = 0.9 * float(np.linalg.eigvalsh(np.sqrt(dAc[g_])[:, None] * Sg * np.sqrt(dAc[g_])[None, :])[0])
+    sol_c = c.start()
+    _, hc, ic = ko.bramble_pasciak_cg_v2(cd["mat"], c.B, c.f, c.g, dAc, c.dM, sol=sol_c, tol=1e-10, maxsteps=20000,
+                                         initialize=False, lam_min=lam, BT=c.BT, cond=cond)
+    sol_u = c.start()
+    ko.bramble_pasciak_cg_v2(c.A, c.B, c.f, c.g, c.dA, c.dM, sol=sol_u, tol=1e-10, maxsteps=20000, initialize=False,
+                             lam_min=0.9 * c.lam_min(), BT=c.BT)
+    assert ic["converged"]
+    assert relerr(sol_c, sol_u) < 1e-6
