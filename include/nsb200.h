@@ -176,6 +176,13 @@ NSB_API int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* 
  * in place.  basis = m vectors of length n stored one after another (stride n). */
 NSB_API int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int tries);
 
+/* Device-resident vector helpers for the time-stepper chains (DoTimeStep / Project,
+ * templates/NavierStokesSIMPLE_iterative.py:427-443): all pointers must be device pointers.
+ *   nsb_vec_axpby:        y = a x + b y          (temp.data += ..., gfu.vec.data += timestep * temp2.data, :432-438)
+ *   nsb_vec_gather_axpy:  y[i] += a x[idx[i]]    (vel.data -= mapV * tmp_projection with mapV = PermutationMatrix, :138-144,:442) */
+NSB_API int nsb_vec_axpby(nsb_ctx ctx, double* y, double a, const double* x, double b, int64_t n);
+NSB_API int nsb_vec_gather_axpy(nsb_ctx ctx, double* y, double a, const double* x, const int32_t* idx, int64_t n);
+
 /* One pass of the time-loop body of heat.py:81-146 ("exponential integrator" in an m-dimensional subspace):
  * basis u, then m-1 implicit Euler sub-steps u -= dt H^-1 K u with dt = time_step/m (heat.py:95-98; H = M + dt K is
  * solved by Jacobi-CG in place of the direct heat.mat.Inverse of heat.py:72), orthonormalize (:100), projected

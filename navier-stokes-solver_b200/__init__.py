@@ -3,7 +3,8 @@ matschiner/navier-stokes-solver (minres.py, bramble_pasciak_cg.py, solvers/bramb
 orthonormalization.py) behind the same call signatures.  Compute lives in libnsb200.so (hand-written
 sm_100a CUDA behind the C ABI of include/nsb200.h); this package is the host-side mirror of the
 reference's operator/vector protocol."""
-from . import _lib, la, solvers  # noqa: F401
+from . import _lib, la, solvers, simple  # noqa: F401
+from .simple import ExtendedInverse, PermutationMatrix, SimpleStepper  # noqa: F401
 from .la import (BaseVector, BlockMatrix, BlockVector, CondensedOperator, Context, DiagonalPreconditioner, IdentityMatrix,  # noqa: F401
                  InnerProduct, Norm, Preconditioner, SparseMatrix, default_context, set_default_context)
 from .solvers import (BramblePasciakCG, CGSolve, CGSolver, EigenValues_Preconditioner, MinRes,  # noqa: F401

@@ -62,6 +62,8 @@ SIGNATURES = {
                                      C.c_int, C.c_double, C.c_int, C.c_int, C.c_void_p, P(C.c_int), P(C.c_double), P(C.c_int)]),
     "nsb_lanczos_eigs_condensed": (C.c_int, [c_ctx, C.c_void_p, c_pre, C.c_void_p, C.c_int, C.c_double, P(C.c_double),
                                              P(C.c_double), P(C.c_int)]),
+    "nsb_vec_axpby": (C.c_int, [c_ctx, C.c_void_p, C.c_double, C.c_void_p, C.c_double, C.c_int64]),
+    "nsb_vec_gather_axpy": (C.c_int, [c_ctx, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int64]),
     "nsb_heat_step": (C.c_int, [c_ctx, c_mat, c_mat, c_mat, c_pre, C.c_void_p, C.c_double, C.c_int, C.c_int, C.c_void_p,
                                 C.c_void_p, C.c_double, C.c_int, P(C.c_int), C.c_void_p, C.c_void_p]),
 }

@@ -68,3 +68,48 @@ int vec_dot(Context& c, const double* x, const double* y, int64_t n, double* out
 }
 
 }  // namespace nsb
+
+// ---- device-resident vector helpers of the time-stepper chains (templates/NavierStokesSIMPLE_iterative.py:427-443) ----
+namespace nsb {
+
+__global__ void __launch_bounds__(kBlock) k_axpby(double* __restrict__ y, double a, const double* __restrict__ x, double b, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] = b == 0.0 ? a * x[i] : a * x[i] + b * y[i];
+}
+
+// y[i] += a * x[idx[i]]   (PermutationMatrix / Embedding apply: vel.data -= mapV * tmp_projection, :442)
+__global__ void __launch_bounds__(kBlock) k_gather_axpy(double* __restrict__ y, double a, const double* __restrict__ x,
+                                                        const int* __restrict__ idx, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] += a * x[idx[i]];
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+extern "C" int nsb_vec_axpby(nsb_ctx ctx, double* y, double a, const double* x, double b, int64_t n) {
+    NSB_REQUIRE(ctx && y && x && n >= 0, "nsb_vec_axpby: bad argument");
+    NSB_REQUIRE(is_device_ptr(y) && is_device_ptr(x), "nsb_vec_axpby: device-resident vectors only");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    if (n == 0) return NSB_OK;
+    k_axpby<<<vec_grid(n, c.num_sms), kBlock, 0, c.stream>>>(y, a, x, b, n);
+    c.launches++;
+    NSB_CUDA(cudaGetLastError());
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    return NSB_OK;
+}
+
+extern "C" int nsb_vec_gather_axpy(nsb_ctx ctx, double* y, double a, const double* x, const int32_t* idx, int64_t n) {
+    NSB_REQUIRE(ctx && y && x && idx && n >= 0, "nsb_vec_gather_axpy: bad argument");
+    NSB_REQUIRE(is_device_ptr(y) && is_device_ptr(x) && is_device_ptr(idx), "nsb_vec_gather_axpy: device-resident arrays only");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    if (n == 0) return NSB_OK;
+    k_gather_axpy<<<vec_grid(n, c.num_sms), kBlock, 0, c.stream>>>(y, a, x, idx, n);
+    c.launches++;
+    NSB_CUDA(cudaGetLastError());
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    return NSB_OK;
+}

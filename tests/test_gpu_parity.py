@@ -518,3 +518,81 @@ def test_bpcg_static_condensation_matches_oracle(nsb, cases, mesh):
         # the exit index and the last digits of the iterate are not comparable -- only that both converged.
         assert nsb.solvers.last_info["status"] == "converged" and info["converged"]
         assert relerr(sol, sol_ref) < 5e-3
+
+
+def _simple_case(mesh_cells=(12, 4), lengths=(2.0, 0.41), dt=1e-3, seed=5):
+    """Synthetic operators with the shapes of NavierStokesSIMPLE_iterative.py:79-144: a, mstar = M + dt a, the mixed
+    projection system [[-Ml, B^T], [B, 0]] condensed onto the pressure (diagonal mass Ml), bproj = [0; B], mapV a
+    permutation between the continuous (V) and the 'broken' (V2) velocity numbering."""
+    import scipy.sparse as sp
+    import navier_stokes_solver_b200.synthetic as syn
+    S = syn.assemble_stokes(mesh_cells, lengths, with_mass2=True)
+    d = S.dim
+    A = S.A.to_scipy()
+    B = S.B.to_scipy()
+    free = S.free_u.numpy()
+    M = sp.kron(sp.identity(d), S.extras["M2"].to_scipy()).tocsr()
+    mstar = (M + dt * A).tocsr()
+    n_u, n_p = S.n_u, S.n_p
+    rng = np.random.default_rng(seed)
+    perm = rng.permutation(n_u)                         # V dof i lives at V2 dof perm[i]
+    Ml = M.diagonal()                                   # (row sums vanish at P2 vertices; the diagonal is positive)
+    Bf = (B @ sp.diags(free.astype(float))).tocsr()
+    P = sp.csr_matrix((np.ones(n_u), (perm, np.arange(n_u))), shape=(n_u, n_u))   # V -> V2
+    B2 = (Bf @ P.T).tocsr()
+    Ml2 = P @ Ml
+    N = n_u + n_p
+    Z = sp.csr_matrix((n_u, n_u))
+    Smat = sp.bmat([[Z, None], [None, B2 @ sp.diags(1.0 / Ml2) @ B2.T]]).tocsr()
+    H = sp.bmat([[Z, sp.diags(1.0 / Ml2) @ B2.T], [sp.csr_matrix((n_p, n_u)), sp.csr_matrix((n_p, n_p))]]).tocsr()
+    inner = sp.bmat([[sp.diags(-1.0 / Ml2), None], [None, sp.csr_matrix((n_p, n_p))]]).tocsr()
+    bproj = sp.bmat([[sp.csr_matrix((n_u, n_u))], [Bf]]).tocsr()
+    dS = Smat.diagonal()
+    return dict(A=A, mstar=mstar, free=free, Bf=Bf, S=Smat, H=H, HT=H.T.tocsr(), inner=inner, bproj=bproj, perm=perm,
+                dS=np.where(dS > 0, 1.0 / np.where(dS > 0, dS, 1.0), 0.0), n_u=n_u, n_p=n_p, N=N, f=S.f.numpy(), u0=S.u0.numpy(), dt=dt)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("condense_mstar", [False, True])
+def test_simple_time_step_chain_matches_oracle(nsb, condense_mstar):
+    """DoTimeStep / Project (NavierStokesSIMPLE_iterative.py:427-443) device-resident over three steps vs the oracle."""
+    import torch
+    from oracle import krylov_oracle as ko
+    from oracle.cases import synthetic_condensation
+    T = _simple_case()
+    n_u, n_p, dt = T["n_u"], T["n_p"], T["dt"]
+    p_range = (n_u, n_u + n_p)
+    if condense_mstar:
+        cd = synthetic_condensation(T["mstar"], T["free"])
+        ms, cond = cd["mat"], dict(H=cd["H"], HT=cd["HT"], inner_solve=cd["inner_solve"])
+        dms = ms.diagonal()
+        dm = np.where(T["free"] & ~cd["interior"] & (dms != 0), 1.0 / np.where(dms != 0, dms, 1.0), 0.0)
+    else:
+        ms, cond = T["mstar"], None
+        dm = np.where(T["free"], 1.0 / T["mstar"].diagonal(), 0.0)
+    pcond = dict(H=T["H"], HT=T["HT"], inner_solve=T["inner"])
+    # ---- oracle
+    inv_ms = ko.extended_inverse(lambda r: ko.pcg(ms, r, pre=dm, tol=1e-12, maxsteps=2000)[0], cond)
+    inv_pr = ko.extended_inverse(lambda r: ko.pcg(T["S"], r, pre=T["dS"], tol=1e-12, maxsteps=4000)[0], pcond)
+    gfu_ref = T["u0"].copy()
+    for _ in range(3):
+        p_ref = ko.simple_time_step(gfu_ref, T["A"], inv_ms, lambda v: ko.simple_project(v, inv_pr, T["bproj"], T["perm"], p_range),
+                                    dt, n_u, f=T["f"])
+    # ---- device
+    up = nsb.SparseMatrix.from_scipy
+    Ms = up(ms)
+    inv1 = nsb.CGSolver(Ms, nsb.DiagonalPreconditioner.from_diagonal(dm), precision=1e-12, maxsteps=2000)
+    invmstar = nsb.ExtendedInverse(inv1, *([up(cond[k]) for k in ("H", "HT", "inner_solve")] if cond else []))
+    Sm = up(T["S"])
+    invp1 = nsb.CGSolver(Sm, nsb.DiagonalPreconditioner.from_diagonal(T["dS"]), precision=1e-12, maxsteps=4000)
+    invproj = nsb.ExtendedInverse(invp1, up(T["H"]), up(T["HT"]), up(T["inner"]))
+    gfu = torch.as_tensor(T["u0"].copy(), device="cuda")
+    stepper = nsb.SimpleStepper(up(T["A"]), invmstar, up(T["bproj"]), invproj, nsb.PermutationMatrix(T["N"], T["perm"]), gfu,
+                                n_u, p_range, dt, f=torch.as_tensor(T["f"], device="cuda"))
+    for _ in range(3):
+        stepper.DoTimeStep()
+    assert relerr(gfu.cpu().numpy(), gfu_ref) < 1e-8
+    assert relerr(stepper.gfup.cpu().numpy(), p_ref) < 1e-6
+    # the projected increment is discretely divergence-free on the free dofs:  B (gfu - u0) = dt * sum B temp2 = 0
+    div = T["Bf"] @ (gfu.cpu().numpy() - T["u0"])
+    assert np.abs(div).max() < 1e-9 * max(1.0, np.abs(T["Bf"]).sum(axis=1).max())
