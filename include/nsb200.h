@@ -121,6 +121,17 @@ NSB_API int nsb_pre_create_diag(nsb_ctx ctx, int64_t n, const double* d, nsb_pre
 NSB_API int nsb_pre_create_jacobi(nsb_ctx ctx, nsb_mat m, const uint8_t* free_mask, nsb_pre* out);
 /* block-diagonal of two diagonal preconditioners: BlockMatrix([[preA, None], [None, preS]]) (run.py:46) */
 NSB_API int nsb_pre_create_blockdiag2(nsb_ctx ctx, nsb_pre a, nsb_pre b, nsb_pre* out);
+/* Block smoother: a.mat.CreateBlockSmoother(blocks) with the facet blocks of NavierStokesSIMPLE_iterative.py:360-373.
+ * Disjoint dof blocks (at most 64 dofs each) in CSR-like form, listed colour by colour: blocks [color_ptr[c], color_ptr[c+1])
+ * are mutually uncoupled through A, so one colour is one parallel launch and a sweep equals the sequential block
+ * Gauss-Seidel sweep in the given block order.  ncolors == 0: additive use only.  As a preconditioner (nsb_pre_apply,
+ * nsb_bpcg preA, nsb_cg pre) the handle acts as  jacobi * x  (gauss_seidel == 0; MypreA with GS = False without the
+ * auxiliary-space term, :383)  or as  y = 0; Smooth(y, x); SmoothBack(y, x)  (gauss_seidel != 0; :375-381). */
+NSB_API int nsb_pre_create_blocks(nsb_ctx ctx, nsb_mat A, int64_t nblocks, const int64_t* block_ptr, const int32_t* block_dofs,
+                                  int ncolors, const int64_t* color_ptr, int gauss_seidel, nsb_pre* out);
+/* jacobi.Smooth(y, x) (backward == 0) / jacobi.SmoothBack(y, x) (backward != 0): one block Gauss-Seidel sweep on y for the
+ * right-hand side x (:377,:381) */
+NSB_API int nsb_pre_smooth(nsb_ctx ctx, nsb_pre p, const double* x, double* y, int backward);
 NSB_API int nsb_pre_destroy(nsb_pre p);
 NSB_API int nsb_pre_apply(nsb_ctx ctx, nsb_pre p, const double* x, double* y);
 

@@ -1,0 +1,213 @@
+// blockpre.cu -- block smoother: a.mat.CreateBlockSmoother(blocks) with its three uses in MypreA
+// (templates/NavierStokesSIMPLE_iterative.py:360-383):
+//   jacobi * x            additive block Jacobi            y   = sum_b P_b^T A_bb^-1 P_b x            (:383)
+//   jacobi.Smooth(y, x)   forward block Gauss-Seidel       y_b += A_bb^-1 (x - A y)_b, b ascending    (:377)
+//   jacobi.SmoothBack     the same sweep, b descending                                                  (:381)
+// Blocks are disjoint dof lists (the facet blocks of :360-362), handed over colour by colour: blocks of one
+// colour are not coupled through A, so a colour is one parallel launch and the sweep equals the sequential
+// sweep in that block order.  Dense inverses are computed once on the device (Gauss-Jordan in shared memory).
+#include "spmv.cuh"
+
+namespace nsb {
+
+constexpr int kMaxBlockDofs = 64;
+
+// one CUDA block per smoother block: gather A_bb from CSR, invert
+__global__ void __launch_bounds__(64) k_block_invert(CsrView A, const int64_t* __restrict__ bptr, const int* __restrict__ bdofs,
+                                                     const int64_t* __restrict__ iptr, double* __restrict__ inv, int64_t nblocks,
+                                                     int* __restrict__ bad) {
+    __shared__ double M[kMaxBlockDofs][kMaxBlockDofs + 1];
+    __shared__ int dofs[kMaxBlockDofs];
+    for (int64_t b = blockIdx.x; b < nblocks; b += gridDim.x) {
+        const int64_t d0 = bptr[b];
+        const int s = (int)(bptr[b + 1] - d0);
+        const int t = threadIdx.x;
+        __syncthreads();
+        if (t < s) dofs[t] = bdofs[d0 + t];
+        __syncthreads();
+        if (t < s) {
+            for (int j = 0; j < s; ++j) M[t][j] = 0.0;
+            const int r = dofs[t];
+            for (int p = A.rowptr[r]; p < A.rowptr[r + 1]; ++p) {
+                const int col = A.colidx[p];
+                for (int j = 0; j < s; ++j)
+                    if (dofs[j] == col) M[t][j] += A.values[p];
+            }
+        }
+        __syncthreads();
+        for (int k = 0; k < s; ++k) {           // in-place Gauss-Jordan without pivoting (A_bb is SPD on free dofs)
+            const double piv = M[k][k];
+            if (t == 0 && !(fabs(piv) > 0.0)) atomicExch(bad, 1);
+            __syncthreads();
+            if (t < s) M[k][t] = (t == k) ? 1.0 / piv : M[k][t] / piv;    // thread t owns column t of the pivot row
+            __syncthreads();
+            if (t < s && t != k) {                                          // thread t owns row t
+                const double f = M[t][k];
+                for (int j = 0; j < s; ++j) M[t][j] = (j == k) ? -f * M[k][k] : M[t][j] - f * M[k][j];
+            }
+            __syncthreads();
+        }
+        if (t < s)
+            for (int j = 0; j < s; ++j) inv[iptr[b] + (int64_t)t * s + j] = M[t][j];
+    }
+}
+
+// additive apply / one colour of a Gauss-Seidel sweep: one warp per block
+template <bool GS>
+__global__ void __launch_bounds__(kBlock) k_block_apply(CsrView A, const int64_t* __restrict__ bptr, const int* __restrict__ bdofs,
+                                                        const int64_t* __restrict__ iptr, const double* __restrict__ inv,
+                                                        int64_t b0, int64_t b1, const double* __restrict__ x, double* y) {
+    __shared__ double sr[kBlock / 32][kMaxBlockDofs];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t b = b0 + warp; b < b1; b += nwarps) {
+        const int64_t d0 = bptr[b];
+        const int s = (int)(bptr[b + 1] - d0);
+        __syncwarp();
+        for (int i = lane; i < s; i += 32) {
+            const int r = bdofs[d0 + i];
+            double v = x[r];
+            if (GS) {                                         // residual row: (x - A y)_r
+                for (int p = A.rowptr[r]; p < A.rowptr[r + 1]; ++p) v -= A.values[p] * y[A.colidx[p]];
+            }
+            sr[w][i] = v;
+        }
+        __syncwarp();
+        const double* Ib = inv + iptr[b];
+        for (int i = lane; i < s; i += 32) {
+            double acc = 0.0;
+            for (int j = 0; j < s; ++j) acc = fma(Ib[(int64_t)i * s + j], sr[w][j], acc);
+            const int r = bdofs[d0 + i];
+            y[r] = GS ? y[r] + acc : acc;
+        }
+    }
+}
+
+static int block_grid(Context& c, int64_t nb) {
+    int64_t want = (nb + (kBlock / 32) - 1) / (kBlock / 32);
+    if (want < 1) want = 1;
+    const int64_t cap = (int64_t)c.num_sms * 8;
+    return (int)(want < cap ? want : cap);
+}
+
+// y = jacobi * x
+static int block_jacobi(Context& c, nsb_pre_s* p, const double* x, double* y) {
+    NSB_CHECK(vec_set(c, y, 0.0, p->n));
+    if (p->nblocks == 0) return NSB_OK;
+    k_block_apply<false><<<block_grid(c, p->nblocks), kBlock, 0, c.stream>>>(view_of(p->mat), p->block_ptr.p, p->block_dofs.p,
+                                                                            p->inv_ptr.p, p->inv.p, 0, p->nblocks, x, y);
+    c.launches++;
+    NSB_CUDA(cudaGetLastError());
+    return NSB_OK;
+}
+
+// jacobi.Smooth(y, x) / jacobi.SmoothBack(y, x): colours ascending / descending
+int block_gs_sweep(Context& c, nsb_pre_s* p, const double* x, double* y, bool backward) {
+    for (int k = 0; k < p->ncolors; ++k) {
+        const int col = backward ? p->ncolors - 1 - k : k;
+        const int64_t b0 = p->color_ptr[col], b1 = p->color_ptr[col + 1];
+        if (b1 <= b0) continue;
+        k_block_apply<true><<<block_grid(c, b1 - b0), kBlock, 0, c.stream>>>(view_of(p->mat), p->block_ptr.p, p->block_dofs.p,
+                                                                            p->inv_ptr.p, p->inv.p, b0, b1, x, y);
+        c.launches++;
+    }
+    NSB_CUDA(cudaGetLastError());
+    return NSB_OK;
+}
+
+int pre_apply_device(Context& c, nsb_pre_s* p, const double* x, double* y) {
+    if (p->kind == 0) return vec_diagmul(c, y, 1.0, p->d.p, x, p->n);
+    if (!p->gs) return block_jacobi(c, p, x, y);
+    // MypreA.Mult with GS = True and no auxiliary-space term (:375-381): y = 0; Smooth(y, x); SmoothBack(y, x)
+    NSB_CHECK(vec_set(c, y, 0.0, p->n));
+    NSB_CHECK(block_gs_sweep(c, p, x, y, false));
+    return block_gs_sweep(c, p, x, y, true);
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+extern "C" int nsb_pre_create_blocks(nsb_ctx ctx, nsb_mat A, int64_t nblocks, const int64_t* block_ptr, const int32_t* block_dofs,
+                                     int ncolors, const int64_t* color_ptr, int gauss_seidel, nsb_pre* out) {
+    NSB_REQUIRE(ctx && A && out && block_ptr && nblocks >= 0, "nsb_pre_create_blocks: bad argument");
+    NSB_REQUIRE(A->rows == A->cols && A->halo == nullptr, "nsb_pre_create_blocks: square, not row-partitioned operator needed");
+    NSB_REQUIRE(ncolors >= 0 && (ncolors == 0 || color_ptr), "nsb_pre_create_blocks: colour table missing");
+    NSB_REQUIRE(!gauss_seidel || ncolors > 0, "nsb_pre_create_blocks: Gauss-Seidel sweeps need the colouring");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    const int64_t ndofs = block_ptr[nblocks];
+    NSB_REQUIRE(block_ptr[0] == 0 && ndofs >= 0 && (ndofs == 0 || block_dofs), "nsb_pre_create_blocks: bad block table");
+    std::vector<int64_t> iptr(nblocks + 1, 0);
+    int maxb = 0;
+    for (int64_t b = 0; b < nblocks; ++b) {
+        const int64_t s = block_ptr[b + 1] - block_ptr[b];
+        NSB_REQUIRE(s >= 0 && s <= kMaxBlockDofs, "nsb_pre_create_blocks: block %lld has %lld dofs (limit %d)", (long long)b,
+                    (long long)s, kMaxBlockDofs);
+        iptr[b + 1] = iptr[b] + s * s;
+        if ((int)s > maxb) maxb = (int)s;
+    }
+    if (ncolors > 0) NSB_REQUIRE(color_ptr[0] == 0 && color_ptr[ncolors] == nblocks, "nsb_pre_create_blocks: colours must cover all blocks");
+    nsb_pre_s* p = new nsb_pre_s();
+    p->ctx = &c;
+    p->n = A->rows;
+    p->kind = 1;
+    p->mat = A;
+    p->nblocks = nblocks;
+    p->ncolors = ncolors;
+    p->max_block = maxb;
+    p->gs = gauss_seidel ? 1 : 0;
+    if (ncolors > 0) p->color_ptr.assign(color_ptr, color_ptr + ncolors + 1);
+    DevBuf<int> bad;
+    int r = p->block_ptr.alloc(nblocks + 1);
+    if (r == NSB_OK) r = p->block_dofs.alloc(ndofs > 0 ? ndofs : 1);
+    if (r == NSB_OK) r = p->inv_ptr.alloc(nblocks + 1);
+    if (r == NSB_OK) r = p->inv.alloc(iptr[nblocks] > 0 ? iptr[nblocks] : 1);
+    if (r == NSB_OK) r = bad.alloc(1);
+    cudaError_t e = cudaSuccess;
+    if (r == NSB_OK) {
+        e = cudaMemcpy(p->block_ptr.p, block_ptr, sizeof(int64_t) * (nblocks + 1), cudaMemcpyDefault);
+        if (e == cudaSuccess && ndofs > 0) e = cudaMemcpy(p->block_dofs.p, block_dofs, sizeof(int32_t) * ndofs, cudaMemcpyDefault);
+        if (e == cudaSuccess) e = cudaMemcpy(p->inv_ptr.p, iptr.data(), sizeof(int64_t) * (nblocks + 1), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemset(bad.p, 0, sizeof(int));
+    }
+    int hbad = 0;
+    if (r == NSB_OK && e == cudaSuccess && nblocks > 0) {
+        const int64_t g = nblocks < (int64_t)c.num_sms * 16 ? nblocks : (int64_t)c.num_sms * 16;
+        k_block_invert<<<(int)g, 64, 0, c.stream>>>(view_of(A), p->block_ptr.p, p->block_dofs.p, p->inv_ptr.p, p->inv.p, nblocks, bad.p);
+        c.launches++;
+        e = cudaStreamSynchronize(c.stream);
+        if (e == cudaSuccess) e = cudaMemcpy(&hbad, bad.p, sizeof(int), cudaMemcpyDeviceToHost);
+    }
+    if (r == NSB_OK && e != cudaSuccess) {
+        set_error("nsb_pre_create_blocks: %s", cudaGetErrorString(e));
+        r = NSB_ERR_CUDA;
+    }
+    if (r == NSB_OK && hbad) {
+        set_error("nsb_pre_create_blocks: a diagonal block is singular (zero pivot)");
+        r = NSB_ERR_BREAKDOWN;
+    }
+    if (r != NSB_OK) {
+        delete p;
+        return r;
+    }
+    *out = p;
+    return NSB_OK;
+}
+
+extern "C" int nsb_pre_smooth(nsb_ctx ctx, nsb_pre p, const double* x, double* y, int backward) {
+    NSB_REQUIRE(ctx && p && x && y, "nsb_pre_smooth: NULL argument");
+    NSB_REQUIRE(p->kind == 1 && p->ncolors > 0, "nsb_pre_smooth: needs a coloured block smoother");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    DevBuf<double> dx, dy;
+    NSB_CHECK(dx.allocs(c, p->n));
+    NSB_CHECK(dy.allocs(c, p->n));
+    NSB_CHECK(copy_in(c, dx.p, x, p->n));
+    NSB_CHECK(copy_in(c, dy.p, y, p->n));
+    NSB_CHECK(block_gs_sweep(c, p, dx.p, dy.p, backward != 0));
+    NSB_CHECK(copy_out(c, y, dy.p, p->n));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    return NSB_OK;
+}

@@ -238,9 +238,15 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     if (preM) NSB_REQUIRE(preM->n == n_p, "nsb_bpcg: preM size mismatch");
     NSB_REQUIRE(maxsteps >= 0, "nsb_bpcg: maxsteps < 0");
     const bool fused = c.nranks == 1;
-    const double* dA = preA->d.p;
+    // preA: diagonal (fused into the SpMV epilogues) or a block smoother (MypreA's Jacobi / Gauss-Seidel part,
+    // NavierStokesSIMPLE_iterative.py:364-383), applied as its own kernels between B1 and B2
+    const bool general_pre = preA->kind != 0;
+    const double* dA = general_pre ? nullptr : preA->d.p;
+    if (preM) NSB_REQUIRE(preM->kind == 0, "nsb_bpcg: preM must be diagonal");
     const double* dM = preM ? preM->d.p : nullptr;
     if (K) NSB_REQUIRE(c.nranks == 1 && mode == 2, "nsb_bpcg_condensed: single-GPU, v2 semantics only");
+    if (K) NSB_REQUIRE(!general_pre, "nsb_bpcg_condensed: diagonal preA_unscaled only");
+    if (general_pre) NSB_REQUIRE(c.nranks == 1, "nsb_bpcg: block smoothers are single-GPU");
     DevBuf<double> cr, cy;   // scratch of the condensed preconditioner chain
     if (K) {
         NSB_CHECK(cr.allocs(c, n_u));
@@ -253,6 +259,10 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     };
     auto applyPre = [&](const double* x, double* y) -> int {
         if (K) return cond_apply_pre(c, K, x, dA, k_scale, cr.p, cy.p, y);
+        if (general_pre) {
+            NSB_CHECK(pre_apply_device(c, preA, x, y));
+            return vec_lincomb(c, y, k_scale, y, 0, nullptr, 0, nullptr, n_u);
+        }
         return vec_diagmul(c, y, k_scale, dA, x, n_u);
     };
 
@@ -312,11 +322,12 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     const int vg = vec_grid(n_u + n_p, c.num_sms);
     auto launch_iteration = [&]() -> int {
         NSB_CHECK(halo_exchange(c, BT->halo, s1.p));
-        if (K) {
+        if (K || general_pre) {
             NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1cOp{S, As0.p, z0.p, s0.p, w0.p, tmp0.p}));
             NSB_CHECK(applyPre(tmp0.p, tmp1.p));                                                   // :209
             NSB_CHECK(vec_lincomb(c, tmp4.p, 1.0, tmp1.p, -1.0, s0.p, 0, nullptr, n_u));           // :212
-            NSB_CHECK((cond_apply_A<1>(c, K, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused})));   // :210,:218,:222
+            if (K) NSB_CHECK((cond_apply_A<1>(c, K, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused})));   // :210,:218,:222
+            else NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
         } else {
             NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p}));
             // tmp1 and tmp4 travel in the velocity halo

@@ -130,11 +130,14 @@ struct CgBuffers {
     DevBuf<CgState> st;
 };
 
-static int cg_run(Context& c, nsb_mat_s* A, const double* dinv, CgBuffers& b, bool want_u, int maxsteps, double tol,
+static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool want_u, int maxsteps, double tol,
                   bool lanczos, int chunk, bool (*host_check)(void*, const CgState&), void* check_arg, CgState* out_state,
                   float* out_ms, nsb_cond_s* K = nullptr) {
     const int64_t n = A->rows;
-    const bool fused = c.nranks == 1;
+    // a block smoother as preconditioner is applied between the update kernel and the <w,d> reduction (unfused)
+    const bool general_pre = pre != nullptr && pre->kind != 0;
+    const double* dinv = (pre && !general_pre) ? pre->d.p : nullptr;
+    const bool fused = c.nranks == 1 && !general_pre;
     CgState* S = b.st.p;
     const int vg = vec_grid(n, c.num_sms);
     double* u = want_u ? b.u.p : nullptr;
@@ -142,7 +145,8 @@ static int cg_run(Context& c, nsb_mat_s* A, const double* dinv, CgBuffers& b, bo
     double* alphas = lanczos ? b.alphas.p : nullptr;
     double* betas = lanczos ? b.betas.p : nullptr;
     // w = C d ; s = w ; wd = <w, d>
-    NSB_CHECK(vec_diagmul(c, b.w.p, 1.0, dinv, b.d.p, n));
+    if (general_pre) NSB_CHECK(pre_apply_device(c, pre, b.d.p, b.w.p));
+    else NSB_CHECK(vec_diagmul(c, b.w.p, 1.0, dinv, b.d.p, n));
     NSB_CHECK(vec_lincomb(c, b.s.p, 1.0, b.w.p, 0, nullptr, 0, nullptr, n));
     NSB_CHECK(vec_dot(c, b.w.p, b.d.p, n, &S->red[0]));
     k_cg_init_scalar<<<1, 1, 0, c.stream>>>(S, maxsteps, tol, hist, lanczos ? 1 : 0);
@@ -162,7 +166,12 @@ static int cg_run(Context& c, nsb_mat_s* A, const double* dinv, CgBuffers& b, bo
         }
         k_cg_c2<<<vg, kBlock, 0, c.stream>>>(S, u, b.s.p, b.d.p, b.q.p, dinv, b.w.p, n, hist, betas, c.partials, c.ticket, fused);
         c.launches++;
-        if (!fused) {
+        if (general_pre) {   // w = P d, then <w,d>
+            NSB_CHECK(pre_apply_device(c, pre, b.d.p, b.w.p));
+            NSB_CHECK(vec_dot(c, b.w.p, b.d.p, n, &S->red[1]));
+            k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
+            c.launches++;
+        } else if (!fused) {
             NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
             c.launches++;
@@ -358,7 +367,7 @@ static int cg_solve_device(Context& c, nsb_mat A, nsb_pre pre, CgBuffers& b, boo
         NSB_CHECK(spmv_launch<0>(c, A, b.u.p, ResidualOp2{b.q.p, b.d.p}));
     }
     const int chunk = n < 200000 ? 16 : 4;
-    return cg_run(c, A, pre ? pre->d.p : nullptr, b, true, maxsteps, tol, false, chunk, nullptr, nullptr, hs, ms);
+    return cg_run(c, A, pre, b, true, maxsteps, tol, false, chunk, nullptr, nullptr, hs, ms);
 }
 
 extern "C" int nsb_cg(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* rhs, double* sol, int maxsteps, double tol,
@@ -406,7 +415,7 @@ static int lanczos_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_pre pre, cons
     L.tol = tol;
     CgState hs;
     float ms = 0.f;
-    NSB_CHECK(cg_run(c, A, pre ? pre->d.p : nullptr, b, false, maxsteps, 0.0, true, 8, lanczos_host_check, &L, &hs, &ms, K));
+    NSB_CHECK(cg_run(c, A, pre, b, false, maxsteps, 0.0, true, 8, lanczos_host_check, &L, &hs, &ms, K));
     if (!L.converged) lanczos_host_check(&L, hs);  // fold whatever the last chunk produced
     NSB_REQUIRE(L.steps > 0, "nsb_lanczos_eigs: Lanczos produced no step (zero start residual?)");
     *lam_min = L.lam_min;

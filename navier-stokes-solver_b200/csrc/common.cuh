@@ -188,7 +188,18 @@ struct nsb_mat_s {
 struct nsb_pre_s {
     nsb::Context* ctx = nullptr;
     int64_t n = 0;
+    int kind = 0;           // 0: diagonal (y = d .* x)   1: block smoother (blockpre.cu)
     nsb::DevBuf<double> d;  // diagonal preconditioner: y = d .* x
+    // block smoother, a.mat.CreateBlockSmoother(blocks) (templates/NavierStokesSIMPLE_iterative.py:360-373): disjoint dof
+    // blocks listed colour by colour (blocks of one colour are not coupled by the matrix), dense inverse per block
+    nsb_mat_s* mat = nullptr;              // not owned
+    int64_t nblocks = 0;
+    int ncolors = 0, max_block = 0, gs = 0; // gs: nsb_pre_apply runs the symmetric block Gauss-Seidel cycle instead of block Jacobi
+    std::vector<int64_t> color_ptr;        // host copy: blocks of colour c are [color_ptr[c], color_ptr[c+1])
+    nsb::DevBuf<int64_t> block_ptr;        // nblocks + 1, into block_dofs
+    nsb::DevBuf<int32_t> block_dofs;
+    nsb::DevBuf<int64_t> inv_ptr;          // nblocks + 1, into inv (block b: size^2 entries, row-major)
+    nsb::DevBuf<double> inv;
 };
 
 namespace nsb {
@@ -284,6 +295,8 @@ int p2p_halo_exchange(Context& c, nsb_halo_s* h, double* x);
 int nccl_allgather_bytes(Context& c, const void* send_dev, void* recv_dev, size_t bytes_per_rank);   // dist.cu
 
 int build_sell(Context& c, nsb_mat_s* m);   // sell.cu
+// y = P x for any preconditioner kind, device vectors (blockpre.cu); y must not alias x
+int pre_apply_device(Context& c, nsb_pre_s* p, const double* x, double* y);
 
 // plain SpMV launch (spmv.cu): y = M x on the context stream; x must have room for the halo tail
 int spmv_plain(Context& c, const nsb_mat_s* m, const double* x, double* y);

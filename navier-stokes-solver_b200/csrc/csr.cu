@@ -432,6 +432,7 @@ int nsb_pre_create_jacobi(nsb_ctx ctx, nsb_mat m, const uint8_t* free_mask, nsb_
 
 int nsb_pre_create_blockdiag2(nsb_ctx ctx, nsb_pre a, nsb_pre b, nsb_pre* out) {
     NSB_REQUIRE(ctx && a && b && out, "nsb_pre_create_blockdiag2: NULL argument");
+    NSB_REQUIRE(a->kind == 0 && b->kind == 0, "nsb_pre_create_blockdiag2: diagonal preconditioners only");
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
     nsb_pre_s* p = new nsb_pre_s();
@@ -465,7 +466,7 @@ int nsb_pre_apply(nsb_ctx ctx, nsb_pre p, const double* x, double* y) {
     NSB_CHECK(dx.allocs(c, p->n));
     NSB_CHECK(dy.allocs(c, p->n));
     NSB_CHECK(copy_in(c, dx.p, x, p->n));
-    NSB_CHECK(vec_diagmul(c, dy.p, 1.0, p->d.p, dx.p, p->n));
+    NSB_CHECK(pre_apply_device(c, p, dx.p, dy.p));
     NSB_CHECK(copy_out(c, y, dy.p, p->n));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
     return NSB_OK;

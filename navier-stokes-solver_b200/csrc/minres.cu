@@ -223,6 +223,7 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
     if (pre) NSB_REQUIRE(pre->n == n, "nsb_minres: preconditioner size %lld != %lld", (long long)pre->n, (long long)n);
     const bool dist = c.nranks > 1;
     const bool fused = !dist;
+    if (pre) NSB_REQUIRE(pre->kind == 0, "nsb_minres: diagonal / block-diagonal-of-diagonal preconditioners only");
     const double* dinv = pre ? pre->d.p : nullptr;
 
     DevBuf<double> u, t, v[3], w[3], z[2], hist, drhs;

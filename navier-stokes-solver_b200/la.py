@@ -309,6 +309,10 @@ class SparseMatrix(BaseMatrix):
     def T(self):
         return self.CreateTranspose()
 
+    def CreateBlockSmoother(self, blocks, pattern=None, gauss_seidel=False):
+        """``a.mat.CreateBlockSmoother(jacblocks)`` (templates/NavierStokesSIMPLE_iterative.py:373)."""
+        return BlockSmoother(self, blocks, pattern, gauss_seidel)
+
     def CreateTranspose(self):
         """Explicit device transpose, built once and cached (solvers/bramblepasciak_new.py:198)."""
         if self._T is None:
@@ -490,6 +494,103 @@ class DiagonalPreconditioner(BaseMatrix):
         py, _, _ = buffer_of(out)
         _lib.check(self.ctx._lib.nsb_pre_apply(self.ctx.h, self.h, px, py), "nsb_pre_apply")
         return BaseVector(out)
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None) and self.ctx.h:
+                self.ctx._lib.nsb_pre_destroy(self.h)
+        except Exception:
+            pass
+
+
+def color_blocks(pattern, blocks):
+    """Greedy colouring of dof blocks: two blocks get different colours when ``pattern`` (scipy sparse, the matrix
+    the smoother belongs to) couples any of their dofs.  Returns (order, color_ptr): the blocks in colour-major order
+    (stable inside a colour) and the block ranges per colour."""
+    import scipy.sparse as sp
+    nb = len(blocks)
+    n = pattern.shape[0]
+    sizes = np.array([len(b) for b in blocks], dtype=np.int64)
+    dofs = np.concatenate([np.asarray(b, dtype=np.int64) for b in blocks]) if nb else np.zeros(0, np.int64)
+    owner = np.repeat(np.arange(nb), sizes)
+    if len(np.unique(dofs)) != len(dofs):
+        raise ValueError("block smoother: blocks must be disjoint")
+    P = sp.csr_matrix((np.ones(len(dofs)), (dofs, owner)), shape=(n, nb))
+    pat = sp.csr_matrix(pattern, copy=True)
+    pat.data[:] = 1.0
+    G = (P.T @ pat @ P).tocsr()
+    color = -np.ones(nb, dtype=np.int64)
+    for b in range(nb):
+        nbr = G.indices[G.indptr[b]:G.indptr[b + 1]]
+        used = set(color[nbr[nbr != b]].tolist())
+        k = 0
+        while k in used:
+            k += 1
+        color[b] = k
+    ncol = int(color.max()) + 1 if nb else 0
+    order = np.argsort(color, kind="stable")
+    color_ptr = np.concatenate([[0], np.cumsum(np.bincount(color, minlength=ncol))]).astype(np.int64)
+    return order, color_ptr
+
+
+class BlockSmoother(BaseMatrix):
+    """``a.mat.CreateBlockSmoother(blocks)`` on the device (templates/NavierStokesSIMPLE_iterative.py:360-373).
+
+    ``blocks``: list of disjoint dof lists (the facet blocks of :360-362).  With ``pattern`` (the scipy matrix, used for
+    colouring only) the sweeps ``Smooth`` / ``SmoothBack`` are available; they equal the sequential block Gauss-Seidel
+    sweep over ``self.blocks`` (the colour-major reordering of the input, kept for the caller).  As a preconditioner the
+    object acts as ``jacobi * x`` (``gauss_seidel=False``, :383) or as ``y=0; Smooth(y,x); SmoothBack(y,x)``
+    (``gauss_seidel=True``, MypreA.Mult :375-381 without the NGSolve-internal auxiliary-space term)."""
+
+    def __init__(self, mat, blocks, pattern=None, gauss_seidel=False):
+        if not isinstance(mat, SparseMatrix):
+            raise TypeError("BlockSmoother needs a device SparseMatrix")
+        self.ctx, self.mat, self.n = mat.ctx, mat, mat.height
+        blocks = [np.asarray(b, dtype=np.int32) for b in blocks if len(b) > 0]
+        if pattern is not None:
+            order, color_ptr = color_blocks(pattern, blocks)
+            blocks = [blocks[i] for i in order]
+        else:
+            if gauss_seidel:
+                raise ValueError("Gauss-Seidel sweeps need `pattern` for the colouring")
+            color_ptr = np.zeros(1, dtype=np.int64)
+        self.blocks = blocks
+        self.color_ptr = color_ptr
+        bptr = np.concatenate([[0], np.cumsum([len(b) for b in blocks])]).astype(np.int64)
+        bd = np.concatenate(blocks).astype(np.int32) if blocks else np.zeros(1, np.int32)
+        h = _lib.c_pre()
+        ncol = len(color_ptr) - 1
+        _lib.check(self.ctx._lib.nsb_pre_create_blocks(self.ctx.h, mat.h, len(blocks), bptr.ctypes.data, bd.ctypes.data, ncol,
+                                                       color_ptr.ctypes.data if ncol else None, int(bool(gauss_seidel)),
+                                                       C.byref(h)), "nsb_pre_create_blocks")
+        self.h = h
+
+    @property
+    def height(self):
+        return self.n
+
+    @property
+    def width(self):
+        return self.n
+
+    def __mul__(self, v):
+        px, nx, keep = buffer_of(v)
+        out = np.empty(self.n) if not _is_torch(keep) else keep.new_empty(self.n)
+        py, _, _ = buffer_of(out)
+        _lib.check(self.ctx._lib.nsb_pre_apply(self.ctx.h, self.h, px, py), "nsb_pre_apply")
+        return BaseVector(out)
+
+    def Smooth(self, y, x):
+        """One forward block Gauss-Seidel sweep on ``y`` for the right-hand side ``x`` (:377)."""
+        px, _, _ = buffer_of(x)
+        py, _, _ = buffer_of(y)
+        _lib.check(self.ctx._lib.nsb_pre_smooth(self.ctx.h, self.h, px, py, 0), "nsb_pre_smooth")
+
+    def SmoothBack(self, y, x):
+        """One backward sweep (:381)."""
+        px, _, _ = buffer_of(x)
+        py, _, _ = buffer_of(y)
+        _lib.check(self.ctx._lib.nsb_pre_smooth(self.ctx.h, self.h, px, py, 1), "nsb_pre_smooth")
 
     def __del__(self):
         try:

@@ -596,3 +596,71 @@ def test_simple_time_step_chain_matches_oracle(nsb, condense_mstar):
     # the projected increment is discretely divergence-free on the free dofs:  B (gfu - u0) = dt * sum B temp2 = 0
     div = T["Bf"] @ (gfu.cpu().numpy() - T["u0"])
     assert np.abs(div).max() < 1e-9 * max(1.0, np.abs(T["Bf"]).sum(axis=1).max())
+
+
+def _blocks_of(c, size=5):
+    free_idx = np.nonzero(c.free_u)[0]
+    return [free_idx[i:i + size] for i in range(0, len(free_idx), size)]
+
+
+@pytest.mark.gpu
+def test_block_smoother_matches_oracle(nsb, cases):
+    """a.mat.CreateBlockSmoother(blocks): jacobi * x, Smooth, SmoothBack (NavierStokesSIMPLE_iterative.py:373-383)."""
+    from oracle import krylov_oracle as ko
+    c = cases("chan3d")
+    A = nsb.SparseMatrix.from_scipy(c.A)
+    sm = A.CreateBlockSmoother(_blocks_of(c), pattern=c.A)
+    assert len(sm.color_ptr) - 1 >= 2                      # neighbouring blocks are coupled: more than one colour
+    ref = ko.BlockSmoother(c.A, sm.blocks)
+    rng = np.random.default_rng(8)
+    x = rng.uniform(-1, 1, c.n_u)
+    np.testing.assert_allclose((sm * x).NumPy(), ref.jacobi(x), rtol=0, atol=1e-12 * np.abs(ref.jacobi(x)).max())
+    y, yr = np.zeros(c.n_u), np.zeros(c.n_u)
+    sm.Smooth(y, x)
+    ref.smooth(yr, x)
+    np.testing.assert_allclose(y, yr, rtol=0, atol=1e-12 * np.abs(yr).max())
+    sm.SmoothBack(y, x)
+    ref.smooth(yr, x, backward=True)
+    np.testing.assert_allclose(y, yr, rtol=0, atol=1e-12 * np.abs(yr).max())
+    gs = A.CreateBlockSmoother(sm.blocks, pattern=c.A, gauss_seidel=True)
+    refg = ko.BlockSmoother(c.A, gs.blocks)
+    np.testing.assert_allclose((gs * x).NumPy(), refg.symmetric_gs(x), rtol=0, atol=1e-12 * np.abs(yr).max())
+    # additive-only smoother without a pattern; overlapping blocks are refused
+    add = nsb.BlockSmoother(A, _blocks_of(c))
+    np.testing.assert_allclose((add * x).NumPy(), ref.jacobi(x), rtol=0, atol=1e-12 * np.abs(ref.jacobi(x)).max())
+    with pytest.raises(ValueError):
+        nsb.BlockSmoother(A, [[1, 2], [2, 3]], pattern=c.A)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gauss_seidel", [False, True])
+def test_bpcg_with_block_smoother_preconditioner(nsb, cases, gauss_seidel):
+    """BramblePasciakCG with MypreA's smoother part as preA (NavierStokesSIMPLE_iterative.py:364-397) vs the oracle."""
+    from oracle import krylov_oracle as ko
+    c = cases("chan2d")
+    A, B = nsb.SparseMatrix.from_scipy(c.A), nsb.SparseMatrix.from_scipy(c.B)
+    pre = A.CreateBlockSmoother(_blocks_of(c, 4), pattern=c.A, gauss_seidel=gauss_seidel)
+    ref = ko.BlockSmoother(c.A, pre.blocks)
+    pre_ref = ref.symmetric_gs if gauss_seidel else ref.jacobi
+    pM = nsb.DiagonalPreconditioner.from_diagonal(c.dM)
+    lam = min(nsb.EigenValues_Preconditioner(A, pre, tol=1e-9, maxsteps=2000))
+    ritz = ko.lanczos_eigs(c.A, pre_ref, c.n_u, maxsteps=2000, tol=1e-9)
+    assert abs(lam - ritz[0]) < 1e-6 * ritz[0]
+    lam *= 0.95
+    sol_ref = c.start()
+    _, h_ref, info = ko.bramble_pasciak_cg_v2(c.A, c.B, c.f, c.g, pre_ref, c.dM, sol=sol_ref, tol=1e-10, maxsteps=20000,
+                                              initialize=False, lam_min=lam, BT=c.BT)
+    sol = c.start()
+    ret = quiet(nsb.BramblePasciakCG, A, B, None, c.f, c.g, pre, pM, sol, tol=1e-10, maxsteps=20000, initialize=False,
+                lam_min=lam)
+    assert abs(ret[0][0] - info["it"]) <= 1
+    h = nsb.solvers.last_info["history"]
+    m = min(50, len(h), len(h_ref))
+    np.testing.assert_allclose(h[:m], np.array(h_ref[:m]), rtol=HIST_RTOL)
+    assert relerr(sol, sol_ref) < 1e-7
+    # the same smoother preconditions plain CG on A restricted to the free dofs
+    rhs = c.A @ (c.free_u * np.random.default_rng(2).uniform(-1, 1, c.n_u)) * c.free_u
+    u, errs = nsb.CGSolve(A, rhs, pre, None, 1e-10, 2000)
+    ur, er, _ = ko.pcg(c.A, rhs, pre=pre_ref, tol=1e-10, maxsteps=2000)
+    assert abs(len(errs) - len(er)) <= 1
+    assert relerr(np.asarray(u), ur) < 1e-7
