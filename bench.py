@@ -28,6 +28,8 @@ sys.path.insert(0, ROOT)
 #   B4 velocity r8 w4 = 12 n_u, pressure r6 w3 = 9 n_p ; B5 r2 w1 = 3 n_u + 3 n_p
 BPCG_VEC_PASSES_U = 24
 BPCG_VEC_PASSES_P = 13
+# MINRES iteration beyond the SpMV's own x/y: re-read z (1) + K2 r4 w2 (6) + K3 r4 w2 (6) = 13 passes of N
+MINRES_VEC_PASSES = 13
 WORKLOAD = ("3D Stokes channel [0,2.5]x[0,0.41]^2 (NavierStokesSIMPLE_test_3D.py), Taylor-Hood P2/P1, "
             "BramblePasciakCG (bramblepasciak_new.py) with Jacobi preA/preM, %d iterations per step")
 
@@ -175,6 +177,8 @@ def main():
     ap.add_argument("--iters", type=int, default=100, help="Krylov iterations per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--lanczos-steps", type=int, default=1500)
+    ap.add_argument("--no-minres", action="store_true")
+    ap.add_argument("--minres-iters", type=int, default=60)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -320,6 +324,30 @@ def main():
     iter_bytes = bpcg_iter_bytes(n_u, n_p, nnzA, nnzB)
     iter_gbs = iter_bytes * (its / loop) / 1e9 / world if loop > 0 else None
 
+    # ---- MINRES on the merged saddle-point operator K = [[A, B^T], [B, 0]] (minres.py; BASELINE metric names both)
+    minres_info = None
+    if world == 1 and not args.no_minres:
+        Kb = nsb.BlockMatrix([[A, BTm], [B, None]]).saddle()
+        pK = nsb.BlockMatrix([[pA, None], [None, pM]]).blockdiag_preconditioner()
+        rhs_d = torch.cat([f_d, g_d])
+        mh = np.zeros(args.minres_iters + 2)
+        best = None
+        for rep in range(3):
+            msol = u_start.clone()
+            its_m, secs_m, st_m = C.c_int(), C.c_double(), C.c_int()
+            pr, _, _ = nsb.la.buffer_of(rhs_d)
+            pz, _, _ = nsb.la.buffer_of(msol)
+            _lib.check(lib.nsb_minres(ctx.h, Kb.h, pK.h, pr, pz, args.minres_iters, 0.0, 0, mh.ctypes.data, C.byref(its_m),
+                                      C.byref(secs_m), C.byref(st_m)), "nsb_minres")
+            if rep > 0 and (best is None or secs_m.value < best):
+                best = secs_m.value
+        Nk = n_u + n_p
+        mbytes = spmv_bytes(Nk, Nk, nnzA + 2 * nnzB) + 8 * MINRES_VEC_PASSES * Nk
+        mrate = its_m.value / best
+        minres_info = {"iterations_per_s": mrate, "iterations": its_m.value, "algorithmic_bytes_per_iteration": mbytes,
+                       "achieved_gbs": mbytes * mrate / 1e9, "frac_of_measured_peak": mbytes * mrate / 1e9 / peak,
+                       "spmv_K_ms": Kb.spmv_bench(warmup=5, reps=20), "spmv_K_format": Kb.format()}
+        del Kb
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -344,6 +372,8 @@ def main():
                 "history_matches_device_leg": bool(same)},
         "gpu_launches": int(launches), "clocks": clocks,
     }
+    if minres_info:
+        line["minres"] = minres_info
     if not args.no_cpu_baseline and world == 1:
         v, info = cpu_oracle_rate(args.dofs, 20)
         line["cpu_baseline"] = {"value": v, "unit": "iterations/s", "cores": info["threads"], "kind": "port",
