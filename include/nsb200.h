@@ -97,6 +97,10 @@ NSB_API int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz);
  * of consecutive columns (8 B per run instead of 4 B per column). */
 NSB_API int nsb_mat_format(nsb_mat m, int* rows_per_chunk, int* chunks, int* max_distinct, int64_t* total_distinct,
                            int* lanes_per_row, int64_t* stored_nnz, int64_t* column_runs);
+/* Row panels: rows [bounds[k], bounds[k+1]) get their own SELL-LX shape (chunk size, lanes per row).  For operators whose
+ * row blocks differ strongly in length, e.g. the stacked local rows [[A, B^T], [B, 0]] of a row-partitioned saddle-point
+ * operator (nsb_saddle_create does this by itself).  Rebuilds the SpMV storage. */
+NSB_API int nsb_mat_set_row_panels(nsb_ctx ctx, nsb_mat m, int nbounds, const int64_t* bounds);
 /* main diagonal of a square (or owned-square) operator, length rows */
 NSB_API int nsb_mat_diagonal(nsb_ctx ctx, nsb_mat m, double* out);
 /* y = M x   (the `mat * vec` primitive, e.g. minres.py:97).  x has `cols`, y has `rows` entries. */

@@ -36,6 +36,7 @@ SIGNATURES = {
     "nsb_mat_destroy": (C.c_int, [c_mat]),
     "nsb_mat_info": (C.c_int, [c_mat, P(C.c_int64), P(C.c_int64), P(C.c_int64)]),
     "nsb_mat_format": (C.c_int, [c_mat, P(C.c_int), P(C.c_int), P(C.c_int), P(C.c_int64), P(C.c_int), P(C.c_int64), P(C.c_int64)]),
+    "nsb_mat_set_row_panels": (C.c_int, [c_ctx, c_mat, C.c_int, C.c_void_p]),
     "nsb_mat_diagonal": (C.c_int, [c_ctx, c_mat, C.c_void_p]),
     "nsb_spmv": (C.c_int, [c_ctx, c_mat, C.c_void_p, C.c_void_p]),
     "nsb_spmv_bench": (C.c_int, [c_ctx, c_mat, C.c_int, C.c_int, P(C.c_double)]),

@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -78,6 +79,7 @@ struct Context {
     bool use_graphs = true;
     // reduction scratch: per-block partials and the arrival ticket of the last-block pattern
     double* partials = nullptr;  // kMaxRed * max grid
+    double* chain = nullptr;     // kMaxRed: totals handed from one row panel's launch to the next (spmv.cuh: ChainOp)
     unsigned int* ticket = nullptr;
     int max_grid = 0;
     // pinned host mailbox for scalar read-back
@@ -140,6 +142,22 @@ struct DevBuf {
     }
 };
 
+// SELL-LX storage of one row panel [row0, row0 + nrows) of an operator (sell.cu, spmv.cuh)
+struct SellData {
+    int64_t row0 = 0, nrows = 0;
+    int sell_R = 0, sell_log2R = 0, sell_T = 1, sell_nchunks = 0, sell_max_uniq = 0, sell_cap = 0;
+    int64_t sell_total_uniq = 0, sell_stored = 0;   // distinct-column list length; stored (padded) nonzeros
+    nsb::DevBuf<double> sell_vals;            // pair-blocks of 32 x 2 values
+    nsb::DevBuf<unsigned short> sell_lcol;    // same layout: index into the chunk's distinct-column list
+    nsb::DevBuf<unsigned int> sell_off;       // per slice (+1), in pair-blocks
+    nsb::DevBuf<unsigned short> sell_perm;    // nchunks * R: sorted position -> row inside the chunk
+    nsb::DevBuf<int32_t> sell_uptr;           // nchunks + 1
+    nsb::DevBuf<int32_t> sell_ucol;           // distinct columns, chunk by chunk, ascending
+    // the same lists as runs of consecutive columns (used when the mean run is >= 8): first column, position
+    int sell_nruns = 0;
+    nsb::DevBuf<int32_t> sell_rstart, sell_rpos, sell_rptr;   // nruns, nruns + 1, nchunks + 1
+};
+
 }  // namespace nsb
 
 // ---------------------------------------------------------------------------------------------
@@ -168,18 +186,11 @@ struct nsb_mat_s {
     nsb::DevBuf<int32_t> colidx;  // nnz
     nsb::DevBuf<double> values;   // nnz
     int threads_per_row = 8;      // sub-warp width of the CSR-vector kernel, chosen from nnz/rows
-    // SELL-LX companion (sell.cu); sell_R == 0 when absent (small or too scattered operators)
-    int sell_R = 0, sell_log2R = 0, sell_T = 1, sell_nchunks = 0, sell_max_uniq = 0, sell_cap = 0;
-    int64_t sell_total_uniq = 0, sell_stored = 0;   // distinct-column list length; stored (padded) nonzeros
-    nsb::DevBuf<double> sell_vals;            // pair-blocks of 32 x 2 values
-    nsb::DevBuf<unsigned short> sell_lcol;    // same layout: index into the chunk's distinct-column list
-    nsb::DevBuf<unsigned int> sell_off;       // per slice (+1), in pair-blocks
-    nsb::DevBuf<unsigned short> sell_perm;    // nchunks * R: sorted position -> row inside the chunk
-    nsb::DevBuf<int32_t> sell_uptr;           // nchunks + 1
-    nsb::DevBuf<int32_t> sell_ucol;           // distinct columns, chunk by chunk, ascending
-    // the same lists as runs of consecutive columns (used when the mean run is >= 8): first column, position
-    int sell_nruns = 0;
-    nsb::DevBuf<int32_t> sell_rstart, sell_rpos, sell_rptr;   // nruns, nruns + 1, nchunks + 1
+    // SELL-LX companion (sell.cu): one SellData per row panel (a saddle-point operator has two: velocity rows
+    // [A B^T] and pressure rows [B 0], whose row lengths differ by a factor of five); empty when absent (small or
+    // too scattered operators: the CSR-vector kernel runs)
+    std::vector<std::unique_ptr<nsb::SellData>> panels;
+    std::vector<int64_t> panel_splits;   // row boundaries requested before build_sell (default: one panel)
     nsb_halo_s* halo = nullptr;   // not owned
     // saddle composition bookkeeping (rows of the velocity block; 0 for a plain matrix)
     int64_t n_u = 0, n_p = 0;

@@ -51,6 +51,8 @@ int ctx_init(Context& c, int device) {
     }
     c.max_grid = c.num_sms * 8 > kMaxBlocks ? c.num_sms * 8 : kMaxBlocks;
     NSB_CUDA(cudaMalloc((void**)&c.partials, sizeof(double) * kMaxRed * (size_t)c.max_grid));
+    NSB_CUDA(cudaMalloc((void**)&c.chain, sizeof(double) * kMaxRed));
+    NSB_CUDA(cudaMemset(c.chain, 0, sizeof(double) * kMaxRed));
     NSB_CUDA(cudaMalloc((void**)&c.ticket, sizeof(unsigned int)));
     NSB_CUDA(cudaMemset(c.ticket, 0, sizeof(unsigned int)));
     NSB_CUDA(cudaMallocHost((void**)&c.h_mail, sizeof(double) * 64));
@@ -117,6 +119,7 @@ int nsb_ctx_destroy(nsb_ctx ctx) {
     dist_destroy(c);
     if (c.partials) cudaFree(c.partials);
     if (c.ticket) cudaFree(c.ticket);
+    if (c.chain) cudaFree(c.chain);
     if (c.d_mail) cudaFree(c.d_mail);
     if (c.h_mail) cudaFreeHost(c.h_mail);
     if (c.stream) cudaStreamDestroy(c.stream);

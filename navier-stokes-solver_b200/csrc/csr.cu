@@ -286,6 +286,8 @@ int nsb_saddle_create(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_mat C, 
         }
     }
     delete bt_owned;
+    // two row panels: velocity rows [A B^T] (~36 nonzeros) and pressure rows [B C] (~190) get their own SELL-LX shapes
+    if (r == NSB_OK) K->panel_splits = {0, n_u, n_u + n_p};
     if (r == NSB_OK) r = build_sell(c, K);
     if (r != NSB_OK) {
         delete K;
@@ -313,14 +315,36 @@ int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz) {
 int nsb_mat_format(nsb_mat m, int* rows_per_chunk, int* chunks, int* max_distinct, int64_t* total_distinct,
                    int* lanes_per_row, int64_t* stored_nnz, int64_t* column_runs) {
     NSB_REQUIRE(m, "nsb_mat_format: NULL matrix");
-    if (rows_per_chunk) *rows_per_chunk = m->sell_R;
-    if (chunks) *chunks = m->sell_nchunks;
-    if (max_distinct) *max_distinct = m->sell_max_uniq;
-    if (total_distinct) *total_distinct = m->sell_total_uniq;
-    if (lanes_per_row) *lanes_per_row = m->sell_R > 0 ? m->sell_T : m->threads_per_row;
-    if (stored_nnz) *stored_nnz = m->sell_R > 0 ? m->sell_stored : m->nnz;
-    if (column_runs) *column_runs = m->sell_R > 0 ? m->sell_nruns : 0;
+    // aggregated over the row panels; rows_per_chunk / lanes_per_row describe the first (largest) panel
+    const bool sell = !m->panels.empty();
+    int chunks_ = 0, maxd = 0;
+    int64_t tot = 0, stored = 0, runs = 0;
+    for (const auto& P : m->panels) {
+        chunks_ += P->sell_nchunks;
+        if (P->sell_max_uniq > maxd) maxd = P->sell_max_uniq;
+        tot += P->sell_total_uniq;
+        stored += P->sell_stored;
+        runs += P->sell_nruns;
+    }
+    if (rows_per_chunk) *rows_per_chunk = sell ? m->panels[0]->sell_R : 0;
+    if (chunks) *chunks = chunks_;
+    if (max_distinct) *max_distinct = maxd;
+    if (total_distinct) *total_distinct = tot;
+    if (lanes_per_row) *lanes_per_row = sell ? m->panels[0]->sell_T : m->threads_per_row;
+    if (stored_nnz) *stored_nnz = sell ? stored : m->nnz;
+    if (column_runs) *column_runs = sell ? runs : 0;
     return NSB_OK;
+}
+
+int nsb_mat_set_row_panels(nsb_ctx ctx, nsb_mat m, int nbounds, const int64_t* bounds) {
+    NSB_REQUIRE(ctx && m && bounds && nbounds >= 2, "nsb_mat_set_row_panels: bad argument");
+    NSB_REQUIRE(bounds[0] == 0 && bounds[nbounds - 1] == m->rows, "nsb_mat_set_row_panels: bounds must run from 0 to rows");
+    for (int k = 1; k < nbounds; ++k) NSB_REQUIRE(bounds[k] >= bounds[k - 1], "nsb_mat_set_row_panels: bounds must ascend");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    m->panel_splits.assign(bounds, bounds + nbounds);
+    return build_sell(c, m);
 }
 
 int nsb_mat_diagonal(nsb_ctx ctx, nsb_mat m, double* out) {

@@ -26,7 +26,7 @@
 namespace nsb {
 
 // ---- chunk-local column numbering ----------------------------------------------------------------
-__global__ void k_sell_keys(CsrView A, int log2R, long long* __restrict__ keys, int* __restrict__ pos) {
+__global__ void k_sell_keys(CsrView A, int pbase, int log2R, long long* __restrict__ keys, int* __restrict__ pos) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -34,8 +34,8 @@ __global__ void k_sell_keys(CsrView A, int log2R, long long* __restrict__ keys, 
         const int p0 = A.rowptr[r], p1 = A.rowptr[r + 1];
         const long long hi = (long long)(r >> log2R) << 32;
         for (int p = p0 + lane; p < p1; p += 32) {
-            keys[p] = hi | (long long)A.colidx[p];
-            pos[p] = p;
+            keys[p - pbase] = hi | (long long)A.colidx[p];
+            pos[p - pbase] = p - pbase;
         }
     }
 }
@@ -140,7 +140,7 @@ __global__ void k_sell_slices(const unsigned long long* __restrict__ keys, int64
 }
 
 // one warp per sorted row position: copy the row's entries to their lanes' slots
-__global__ void k_sell_fill(CsrView A, const unsigned short* __restrict__ lcol_csr, int log2R, int64_t nvr, int rps, int T,
+__global__ void k_sell_fill(CsrView A, int pbase, const unsigned short* __restrict__ lcol_csr, int log2R, int64_t nvr, int rps, int T,
                             const unsigned short* __restrict__ perm, const unsigned int* __restrict__ off,
                             double* __restrict__ vals, unsigned short* __restrict__ lcol) {
     const int lane = threadIdx.x & 31;
@@ -156,7 +156,7 @@ __global__ void k_sell_fill(CsrView A, const unsigned short* __restrict__ lcol_c
             const int pair = e >> 1;
             const int64_t dst = base + (int64_t)(pair / T) * 64 + (ris * T + pair % T) * 2 + (e & 1);
             vals[dst] = A.values[p0 + e];
-            lcol[dst] = lcol_csr[p0 + e];
+            lcol[dst] = lcol_csr[p0 + e - pbase];
         }
     }
 }
@@ -182,15 +182,21 @@ static int pick_lanes_per_row(double mean) {
     return 32;
 }
 
-// Try to build the SELL-LX companion of m.  Leaves m->sell_R == 0 when the operator does not qualify.
-int build_sell(Context& c, nsb_mat_s* m) {
-    m->sell_R = 0;
-    const char* env = getenv("NSB_SELL");
-    if (env && atoi(env) == 0) return NSB_OK;
-    const int64_t nnz = m->nnz, rows = m->rows;
-    const int64_t min_nnz = getenv("NSB_SELL_MIN_NNZ") ? atoll(getenv("NSB_SELL_MIN_NNZ")) : 200000;
+// Try to build the SELL-LX storage of the row panel [row0, row0 + rows) of m into S.  Leaves S.sell_R == 0 when the
+// panel does not qualify.
+static int build_sell_panel(Context& c, nsb_mat_s* m, int64_t row0, int64_t rows, SellData& S_) {
+    SellData* ms = &S_;
+    ms->sell_R = 0;
+    ms->row0 = row0;
+    ms->nrows = rows;
     const bool debug = getenv("NSB_SELL_DEBUG") != nullptr;
-    if (nnz < min_nnz || rows < 1 || nnz < 1) return NSB_OK;
+    if (rows < 1) return NSB_OK;
+    int pends[2] = {0, 0};
+    NSB_CUDA(cudaMemcpy(&pends[0], m->rowptr.p + row0, sizeof(int), cudaMemcpyDeviceToHost));
+    NSB_CUDA(cudaMemcpy(&pends[1], m->rowptr.p + row0 + rows, sizeof(int), cudaMemcpyDeviceToHost));
+    const int pbase = pends[0];
+    const int64_t nnz = (int64_t)pends[1] - pends[0];
+    if (nnz < 1) return NSB_OK;
     const double mean = (double)nnz / (double)rows;
     const int T = pick_lanes_per_row(mean);
     const int rps = 32 / T;
@@ -201,7 +207,7 @@ int build_sell(Context& c, nsb_mat_s* m) {
     if (envR) log2R = atoi(envR);
     if (log2R > 11) log2R = 11;
     if (log2R < minlog) log2R = minlog;
-    CsrView A = view_of(m);
+    CsrView A{rows, m->rowptr.p + row0, m->colidx.p, m->values.p};   // the panel's rows; positions stay absolute
     const int vg = vec_grid(nnz, c.num_sms);
     const int64_t stage_cap = getenv("NSB_SELL_STAGE") ? atoll(getenv("NSB_SELL_STAGE")) : kSellStage;
     const int64_t stage_max = stage_cap > kSellStageMax ? stage_cap : kSellStageMax;
@@ -230,7 +236,7 @@ int build_sell(Context& c, nsb_mat_s* m) {
             nchunks = (int)((rows + R - 1) / R);
             const int end_bit = 32 + ilog2(nchunks) + 1;
             const int64_t kg = (rows + 7) / 8 < (int64_t)c.num_sms * 8 ? (rows + 7) / 8 : (int64_t)c.num_sms * 8;
-            k_sell_keys<<<(int)kg, kBlock, 0, c.stream>>>(A, log2R, k0.p, p0.p);
+            k_sell_keys<<<(int)kg, kBlock, 0, c.stream>>>(A, pbase, log2R, k0.p, p0.p);
             NSB_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, sort_bytes, k0.p, k1.p, p0.p, p1.p, (int)nnz, 0,
                                                      end_bit < 64 ? end_bit : 64, c.stream));
             k_sell_heads<<<vg, kBlock, 0, c.stream>>>(k1.p, head.p, nnz);
@@ -252,12 +258,12 @@ int build_sell(Context& c, nsb_mat_s* m) {
             const bool small = log2R <= ilog2((int64_t)rps * kSellWarps * 2);
             if (h[0] + R > (small ? stage_max : stage_cap)) continue;
             NSB_CHECK(lcol_csr.alloc(nnz));
-            NSB_CHECK(m->sell_ucol.alloc(h[1] > 0 ? h[1] : 1));
-            k_sell_localcols<<<vg, kBlock, 0, c.stream>>>(k1.p, p1.p, head.p, gidx.p, uptr.p, lcol_csr.p, m->sell_ucol.p, nnz);
+            NSB_CHECK(ms->sell_ucol.alloc(h[1] > 0 ? h[1] : 1));
+            k_sell_localcols<<<vg, kBlock, 0, c.stream>>>(k1.p, p1.p, head.p, gidx.p, uptr.p, lcol_csr.p, ms->sell_ucol.p, nnz);
             NSB_CUDA(cudaStreamSynchronize(c.stream));
-            m->sell_uptr.release();
-            m->sell_uptr.p = uptr.p;   // adopt
-            m->sell_uptr.n = uptr.n;
+            ms->sell_uptr.release();
+            ms->sell_uptr.p = uptr.p;   // adopt
+            ms->sell_uptr.n = uptr.n;
             uptr.p = nullptr;
             max_uniq = h[0];
             total_uniq = h[1];
@@ -266,11 +272,11 @@ int build_sell(Context& c, nsb_mat_s* m) {
         }
     }
     if (!found) {
-        m->sell_ucol.release();
+        ms->sell_ucol.release();
         return NSB_OK;
     }
     // ---- runs of consecutive distinct columns
-    m->sell_nruns = 0;
+    ms->sell_nruns = 0;
     if (total_uniq > 0 && !(getenv("NSB_SELL_RUNS") && atoi(getenv("NSB_SELL_RUNS")) == 0)) {
         DevBuf<int> flag, ridx;
         DevBuf<char> stmp;
@@ -281,22 +287,22 @@ int build_sell(Context& c, nsb_mat_s* m) {
         NSB_CHECK(stmp.alloc((int64_t)sb + 16));
         const int ug = vec_grid(total_uniq, c.num_sms);
         NSB_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int) * (size_t)total_uniq, c.stream));
-        k_sell_chunkflags<<<(nchunks + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(m->sell_uptr.p, nchunks, total_uniq, flag.p);
-        k_sell_runheads<<<ug, kBlock, 0, c.stream>>>(m->sell_ucol.p, total_uniq, flag.p);
+        k_sell_chunkflags<<<(nchunks + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(ms->sell_uptr.p, nchunks, total_uniq, flag.p);
+        k_sell_runheads<<<ug, kBlock, 0, c.stream>>>(ms->sell_ucol.p, total_uniq, flag.p);
         NSB_CUDA(cub::DeviceScan::InclusiveSum(stmp.p, sb, flag.p, ridx.p, total_uniq, c.stream));
         int nruns = 0;
         NSB_CUDA(cudaMemcpyAsync(&nruns, ridx.p + (total_uniq - 1), sizeof(int), cudaMemcpyDeviceToHost, c.stream));
         NSB_CUDA(cudaStreamSynchronize(c.stream));
         if (debug) fprintf(stderr, "[sell] %d runs for %d distinct columns (mean run %.1f)\n", nruns, total_uniq, (double)total_uniq / nruns);
         if ((int64_t)nruns * 8 <= (int64_t)total_uniq) {   // mean run >= 8 columns: descriptors beat the list
-            NSB_CHECK(m->sell_rstart.alloc(nruns));
-            NSB_CHECK(m->sell_rpos.alloc(nruns + 1));
-            NSB_CHECK(m->sell_rptr.alloc(nchunks + 1));
-            k_sell_runfill<<<ug, kBlock, 0, c.stream>>>(m->sell_ucol.p, flag.p, ridx.p, total_uniq, m->sell_rstart.p, m->sell_rpos.p);
-            k_sell_runptr<<<(nchunks + 1 + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(m->sell_uptr.p, ridx.p, nchunks, total_uniq,
-                                                                                         nruns, m->sell_rptr.p, m->sell_rpos.p);
+            NSB_CHECK(ms->sell_rstart.alloc(nruns));
+            NSB_CHECK(ms->sell_rpos.alloc(nruns + 1));
+            NSB_CHECK(ms->sell_rptr.alloc(nchunks + 1));
+            k_sell_runfill<<<ug, kBlock, 0, c.stream>>>(ms->sell_ucol.p, flag.p, ridx.p, total_uniq, ms->sell_rstart.p, ms->sell_rpos.p);
+            k_sell_runptr<<<(nchunks + 1 + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(ms->sell_uptr.p, ridx.p, nchunks, total_uniq,
+                                                                                         nruns, ms->sell_rptr.p, ms->sell_rpos.p);
             NSB_CUDA(cudaStreamSynchronize(c.stream));
-            m->sell_nruns = nruns;
+            ms->sell_nruns = nruns;
         }
     }
     const int64_t R = 1LL << log2R;
@@ -310,52 +316,79 @@ int build_sell(Context& c, nsb_mat_s* m) {
     NSB_CHECK(rk0.alloc(nvr));
     NSB_CHECK(rk1.alloc(nvr));
     NSB_CHECK(npb.alloc(nslices + 1));
-    NSB_CHECK(m->sell_perm.alloc(nvr));
-    NSB_CHECK(m->sell_off.alloc(nslices + 1));
+    NSB_CHECK(ms->sell_perm.alloc(nvr));
+    NSB_CHECK(ms->sell_off.alloc(nslices + 1));
     size_t sort_bytes = 0, scan_bytes = 0;
     cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, rk0.p, rk1.p, (int)nvr, 0, 64, c.stream);
-    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, npb.p, m->sell_off.p, (int)(nslices + 1), c.stream);
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, npb.p, ms->sell_off.p, (int)(nslices + 1), c.stream);
     NSB_CHECK(tmp.alloc((int64_t)(sort_bytes > scan_bytes ? sort_bytes : scan_bytes) + 16));
     const int rg = vec_grid(nvr, c.num_sms);
     k_sell_rowkeys<<<rg, kBlock, 0, c.stream>>>(A, log2R, nvr, rk0.p);
     const int end_bit = 40 + ilog2(nchunks) + 1;
     NSB_CUDA(cub::DeviceRadixSort::SortKeys(tmp.p, sort_bytes, rk0.p, rk1.p, (int)nvr, 0, end_bit < 64 ? end_bit : 64, c.stream));
     NSB_CUDA(cudaMemsetAsync(npb.p, 0, sizeof(unsigned int) * (size_t)(nslices + 1), c.stream));
-    k_sell_slices<<<rg, kBlock, 0, c.stream>>>(rk1.p, nvr, rps, T, m->sell_perm.p, npb.p);
-    NSB_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, scan_bytes, npb.p, m->sell_off.p, (int)(nslices + 1), c.stream));
+    k_sell_slices<<<rg, kBlock, 0, c.stream>>>(rk1.p, nvr, rps, T, ms->sell_perm.p, npb.p);
+    NSB_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, scan_bytes, npb.p, ms->sell_off.p, (int)(nslices + 1), c.stream));
     unsigned int total_pb = 0;
-    NSB_CUDA(cudaMemcpyAsync(&total_pb, m->sell_off.p + nslices, sizeof(unsigned int), cudaMemcpyDeviceToHost, c.stream));
+    NSB_CUDA(cudaMemcpyAsync(&total_pb, ms->sell_off.p + nslices, sizeof(unsigned int), cudaMemcpyDeviceToHost, c.stream));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
     const int64_t stored = (int64_t)total_pb * 64;
     if (stored > 6 * nnz + 4096 || total_pb > 0x7FFFFFFFu / 2) {   // pathological padding: keep CSR-vector
         if (debug) fprintf(stderr, "[sell] rejected: stored=%lld for nnz=%lld\n", (long long)stored, (long long)nnz);
-        m->sell_perm.release();
-        m->sell_off.release();
-        m->sell_uptr.release();
-        m->sell_ucol.release();
+        ms->sell_perm.release();
+        ms->sell_off.release();
+        ms->sell_uptr.release();
+        ms->sell_ucol.release();
         return NSB_OK;
     }
-    NSB_CHECK(m->sell_vals.alloc(stored > 0 ? stored : 64));
-    NSB_CHECK(m->sell_lcol.alloc(stored > 0 ? stored : 64));
-    NSB_CUDA(cudaMemsetAsync(m->sell_vals.p, 0, sizeof(double) * (size_t)(stored > 0 ? stored : 64), c.stream));
-    NSB_CUDA(cudaMemsetAsync(m->sell_lcol.p, 0, sizeof(unsigned short) * (size_t)(stored > 0 ? stored : 64), c.stream));
+    NSB_CHECK(ms->sell_vals.alloc(stored > 0 ? stored : 64));
+    NSB_CHECK(ms->sell_lcol.alloc(stored > 0 ? stored : 64));
+    NSB_CUDA(cudaMemsetAsync(ms->sell_vals.p, 0, sizeof(double) * (size_t)(stored > 0 ? stored : 64), c.stream));
+    NSB_CUDA(cudaMemsetAsync(ms->sell_lcol.p, 0, sizeof(unsigned short) * (size_t)(stored > 0 ? stored : 64), c.stream));
     const int64_t fg = (nvr + 7) / 8 < (int64_t)c.num_sms * 8 ? (nvr + 7) / 8 : (int64_t)c.num_sms * 8;
-    k_sell_fill<<<(int)fg, kBlock, 0, c.stream>>>(A, lcol_csr.p, log2R, nvr, rps, T, m->sell_perm.p, m->sell_off.p,
-                                                 m->sell_vals.p, m->sell_lcol.p);
+    k_sell_fill<<<(int)fg, kBlock, 0, c.stream>>>(A, pbase, lcol_csr.p, log2R, nvr, rps, T, ms->sell_perm.p, ms->sell_off.p,
+                                                 ms->sell_vals.p, ms->sell_lcol.p);
     NSB_CUDA(cudaGetLastError());
     NSB_CUDA(cudaStreamSynchronize(c.stream));
-    m->sell_R = (int)R;
-    m->sell_log2R = log2R;
-    m->sell_T = T;
-    m->sell_nchunks = nchunks;
-    m->sell_max_uniq = max_uniq;
-    m->sell_cap = (max_uniq + 31) & ~31;
-    if (m->sell_cap < 32) m->sell_cap = 32;
-    m->sell_total_uniq = total_uniq;
-    m->sell_stored = stored;
+    ms->sell_R = (int)R;
+    ms->sell_log2R = log2R;
+    ms->sell_T = T;
+    ms->sell_nchunks = nchunks;
+    ms->sell_max_uniq = max_uniq;
+    ms->sell_cap = (max_uniq + 31) & ~31;
+    if (ms->sell_cap < 32) ms->sell_cap = 32;
+    ms->sell_total_uniq = total_uniq;
+    ms->sell_stored = stored;
     if (debug)
         fprintf(stderr, "[sell] built: R=%lld T=%d chunks=%d stored=%lld (%.2f%% padding) smem=%zu B\n", (long long)R, T, nchunks,
-                (long long)stored, 100.0 * (double)(stored - nnz) / (double)nnz, sell_smem_bytes(m));
+                (long long)stored, 100.0 * (double)(stored - nnz) / (double)nnz, sell_smem_bytes(ms));
+    return NSB_OK;
+}
+
+// Build the SELL-LX companion of m, one panel per entry of m->panel_splits (default: the whole matrix).  Leaves
+// m->panels empty when the operator is small or any panel does not qualify (the CSR-vector kernel then runs).
+int build_sell(Context& c, nsb_mat_s* m) {
+    m->panels.clear();
+    const char* env = getenv("NSB_SELL");
+    if (env && atoi(env) == 0) return NSB_OK;
+    const int64_t min_nnz = getenv("NSB_SELL_MIN_NNZ") ? atoll(getenv("NSB_SELL_MIN_NNZ")) : 200000;
+    if (m->nnz < min_nnz || m->rows < 1 || m->nnz < 1) return NSB_OK;
+    std::vector<int64_t> sp = m->panel_splits;
+    if (sp.size() < 2 || sp.front() != 0 || sp.back() != m->rows) sp = {0, m->rows};
+    for (size_t k = 0; k + 1 < sp.size(); ++k) {
+        if (sp[k + 1] <= sp[k]) continue;
+        std::unique_ptr<SellData> S(new SellData());
+        int r = build_sell_panel(c, m, sp[k], sp[k + 1] - sp[k], *S);
+        if (r != NSB_OK) {
+            m->panels.clear();
+            return r;
+        }
+        if (S->sell_R == 0) {   // a panel that does not fit sends the whole operator to the CSR-vector kernel
+            m->panels.clear();
+            return NSB_OK;
+        }
+        m->panels.push_back(std::move(S));
+    }
     return NSB_OK;
 }
 

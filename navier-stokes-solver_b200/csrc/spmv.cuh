@@ -148,7 +148,8 @@ constexpr int kSellMaxSmem = 160 * 1024;
 #endif
 
 struct SellView {
-    int64_t rows;
+    int64_t rows;   // rows of the panel
+    int64_t row0;   // first operator row of the panel
     int R, log2R, nchunks, nsl;   // rows per chunk, chunks, slices per chunk (R * T / 32)
     int cap;                      // staged x entries a chunk may need (max distinct columns, padded)
     const double* __restrict__ vals;
@@ -274,7 +275,7 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
         const int64_t r0 = (int64_t)chunk << S.log2R;
         for (int t = threadIdx.x; t < S.R; t += kSellBlock) {
             const int64_t r = r0 + t;
-            if (r < S.rows) op.row(r, sy[t], acc);
+            if (r < S.rows) op.row(S.row0 + r, sy[t], acc);
         }
     }
     if constexpr (NS > 0) {
@@ -284,19 +285,19 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
     }
 }
 
-inline SellView sell_view_of(const nsb_mat_s* m) {
-    return SellView{m->rows, m->sell_R, m->sell_log2R, m->sell_nchunks, m->sell_R * m->sell_T / 32, m->sell_cap,
+inline SellView sell_view_of(const SellData* m) {
+    return SellView{m->nrows, m->row0, m->sell_R, m->sell_log2R, m->sell_nchunks, m->sell_R * m->sell_T / 32, m->sell_cap,
                     m->sell_vals.p, m->sell_lcol.p, m->sell_off.p, m->sell_perm.p, m->sell_uptr.p, m->sell_ucol.p,
                     m->sell_nruns > 0 ? m->sell_rptr.p : nullptr, m->sell_rstart.p, m->sell_rpos.p};
 }
 
-inline size_t sell_smem_bytes(const nsb_mat_s* m) {
+inline size_t sell_smem_bytes(const SellData* m) {
     const int nsl = m->sell_R * m->sell_T / 32;
     return sizeof(double) * ((size_t)m->sell_cap + m->sell_R) + sizeof(unsigned int) * ((size_t)nsl + 2);
 }
 
 template <int T, int NS, class RowOp>
-int spmv_sell_launch_t(Context& c, const nsb_mat_s* m, const double* x, RowOp op) {
+int spmv_sell_launch_t(Context& c, const SellData* m, const double* x, RowOp op) {
     static bool attr_set = false;        // per instantiation
     static size_t cached_smem = ~(size_t)0;
     static int cached_bps = 0;
@@ -320,18 +321,54 @@ int spmv_sell_launch_t(Context& c, const nsb_mat_s* m, const double* x, RowOp op
     return NSB_OK;
 }
 
-// Launch with the matrix's sub-warp width.  x must cover cols (+ halo tail when partitioned).
+template <int NS, class RowOp>
+int spmv_sell_panel(Context& c, const SellData* m, const double* x, RowOp op) {
+    switch (m->sell_T) {
+        case 1: return spmv_sell_launch_t<1, NS, RowOp>(c, m, x, op);
+        case 2: return spmv_sell_launch_t<2, NS, RowOp>(c, m, x, op);
+        case 4: return spmv_sell_launch_t<4, NS, RowOp>(c, m, x, op);
+        case 8: return spmv_sell_launch_t<8, NS, RowOp>(c, m, x, op);
+        case 16: return spmv_sell_launch_t<16, NS, RowOp>(c, m, x, op);
+        default: return spmv_sell_launch_t<32, NS, RowOp>(c, m, x, op);
+    }
+}
+
+// Row panels run as consecutive launches.  The fused reductions of a multi-panel operator are chained: every
+// launch but the last parks its totals in c.chain, the last one adds them (fixed order) and runs the inner finish.
+template <class Inner, int NSA>
+struct ChainOp {
+    Inner in;
+    double* chain;
+    int first, last;
+    __device__ bool skip() const { return in.skip(); }
+    __device__ void row(int64_t r, double ax, double (&acc)[NSA]) const { in.row(r, ax, acc); }
+    __device__ void finish(const double (&tot)[NSA]) const {
+        double t[NSA];
+#pragma unroll
+        for (int k = 0; k < NSA; ++k) t[k] = first ? tot[k] : chain[k] + tot[k];
+        if (last) in.finish(t);
+        else {
+#pragma unroll
+            for (int k = 0; k < NSA; ++k) chain[k] = t[k];
+        }
+    }
+};
+
+// Launch with the matrix's storage.  x must cover cols (+ halo tail when partitioned).
 template <int NS, class RowOp>
 int spmv_launch(Context& c, const nsb_mat_s* m, const double* x, RowOp op) {
-    if (m->sell_R > 0) {
-        switch (m->sell_T) {
-            case 1: return spmv_sell_launch_t<1, NS, RowOp>(c, m, x, op);
-            case 2: return spmv_sell_launch_t<2, NS, RowOp>(c, m, x, op);
-            case 4: return spmv_sell_launch_t<4, NS, RowOp>(c, m, x, op);
-            case 8: return spmv_sell_launch_t<8, NS, RowOp>(c, m, x, op);
-            case 16: return spmv_sell_launch_t<16, NS, RowOp>(c, m, x, op);
-            default: return spmv_sell_launch_t<32, NS, RowOp>(c, m, x, op);
+    const size_t np = m->panels.size();
+    if (np == 1) return spmv_sell_panel<NS, RowOp>(c, m->panels[0].get(), x, op);
+    if (np > 1) {
+        for (size_t k = 0; k < np; ++k) {
+            if constexpr (NS > 0) {
+                NSB_CHECK((spmv_sell_panel<NS, ChainOp<RowOp, NS>>(c, m->panels[k].get(), x,
+                                                                   ChainOp<RowOp, NS>{op, c.chain, k == 0, k + 1 == np})));
+            } else {
+                NSB_CHECK((spmv_sell_panel<NS, RowOp>(c, m->panels[k].get(), x, op)));
+            }
         }
+        return NSB_OK;
     }
     CsrView A = view_of(m);
     const int grid = spmv_grid(m->rows, m->threads_per_row, c.num_sms);

@@ -336,6 +336,11 @@ class SparseMatrix(BaseMatrix):
         return dict(rows_per_chunk=a.value, chunks=b.value, max_distinct=c_.value, total_distinct=d.value,
                     lanes_per_row=t.value, stored_nnz=e.value, column_runs=f.value)
 
+    def set_row_panels(self, bounds):
+        """Give row ranges [bounds[k], bounds[k+1]) their own SpMV storage shape (stacked saddle-point rows)."""
+        b = np.ascontiguousarray(bounds, dtype=np.int64)
+        _lib.check(self.ctx._lib.nsb_mat_set_row_panels(self.ctx.h, self.h, len(b), b.ctypes.data), "nsb_mat_set_row_panels")
+
     def diagonal(self):
         out = np.empty(self.height)
         _lib.check(self.ctx._lib.nsb_mat_diagonal(self.ctx.h, self.h, out.ctypes.data), "nsb_mat_diagonal")

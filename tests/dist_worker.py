@@ -71,6 +71,7 @@ def main():
                                                 rank, world))
     hk = P.upload_halo(ctx, plan)
     K = nsb.SparseMatrix.from_csr(Kl, ctx)
+    K.set_row_panels([0, D.local.n_u, D.local.n_u + D.local.n_p])
     hk.attach(K)
     C = nsb.DiagonalPreconditioner.from_diagonal(torch.cat([D.dA, D.dM]), ctx)
     msol = D.u_start.clone()

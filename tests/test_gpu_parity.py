@@ -132,7 +132,7 @@ def test_spmv_sell_format_matches_scipy(nsb, cases, monkeypatch, log2r, runs):
     np.testing.assert_allclose((B * xu).NumPy(), c.B @ xu, rtol=0, atol=1e-12)
     np.testing.assert_allclose((BT * xp).NumPy(), c.BT @ xp, rtol=0, atol=1e-12)
     K = nsb.BlockMatrix([[A, BT], [B, None]])
-    assert K.saddle().format()["rows_per_chunk"] > 0
+    assert K.saddle().format()["rows_per_chunk"] > 0          # two row panels: [A B^T] rows and [B 0] rows
     yr = np.concatenate([c.A @ xu + c.BT @ xp, c.B @ xu])
     np.testing.assert_allclose((K * np.concatenate([xu, xp])).NumPy(), yr, rtol=0, atol=1e-12)
     # ragged: dense row, empty rows, wide column spread (forces small chunks or the CSR-vector fallback)
