@@ -13,6 +13,7 @@
 #include <math.h>
 
 #include "cond.cuh"
+#include "p2p.cuh"
 
 namespace nsb {
 
@@ -55,6 +56,17 @@ __device__ void bpcg_after_wd(BpcgState* S, double wdn, double* hist) {
     S->it = it + 1;
     S->wd = wdn;                           // :221
 }
+
+struct BpcgPost {   // scalar step run inside the peer-memory all-reduce kernel
+    BpcgState* S;
+    int which;
+    double* hist;
+    __device__ void operator()() const {
+        if (S->stop) return;
+        if (which == 0) bpcg_after_as(S, S->red[0], S->red[1]);
+        else bpcg_after_wd(S, S->red[2], hist);
+    }
+};
 
 __global__ void k_bpcg_scalar(BpcgState* S, int which, double* hist) {
     if (S->stop) return;
@@ -330,20 +342,22 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
             else NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
         } else {
             NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p}));
-            // tmp1 and tmp4 travel in the velocity halo
-            NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
+            // tmp1 and tmp4 travel in the velocity halo, in one exchange when A and B share the halo plan
+            if (A->halo == B->halo) NSB_CHECK(halo_exchange2(c, A->halo, tmp1.p, tmp4.p));
+            else NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
             NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
+            if (A->halo != B->halo) NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
         }
-        NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
+        if (K || general_pre) NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
         NSB_CHECK(spmv_launch<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, fused}));
-        if (!fused) {
+        if (!fused && !p2p_allreduce_then(c, &S->red[0], 2, BpcgPost{S, 0, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[0], 2));
             k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
             c.launches++;
         }
         k_bpcg_b4<<<vg, kBlock, 0, c.stream>>>(S, V, hist.p, c.partials, c.ticket, fused);
         c.launches++;
-        if (!fused) {
+        if (!fused && !p2p_allreduce_then(c, &S->red[2], 1, BpcgPost{S, 1, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[2], 1));
             k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;

@@ -10,6 +10,7 @@
 #include <algorithm>
 
 #include "cond.cuh"
+#include "p2p.cuh"
 
 namespace nsb {
 
@@ -38,6 +39,17 @@ __device__ void cg_after_wd(CgState* S, double wdn, double* hist, double* betas)
     if (!betas && err <= S->tol_abs) { S->stop = 1; S->status = NSB_CONVERGED; }
     else if (it + 1 >= S->maxsteps) { S->stop = 1; S->status = NSB_MAXSTEPS; }
 }
+
+struct CgPost {   // scalar step run inside the peer-memory all-reduce kernel
+    CgState* S;
+    int which;
+    double *hist, *alphas, *betas;
+    __device__ void operator()() const {
+        if (S->stop) return;
+        if (which == 0) cg_after_as(S, S->red[0], alphas);
+        else cg_after_wd(S, S->red[1], hist, betas);
+    }
+};
 
 __global__ void k_cg_scalar(CgState* S, int which, double* hist, double* alphas, double* betas) {
     if (S->stop) return;
@@ -159,7 +171,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
         NSB_CHECK(halo_exchange(c, A->halo, b.s.p));
         if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused})));
         else NSB_CHECK(spmv_launch<1>(c, A, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused}));
-        if (!fused) {
+        if (!fused && !p2p_allreduce_then(c, &S->red[0], 1, CgPost{S, 0, hist, alphas, betas})) {
             NSB_CHECK(allreduce_sum(c, &S->red[0], 1));
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist, alphas, betas);
             c.launches++;
@@ -171,7 +183,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
             NSB_CHECK(vec_dot(c, b.w.p, b.d.p, n, &S->red[1]));
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
             c.launches++;
-        } else if (!fused) {
+        } else if (!fused && !p2p_allreduce_then(c, &S->red[1], 1, CgPost{S, 1, hist, alphas, betas})) {
             NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
             c.launches++;

@@ -302,7 +302,8 @@ void p2p_reduce_destroy(Context& c);
 int p2p_allreduce(Context& c, double* dev, int count);
 int p2p_halo_init(Context& c, nsb_halo_s* h);                                 // collective; leaves h->p2p null on failure
 void p2p_halo_destroy(nsb_halo_s* h);
-int p2p_halo_exchange(Context& c, nsb_halo_s* h, double* x);
+int p2p_halo_exchange(Context& c, nsb_halo_s* h, double* x, double* x2 = nullptr);   // x2: a second vector in the same exchange
+int halo_exchange2(Context& c, nsb_halo_s* h, double* x1, double* x2);             // dist.cu
 int nccl_allgather_bytes(Context& c, const void* send_dev, void* recv_dev, size_t bytes_per_rank);   // dist.cu
 
 int build_sell(Context& c, nsb_mat_s* m);   // sell.cu

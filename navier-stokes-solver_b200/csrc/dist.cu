@@ -136,6 +136,13 @@ int halo_exchange(Context& c, nsb_halo_s* h, double* x) {
     return NSB_OK;
 }
 
+int halo_exchange2(Context& c, nsb_halo_s* h, double* x1, double* x2) {
+    if (!h || c.nranks <= 1) return NSB_OK;
+    if (h->p2p) return p2p_halo_exchange(c, h, x1, x2);
+    NSB_CHECK(halo_exchange(c, h, x1));
+    return halo_exchange(c, h, x2);
+}
+
 }  // namespace nsb
 
 nsb_halo_s::~nsb_halo_s() { nsb::p2p_halo_destroy(this); }

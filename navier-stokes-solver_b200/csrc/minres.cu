@@ -14,6 +14,7 @@
 // the exit iteration no-ops.  Exit logic reproduces minres.py:96,126,145-146 exactly.
 #include <math.h>
 
+#include "p2p.cuh"
 #include "spmv.cuh"
 
 namespace nsb {
@@ -76,6 +77,17 @@ __device__ void minres_after_gamma(MinresState* S, double sum, double* hist) {
         S->status = NSB_ABSTOL;
     }
 }
+
+struct MinresPost {   // scalar step run inside the peer-memory all-reduce kernel
+    MinresState* S;
+    int which;
+    double* hist;
+    __device__ void operator()() const {
+        if (S->stop) return;
+        if (which == 0) minres_after_delta(S, S->red[0]);
+        else minres_after_gamma(S, S->red[1], hist);
+    }
+};
 
 __global__ void k_minres_scalar(MinresState* S, int which, double* hist) {
     if (which == 0) {
@@ -276,14 +288,14 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
         double* z_new = z[(j + 1) % 2].p;
         NSB_CHECK(halo_exchange(c, K->halo, zc));
         NSB_CHECK(spmv_launch<1>(c, K, zc, MinresK1Op{S, t.p, zc, fused}));
-        if (!fused) {
+        if (!fused && !p2p_allreduce_then(c, &S->red[0], 1, MinresPost{S, 0, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[0], 1));
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
             c.launches++;
         }
         k_minres_k2<<<vg, kBlock, 0, c.stream>>>(S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, fused);
         c.launches++;
-        if (!fused) {
+        if (!fused && !p2p_allreduce_then(c, &S->red[1], 1, MinresPost{S, 1, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;

@@ -22,23 +22,9 @@
 
 #include <vector>
 
-#include "common.cuh"
+#include "p2p.cuh"
 
 namespace nsb {
-
-typedef unsigned long long u64;
-
-__device__ __forceinline__ void st_release_sys(u64* p, u64 v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ u64 ld_acquire_sys(const u64* p) {
-    u64 v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_sys_f64(double* p, double v) {
-    asm volatile("st.volatile.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
-}
 
 // ---- IPC helper: all ranks export one allocation and open everyone else's -------------------------------
 struct IpcBlock {
@@ -115,7 +101,6 @@ static int ipc_exchange(Context& c, size_t bytes, const std::vector<char>& want,
 }
 
 // ---- scalar all-reduce -------------------------------------------------------------------------------
-constexpr int kArSlots = 8;   // doubles per rank per reduction
 
 struct P2PReduce {
     IpcBlock blk;              // [ box: 2 x nranks x kArSlots doubles | flags: nranks u64 | seq u64 ]
@@ -126,29 +111,9 @@ struct P2PReduce {
     u64* seq = nullptr;
 };
 
-__global__ void k_p2p_allreduce(double* const* peer_box, u64* const* peer_flag, const double* my_box, const u64* my_flag,
-                                u64* seq, int me, int nranks, double* vals, int count) {
-    __shared__ double mine[kArSlots];
-    const u64 e = *seq + 1;
-    const int par = (int)(e & 1);
-    if (threadIdx.x < count) mine[threadIdx.x] = vals[threadIdx.x];
-    __syncthreads();
-    const int r = threadIdx.x;
-    if (r < nranks) {
-        double* dst = peer_box[r] + ((size_t)par * nranks + me) * kArSlots;
-        for (int k = 0; k < count; ++k) st_sys_f64(dst + k, mine[k]);
-        __threadfence_system();
-        st_release_sys(peer_flag[r] + me, e);
-        while (ld_acquire_sys(my_flag + r) < e) {
-        }
-    }
-    __syncthreads();
-    if (threadIdx.x < count) {
-        double s = 0.0;
-        for (int q = 0; q < nranks; ++q) s += __ldcv(my_box + ((size_t)par * nranks + q) * kArSlots + threadIdx.x);
-        vals[threadIdx.x] = s;
-    }
-    if (threadIdx.x == 0) *seq = e;
+P2PReduceView p2p_reduce_view(Context& c) {
+    P2PReduce* P = c.p2p;
+    return P2PReduceView{P->peer_box.p, P->peer_flag.p, P->my_box, P->my_flag, P->seq, c.rank, c.nranks};
 }
 
 int p2p_reduce_init(Context& c) {
@@ -197,11 +162,7 @@ void p2p_reduce_destroy(Context& c) {
 }
 
 int p2p_allreduce(Context& c, double* dev, int count) {
-    P2PReduce* P = c.p2p;
-    const int threads = ((c.nranks > count ? c.nranks : count) + 31) / 32 * 32;
-    k_p2p_allreduce<<<1, threads, 0, c.stream>>>(P->peer_box.p, P->peer_flag.p, P->my_box, P->my_flag, P->seq, c.rank, c.nranks,
-                                                 dev, count);
-    c.launches++;
+    p2p_allreduce_then(c, dev, count, NoPost{});
     NSB_CUDA(cudaGetLastError());
     return NSB_OK;
 }
@@ -216,6 +177,8 @@ struct HaloDev {
     u64* const* peer_ready;     // per neighbour: its ready flag for me
     u64* const* peer_consumed;  // per neighbour: its "neighbour consumed" word for me
     const double* my_land;
+    int64_t land2;              // offset (doubles) of the second vector's area in every landing buffer
+    const int64_t* peer_land2;  // per neighbour: the same offset in ITS landing buffer
     const u64* my_ready;        // written by the neighbours
     const u64* my_consumed;     // written by the neighbours
     u64* seq;
@@ -223,15 +186,16 @@ struct HaloDev {
 };
 
 struct P2PHalo {
-    IpcBlock blk;   // [ landing: n_halo doubles (padded) | ready: nnb u64 | consumed: nnb u64 | seq u64 | ticket u32 ]
+    IpcBlock blk;   // [ landing: 2 x n_halo doubles (padded; one area per vector of a dual exchange) | ready: nnb u64 | consumed: nnb u64 | seq u64 | ticket u32 ]
     DevBuf<int64_t> send_off;
     DevBuf<double*> peer_land;
     DevBuf<u64*> peer_ready, peer_consumed;
+    DevBuf<int64_t> peer_land2;
     HaloDev dev;
     int push_grid = 1, copy_grid = 1;
 };
 
-__global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* __restrict__ x) {
+__global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* __restrict__ x, const double* __restrict__ x2) {
     const u64 e = *H.seq + 1;
     // my previous landing buffer content has been moved out (stream order): tell the neighbours, then wait
     // until they have moved out what I pushed last time
@@ -244,7 +208,9 @@ __global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* _
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < H.n_send; i += (int64_t)gridDim.x * blockDim.x) {
         int k = 0;
         while (k + 1 < H.nnb && i >= H.send_off[k + 1]) ++k;
-        H.peer_land[k][i - H.send_off[k]] = x[H.send_idx[i]];
+        const int src = H.send_idx[i];
+        H.peer_land[k][i - H.send_off[k]] = x[src];
+        if (x2) H.peer_land[k][H.peer_land2[k] + i - H.send_off[k]] = x2[src];
     }
     __threadfence_system();
     __syncthreads();
@@ -261,7 +227,7 @@ __global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* _
     }
 }
 
-__global__ void __launch_bounds__(kBlock) k_halo_wait_copy(HaloDev H, double* __restrict__ tail) {
+__global__ void __launch_bounds__(kBlock) k_halo_wait_copy(HaloDev H, double* __restrict__ tail, double* __restrict__ tail2) {
     const u64 e = *H.seq;   // the push of this exchange is earlier in the stream
     if (threadIdx.x < H.nnb) {
         while (ld_acquire_sys(H.my_ready + threadIdx.x) < e) {
@@ -269,7 +235,10 @@ __global__ void __launch_bounds__(kBlock) k_halo_wait_copy(HaloDev H, double* __
     }
     __syncthreads();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < H.n_halo; i += (int64_t)gridDim.x * blockDim.x)
+    {
         tail[i] = __ldcv(H.my_land + i);
+        if (tail2) tail2[i] = __ldcv(H.my_land + H.land2 + i);
+    }
 }
 
 int p2p_halo_init(Context& c, nsb_halo_s* h) {
@@ -302,7 +271,7 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     auto tab = [&](int r) { return all.data() + (size_t)r * mine.size(); };
 
     P2PHalo* P = new P2PHalo();
-    const size_t bytes = sizeof(double) * (size_t)land + sizeof(u64) * (2 * (size_t)nnb + 1) + 16;
+    const size_t bytes = sizeof(double) * 2 * (size_t)land + sizeof(u64) * (2 * (size_t)nnb + 1) + 16;   // two vector areas
     std::vector<char> want(R, 0);
     for (int k = 0; k < nnb; ++k) want[h->neighbors[k]] = 1;
     bool ok = false;
@@ -313,7 +282,7 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     }
     std::vector<double*> pl(nnb > 0 ? nnb : 1, nullptr);
     std::vector<u64*> pr(nnb > 0 ? nnb : 1, nullptr), pc(nnb > 0 ? nnb : 1, nullptr);
-    std::vector<int64_t> so(nnb + 1, 0);
+    std::vector<int64_t> so(nnb + 1, 0), l2(nnb > 0 ? nnb : 1, 0);
     bool sym = true;
     for (int k = 0; k < nnb; ++k) {
         const int nb = h->neighbors[k];
@@ -325,7 +294,8 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
         }
         char* base = (char*)P->blk.peer[nb];
         pl[k] = (double*)base + off;
-        u64* flags = (u64*)(base + sizeof(double) * (size_t)T[0]);
+        u64* flags = (u64*)(base + sizeof(double) * 2 * (size_t)T[0]);
+        l2[k] = T[0];
         pr[k] = flags + slot;
         pc[k] = flags + T[1] + slot;
         so[k + 1] = so[k] + h->send_counts[k];
@@ -340,6 +310,7 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     if (rc == NSB_OK) rc = P->peer_land.alloc(nnb > 0 ? nnb : 1);
     if (rc == NSB_OK) rc = P->peer_ready.alloc(nnb > 0 ? nnb : 1);
     if (rc == NSB_OK) rc = P->peer_consumed.alloc(nnb > 0 ? nnb : 1);
+    if (rc == NSB_OK) rc = P->peer_land2.alloc(nnb > 0 ? nnb : 1);
     if (rc != NSB_OK) {
         ipc_release(P->blk);
         delete P;
@@ -349,8 +320,9 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     cudaMemcpy(P->peer_land.p, pl.data(), sizeof(double*) * pl.size(), cudaMemcpyHostToDevice);
     cudaMemcpy(P->peer_ready.p, pr.data(), sizeof(u64*) * pr.size(), cudaMemcpyHostToDevice);
     cudaMemcpy(P->peer_consumed.p, pc.data(), sizeof(u64*) * pc.size(), cudaMemcpyHostToDevice);
+    cudaMemcpy(P->peer_land2.p, l2.data(), sizeof(int64_t) * l2.size(), cudaMemcpyHostToDevice);
     char* lb = (char*)P->blk.local;
-    u64* flags = (u64*)(lb + sizeof(double) * (size_t)land);
+    u64* flags = (u64*)(lb + sizeof(double) * 2 * (size_t)land);
     HaloDev& D = P->dev;
     D.nnb = nnb;
     D.n_send = h->n_send;
@@ -361,6 +333,8 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     D.peer_ready = P->peer_ready.p;
     D.peer_consumed = P->peer_consumed.p;
     D.my_land = (const double*)lb;
+    D.land2 = land;
+    D.peer_land2 = P->peer_land2.p;
     D.my_ready = flags;
     D.my_consumed = flags + nnb;
     D.seq = flags + 2 * nnb;
@@ -390,11 +364,11 @@ void p2p_halo_destroy(nsb_halo_s* h) {
     h->p2p = nullptr;
 }
 
-int p2p_halo_exchange(Context& c, nsb_halo_s* h, double* x) {
+int p2p_halo_exchange(Context& c, nsb_halo_s* h, double* x, double* x2) {
     P2PHalo* P = h->p2p;
     if (P->dev.nnb == 0) return NSB_OK;
-    k_halo_push<<<P->push_grid, kBlock, 0, c.stream>>>(P->dev, x);
-    k_halo_wait_copy<<<P->copy_grid, kBlock, 0, c.stream>>>(P->dev, x + h->n_owned);
+    k_halo_push<<<P->push_grid, kBlock, 0, c.stream>>>(P->dev, x, x2);
+    k_halo_wait_copy<<<P->copy_grid, kBlock, 0, c.stream>>>(P->dev, x + h->n_owned, x2 ? x2 + h->n_owned : nullptr);
     c.launches += 2;
     NSB_CUDA(cudaGetLastError());
     return NSB_OK;
