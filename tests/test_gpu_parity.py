@@ -269,12 +269,18 @@ BPCG_CASES = [("bpcg_sq8", "sq8"), ("bpcg_chan2d", "chan2d"), ("bpcg_chan3d", "c
 @pytest.mark.parametrize("name,mesh", BPCG_CASES)
 def test_bpcg_v1_and_v2_match_reference_golden(nsb, dev, name, mesh):
     from oracle.cases import load_golden
-    slack = 8 if name.endswith("_floor") else 1      # see tests/test_oracle_golden.py
+    # bpcg_sq8 runs ~265 iterations to 1e-10 on a system whose recurrence decorrelates under rounding after ~100
+    # (tests/test_oracle_golden.py::test_bpcg_sq8_is_rounding_sensitive): the C oracle's count moves over 254..264 and
+    # its final iterate by up to 1.9e-7 with the OpenMP thread count alone, and the device moves the same way with
+    # the reduction grid.  Its first 50 residuals are held to 1e-10; count and iterate to that envelope.
+    # All other cases: +-1 and 1e3*tol.
+    loose = name == "bpcg_sq8"
+    slack = 8 if name.endswith("_floor") else (13 if loose else 1)
     c, A, B, pA, pM = dev(mesh)
     gold = load_golden(name)
     tol, maxsteps = gold["args"]
     lam = float(gold["lam_min"])
-    sol_rtol = max(SOL_RTOL, 1e3 * float(tol))
+    sol_rtol = max(SOL_RTOL, (5e3 if loose else 1e3) * float(tol))
     # v1  (stokes_hcurldiv.py:75-77)
     gfu, gfp = nsb.BaseVector(c.u0.copy()), nsb.BaseVector(np.zeros(c.n_p))
     solution = nsb.BlockVector([gfu, gfp])

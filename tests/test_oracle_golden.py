@@ -154,6 +154,23 @@ def test_pcg_oracle(cases):
     assert info["converged"] and np.linalg.norm(r) < 1e-9 * np.linalg.norm(b)
 
 
+def test_bpcg_sq8_is_rounding_sensitive(cases):
+    # Why bpcg_sq8's exit index and final iterate get a wider window wherever a different summation order is in play
+    # (C oracle, device): the reference's own loop, with the right-hand side moved by one ulp, keeps its first 50
+    # residuals to 1e-10 but has lost six digits of the history by iteration ~110 of 266.
+    c, gold = cases("sq8"), load_golden("bpcg_sq8")
+    tol, maxsteps = gold["args"]
+    f = c.f * (1 + 1e-16 * np.random.default_rng(0).standard_normal(c.f.shape))
+    _, e1, _ = ko.bramble_pasciak_cg_v1(c.A, c.B, None, c.dA, c.dM, f, c.g, solution=c.start(), tolerance=float(tol),
+                                        max_steps=int(maxsteps), lam_min=float(gold["lam_min"]), BT=c.BT)
+    ref = gold["errors_v1"]
+    np.testing.assert_allclose(e1[:50], ref[:50], rtol=HIST_RTOL)
+    m = min(len(e1), len(ref), 130)
+    dev = np.abs(np.array(e1[:m]) - ref[:m]) / ref[:m]
+    assert dev.max() > 1e-6
+    assert abs(len(e1) - len(ref)) <= 13
+
+
 # ---- C + OpenMP twin of the oracle (oracle/c/krylov_omp.c): the timed CPU baseline of bench.py -----------------
 # bpcg_sq8 is left to the numpy oracle: at 1e-10 it runs ~150 iterations past the point where rounding
 # decorrelates the recurrence (history differences reach 1e-2 by iteration 120 between any two summation
