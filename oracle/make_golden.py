@@ -100,6 +100,41 @@ def gold_bpcg(mesh, tol, maxsteps, tag=""):
     print(name, "v1 passes", len(errors1), "v2 it", it2, "hist", len(hist2), "lam_min", lam)
 
 
+def gold_bpcg_condensed(mesh, tol, maxsteps):
+    """solvers/bramblepasciak_new.py with blfA.condense = True (:8-21, :84-103) on the synthetic condensation of
+    oracle/cases.py: myAmatrix and harmonic_extension are the reference's own code, only the five operators are ours."""
+    from oracle.cases import synthetic_condensation
+    c = Case(mesh)
+    cd = synthetic_condensation(c.A, c.free_u)
+    dS = cd["mat"].diagonal()
+    g_ = c.free_u & ~cd["interior"] & (dS != 0)
+    dAc = np.where(g_, 1.0 / np.where(dS != 0, dS, 1.0), 0.0)
+    Sg = cd["mat"][g_][:, g_].toarray()
+    lam = 0.9 * float(np.linalg.eigvalsh(np.sqrt(dAc[g_])[:, None] * Sg * np.sqrt(dAc[g_])[None, :])[0])
+
+    class Blf:
+        pass
+    blfA, blfB = Blf(), Blf()
+    blfA.condense = True
+    blfA.mat = SparseMatrix(cd["mat"])
+    blfA.harmonic_extension = SparseMatrix(cd["H"])
+    blfA.harmonic_extension_trans = SparseMatrix(cd["HT"])
+    blfA.inner_solve = SparseMatrix(cd["inner_solve"])
+    blfA.inner_matrix = SparseMatrix(cd["inner_matrix"])
+    blfB.mat, blfB.condense = SparseMatrix(c.B), False
+    sol = BlockVector([BaseVector(c.u0.copy()), BaseVector(np.zeros(c.n_p))])
+    ngla.inject_eigenvalues([lam, 1.0])
+    (it, secs), out = quiet(ref_bpcg2.BramblePasciakCG, blfA, blfB, None, BaseVector(c.f.copy()), BaseVector(c.g.copy()),
+                            DiagonalMatrix(dAc), DiagonalMatrix(c.dM), sol, initialize=False, tol=tol,
+                            maxsteps=maxsteps, rel_err=True)
+    hist = [float(m.group(2)) for m in re.finditer(r"it =\s+(\d+)\s+err =\s+(\S+)", out)]
+    err0 = float(re.search(r"err0 (\S+)", out).group(1))
+    name = "bpcg_condensed_%s" % mesh
+    np.savez_compressed(os.path.join(GOLDEN_DIR, name), lam_min=lam, it_v2=it, hist_v2=np.array(hist), err0_v2=err0,
+                        sol_v2=sol.NumPy().copy(), dAc=dAc, fingerprint=c.fingerprint(), args=np.array([tol, maxsteps]))
+    print(name, "it", it, "hist", len(hist), "lam_min", lam)
+
+
 def gold_orth():
     rng = np.random.default_rng(7)
     n, m = 777, 5
@@ -146,5 +181,6 @@ if __name__ == "__main__":
     gold_bpcg("chan2d", tol=1e-10, maxsteps=10000)
     gold_bpcg("chan3d", tol=1e-10, maxsteps=100000)
     gold_bpcg("sq8", tol=1e-12, maxsteps=25, tag="_cap25")
+    gold_bpcg_condensed("chan2d", tol=1e-10, maxsteps=20000)
     gold_orth()
     gold_rk()

@@ -526,6 +526,32 @@ def test_bpcg_static_condensation_matches_oracle(nsb, cases, mesh):
         assert relerr(sol, sol_ref) < 5e-3
 
 
+@pytest.mark.gpu
+def test_bpcg_static_condensation_matches_reference_golden(nsb, cases):
+    """Device condensed BramblePasciakCG against the output of the reference's own condensed code
+    (tests/golden/bpcg_condensed_chan2d.npz, oracle/make_golden.py::gold_bpcg_condensed)."""
+    from oracle.cases import synthetic_condensation, load_golden
+    c, gold = cases("chan2d"), load_golden("bpcg_condensed_chan2d")
+    cd = synthetic_condensation(c.A, c.free_u)
+
+    class Blf:
+        condense = True
+    blf = Blf()
+    for k in ("mat", "H", "HT", "inner_solve", "inner_matrix"):
+        setattr(blf, {"H": "harmonic_extension", "HT": "harmonic_extension_trans"}.get(k, k), nsb.SparseMatrix.from_scipy(cd[k]))
+    pA, pM = nsb.DiagonalPreconditioner.from_diagonal(gold["dAc"]), nsb.DiagonalPreconditioner.from_diagonal(c.dM)
+    tol, maxsteps = gold["args"]
+    sol = c.start()
+    ret = quiet(nsb.BramblePasciakCG, blf, nsb.SparseMatrix.from_scipy(c.B), None, c.f, c.g, pA, pM, sol, tol=float(tol),
+                maxsteps=int(maxsteps), initialize=False, lam_min=float(gold["lam_min"]))
+    it = ret[0][0]
+    h = nsb.solvers.last_info["history"]
+    assert abs(it - int(gold["it_v2"])) <= 1
+    np.testing.assert_allclose(h[0], float(gold["err0_v2"]), rtol=1e-11)
+    np.testing.assert_allclose(h[:50], gold["hist_v2"][:50], rtol=HIST_RTOL)
+    assert relerr(sol, gold["sol_v2"]) < max(SOL_RTOL, 1e3 * float(tol))
+
+
 def _simple_case(mesh_cells=(12, 4), lengths=(2.0, 0.41), dt=1e-3, seed=5):
     """Synthetic operators with the shapes of NavierStokesSIMPLE_iterative.py:79-144: a, mstar = M + dt a, the mixed
     projection system [[-Ml, B^T], [B, 0]] condensed onto the pressure (diagonal mass Ml), bproj = [0; B], mapV a

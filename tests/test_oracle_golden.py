@@ -243,3 +243,22 @@ def test_condensed_operator_identity_and_oracle_path(cases):
                              lam_min=0.9 * c.lam_min(), BT=c.BT)
     assert ic["converged"]
     assert relerr(sol_c, sol_u) < 1e-6
+
+
+def test_condensed_oracle_matches_reference_golden(cases):
+    """tests/golden/bpcg_condensed_chan2d.npz is the output of the reference's own myAmatrix / harmonic_extension
+    code (bramblepasciak_new.py:8-21,84-103, run unmodified by oracle/make_golden.py::gold_bpcg_condensed)."""
+    from oracle.cases import synthetic_condensation
+    c, gold = cases("chan2d"), load_golden("bpcg_condensed_chan2d")
+    check_fingerprint(c, gold)
+    cd = synthetic_condensation(c.A, c.free_u)
+    cond = dict(H=cd["H"], HT=cd["HT"], inner_solve=cd["inner_solve"], inner_matrix=cd["inner_matrix"])
+    tol, maxsteps = gold["args"]
+    sol = c.start()
+    _, h, info = ko.bramble_pasciak_cg_v2(cd["mat"], c.B, c.f, c.g, gold["dAc"], c.dM, sol=sol, tol=float(tol),
+                                          maxsteps=int(maxsteps), initialize=False, lam_min=float(gold["lam_min"]),
+                                          BT=c.BT, cond=cond)
+    assert abs(info["it"] - int(gold["it_v2"])) <= 1
+    np.testing.assert_allclose(info["err0"], float(gold["err0_v2"]), rtol=1e-12)
+    np.testing.assert_allclose(h[:50], gold["hist_v2"][:50], rtol=HIST_RTOL)
+    assert relerr(sol, gold["sol_v2"]) < max(SOL_RTOL, 1e3 * float(tol))
