@@ -199,8 +199,8 @@ NSB_API int nsb_vec_axpby(nsb_ctx ctx, double* y, double a, const double* x, dou
 NSB_API int nsb_vec_gather_axpy(nsb_ctx ctx, double* y, double a, const double* x, const int32_t* idx, int64_t n);
 
 /* One pass of the time-loop body of heat.py:81-146 ("exponential integrator" in an m-dimensional subspace):
- * basis u, then m-1 implicit Euler sub-steps u -= dt H^-1 K u with dt = time_step/m (heat.py:95-98; H = M + dt K is
- * solved by Jacobi-CG in place of the direct heat.mat.Inverse of heat.py:72), orthonormalize (:100), projected
+ * basis u, then m-1 implicit Euler sub-steps u -= dt H^-1 K u with dt = time_step/m (heat.py:95-98; H, the caller's
+ * heat.mat = M + time_step K of heat.py:51-52, is solved by Jacobi-CG in place of the direct heat.mat.Inverse of heat.py:72), orthonormalize (:100), projected
  * m x m diffusion and mass matrices (:109-118), Gauss collocation step of the projected ODE on the host
  * (runge_kutta_method.py:26-59; rk_a is stages x stages row-major, rk_b has `stages` entries) and the lift back
  * (:140-142).  u (length rows; host or device) is replaced by the new temperature.  Khat_out / Mhat_out

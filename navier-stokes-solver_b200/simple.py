@@ -102,7 +102,7 @@ class SimpleStepper:
         temp = _t(self.a * self.gfu)
         axpby(temp, 0.0, temp, -1.0)                     # temp = -a.mat * gfu.vec
         if convection is not None:
-            axpby(temp, 1.0, convection(self.gfu))       # += conv_operator * gfu.vec
+            axpby(temp, 1.0, _t(convection(self.gfu)))       # += conv_operator * gfu.vec
         if self.f is not None:
             axpby(temp, 1.0, self.f)                     # += f.vec
         temp2 = _t(self.invmstar * temp)                 # :436

@@ -308,7 +308,7 @@ def heat_large_step(diffusion, mass, heat, pre_heat, temperature, time_step, wei
     """One pass of the time-loop body of heat.py:81-146 on the device: Krylov-like basis from m-1 implicit Euler
     sub-steps (:95-98), orthonormalize (:100), projected m x m matrices (:109-118), Gauss collocation step of the
     projected system (:135) and the lift (:140-142).  ``diffusion`` / ``mass`` / ``heat`` are device SparseMatrix
-    (diffusion.mat, mass.mat, heat.mat = M + dt K); the direct ``heat.mat.Inverse(freedofs)`` of heat.py:72 is
+    (diffusion.mat, mass.mat, heat.mat = M + time_step K, heat.py:51-52); the direct ``heat.mat.Inverse(freedofs)`` of heat.py:72 is
     replaced by Jacobi-CG with ``pre_heat`` (zero on constrained dofs) to ``cg_tol``.  ``temperature`` is updated
     in place and returned; diagnostics in ``last_info``."""
     for m_ in (diffusion, mass, heat):

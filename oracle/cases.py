@@ -110,3 +110,50 @@ def synthetic_condensation(A, free):
         out[k].eliminate_zeros()
         out[k].sort_indices()
     return out
+
+
+def heat_case(cells=(10, 10)):
+    """2D heat problem of heat.py on the unit square: P2 mass / stiffness on a structured mesh, zero Dirichlet boundary,
+    initial temperature = nodal values of the sine series of heat.py:13-18,150-151.  Returns K, M, free, (x, y), u0."""
+    import navier_stokes_solver_b200.synthetic as syn
+    S = syn.assemble_stokes(cells, (1.0, 1.0), with_mass2=True)
+    K, M = S.extras["K2"].to_scipy(), S.extras["M2"].to_scipy()
+    nx, ny = 2 * cells[0] + 1, 2 * cells[1] + 1
+    ix, iy = np.divmod(np.arange(nx * ny), ny)
+    free = (ix > 0) & (ix < nx - 1) & (iy > 0) & (iy < ny - 1)
+    x, y = ix / (nx - 1), iy / (ny - 1)
+    kl = [(1, 1), (2, 1), (1, 3), (3, 3), (2, 3), (4, 5), (5, 2)]
+    u0 = sum(2 * np.sin(k * np.pi * x) * np.sin(l * np.pi * y) for k, l in kl) * free
+    return K, M, free, (x, y), u0
+
+
+def simple_case(mesh_cells=(12, 4), lengths=(2.0, 0.41), dt=1e-3, seed=5):
+    """Synthetic operators with the shapes of NavierStokesSIMPLE_iterative.py:79-144: a, mstar = M + dt a, the mixed
+    projection system [[-Ml, B^T], [B, 0]] condensed onto the pressure (diagonal mass Ml), bproj = [0; B], mapV a
+    permutation between the continuous (V) and the 'broken' (V2) velocity numbering."""
+    import scipy.sparse as sp
+    import navier_stokes_solver_b200.synthetic as syn
+    S = syn.assemble_stokes(mesh_cells, lengths, with_mass2=True)
+    d = S.dim
+    A = S.A.to_scipy()
+    B = S.B.to_scipy()
+    free = S.free_u.numpy()
+    M = sp.kron(sp.identity(d), S.extras["M2"].to_scipy()).tocsr()
+    mstar = (M + dt * A).tocsr()
+    n_u, n_p = S.n_u, S.n_p
+    rng = np.random.default_rng(seed)
+    perm = rng.permutation(n_u)                         # V dof i lives at V2 dof perm[i]
+    Ml = M.diagonal()                                   # (row sums vanish at P2 vertices; the diagonal is positive)
+    Bf = (B @ sp.diags(free.astype(float))).tocsr()
+    P = sp.csr_matrix((np.ones(n_u), (perm, np.arange(n_u))), shape=(n_u, n_u))   # V -> V2
+    B2 = (Bf @ P.T).tocsr()
+    Ml2 = P @ Ml
+    N = n_u + n_p
+    Z = sp.csr_matrix((n_u, n_u))
+    Smat = sp.bmat([[Z, None], [None, B2 @ sp.diags(1.0 / Ml2) @ B2.T]]).tocsr()
+    H = sp.bmat([[Z, sp.diags(1.0 / Ml2) @ B2.T], [sp.csr_matrix((n_p, n_u)), sp.csr_matrix((n_p, n_p))]]).tocsr()
+    inner = sp.bmat([[sp.diags(-1.0 / Ml2), None], [None, sp.csr_matrix((n_p, n_p))]]).tocsr()
+    bproj = sp.bmat([[sp.csr_matrix((n_u, n_u))], [Bf]]).tocsr()
+    dS = Smat.diagonal()
+    return dict(A=A, mstar=mstar, free=free, Bf=Bf, S=Smat, H=H, HT=H.T.tocsr(), inner=inner, bproj=bproj, perm=perm,
+                dS=np.where(dS > 0, 1.0 / np.where(dS > 0, dS, 1.0), 0.0), n_u=n_u, n_p=n_p, N=N, f=S.f.numpy(), u0=S.u0.numpy(), dt=dt)

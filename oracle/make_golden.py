@@ -135,6 +135,107 @@ def gold_bpcg_condensed(mesh, tol, maxsteps):
     print(name, "it", it, "hist", len(hist), "lam_min", lam)
 
 
+def gold_heat():
+    """Runs /root/reference/heat.py as it is (module body included: the sweep over 7 time steps of :150-163) over the
+    FEM stand-in of ngs_standin/ngsolve/fem.py with the matrices of oracle.cases.heat_case, and records the temperature
+    vector after every pass of the time loop (heat.py calls Redraw() once per pass, :146)."""
+    import builtins
+    import runpy
+    import tempfile
+    import pandas as pd
+    from ngsolve import fem
+    from oracle.cases import heat_case
+    K, M, free, nodes, u0 = heat_case()
+    fem.install(K, M, free, nodes)
+    runs = []                       # one list of states per solve() call
+
+    def on_redraw():
+        gf = fem.gridfunctions[-1]
+        if not runs or runs[-1][0] is not gf:
+            runs.append((gf, []))
+        runs[-1][1].append(gf.vec.NumPy().copy())
+    fem.redraw_hooks[:] = [on_redraw]
+    cwd, old_input = os.getcwd(), builtins.input
+    sys.path.insert(0, REF)         # heat.py:7-8 import its sibling modules by bare name
+    try:
+        with tempfile.TemporaryDirectory() as tmp:
+            os.chdir(tmp)
+            builtins.input = lambda *a: ""                     # heat.py:165
+            _, out = quiet(runpy.run_path, os.path.join(REF, "heat.py"), run_name="ref_heat")
+            errors = pd.read_csv("heat_errors.csv")
+    finally:
+        os.chdir(cwd)
+        builtins.input = old_input
+        sys.path.remove(REF)
+        fem.redraw_hooks[:] = []
+    out = dict(fingerprint=np.array([K.nnz, float(abs(K).sum()), float(abs(M).sum()), float(np.abs(u0).sum())]),
+               time_steps=errors["time_step"].to_numpy(), errors=errors["error"].to_numpy(),
+               n_steps=np.array([len(st) for _, st in runs]))
+    assert len(runs) == len(out["time_steps"]) == 7
+    for k, (_, st) in enumerate(runs):
+        out["final_%d" % k] = st[-1]
+        out["first_%d" % k] = np.stack(st[:3])
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "heat_sweep"), **out)
+    print("heat_sweep steps", out["n_steps"], "errors", out["errors"])
+
+
+def gold_simple():
+    """DoTimeStep / Project of templates/NavierStokesSIMPLE_iterative.py:427-443, the reference's own method bodies,
+    called unbound on a namespace that carries the attributes they read (operators of oracle.cases.simple_case composed
+    exactly as :93-98 and :128-131 compose them, with the commented-out sparse direct inverses of :90,127 as inv1)."""
+    import types
+    import scipy.sparse as sp
+    from ngsolve import IdentityMatrix, PermutationMatrix
+    from ngsolve.fem import _DirectInverse
+    from oracle.cases import simple_case, synthetic_condensation
+    sys.path.insert(0, REF)          # :7 imports solvers.bramblepasciak_new relative to the repository root
+    try:
+        ref_simple = load_ref("templates/NavierStokesSIMPLE_iterative.py", "ref_simple")
+    finally:
+        sys.path.remove(REF)
+    NS = ref_simple.NavierStokes
+    T = simple_case()
+    n_u, n_p, N, dt = T["n_u"], T["n_p"], T["N"], T["dt"]
+    conv = (0.3 * T["mstar"] - 0.3 * dt * T["A"]).tocsr()      # any linear operator in place of conv_operator: 0.3 M
+    out = dict(conv_scale=0.3, fingerprint=np.array([T["A"].nnz, float(abs(T["A"]).sum()), float(abs(T["mstar"]).sum()),
+                                                     float(abs(T["bproj"]).sum()), float(T["perm"][:7].sum())]))
+    for tag, condense in (("plain", False), ("cond", True)):
+        if condense:
+            cd = synthetic_condensation(T["mstar"], T["free"])
+            inv1 = _DirectInverse(cd["mat"], T["free"] & ~cd["interior"])
+            ext = IdentityMatrix(n_u) + SparseMatrix(cd["H"])                    # :94-96
+            extT = IdentityMatrix(n_u) + SparseMatrix(cd["HT"])
+            invmstar = ext @ inv1 @ extT + SparseMatrix(cd["inner_solve"])
+        else:
+            invmstar = _DirectInverse(T["mstar"], T["free"])
+        invproj1 = _DirectInverse(T["S"], T["dS"] > 0)
+        ext = IdentityMatrix() + SparseMatrix(T["H"])                            # :129-131
+        extT = IdentityMatrix() + SparseMatrix(T["HT"])
+        invproj = ext @ invproj1 @ extT + SparseMatrix(T["inner"])
+        me = types.SimpleNamespace()
+        me.a = types.SimpleNamespace(mat=SparseMatrix(T["A"]))
+        me.f = types.SimpleNamespace(vec=BaseVector(T["f"].copy()), Assemble=lambda: None)
+        me.conv_operator = SparseMatrix(conv)
+        me.gfu = types.SimpleNamespace(vec=BaseVector(T["u0"].copy()))
+        me.gfup = types.SimpleNamespace(vec=BaseVector(n_p))
+        me.invmstar, me.invproj = invmstar, invproj
+        me.bproj = types.SimpleNamespace(mat=SparseMatrix(T["bproj"]))
+        me.tmp_projection = BaseVector(N)
+        me.mapV = PermutationMatrix(N, T["perm"])
+        me.V, me.V2, me.Q = (types.SimpleNamespace(ndof=n) for n in (n_u, n_u, n_p))
+        me.timestep = dt
+        me.Project = lambda vel, me=me: NS.Project(me, vel)
+        us, ps = [], []
+        for _ in range(3):
+            NS.DoTimeStep(me)
+            us.append(me.gfu.vec.NumPy().copy())
+            ps.append(me.gfup.vec.NumPy().copy())
+        out["gfu_" + tag], out["gfup_" + tag] = np.stack(us), np.stack(ps)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "simple_steps"), **out)
+    print("simple_steps |gfu|", [float(np.linalg.norm(u)) for u in out["gfu_plain"]],
+          "plain vs cond", float(np.linalg.norm(out["gfu_plain"][-1] - out["gfu_cond"][-1])))
+
+
 def gold_orth():
     rng = np.random.default_rng(7)
     n, m = 777, 5
@@ -184,3 +285,5 @@ if __name__ == "__main__":
     gold_bpcg_condensed("chan2d", tol=1e-10, maxsteps=20000)
     gold_orth()
     gold_rk()
+    gold_heat()
+    gold_simple()

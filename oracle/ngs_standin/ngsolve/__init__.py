@@ -23,7 +23,7 @@ import scipy.sparse as _sp
 __all__ = [
     "BaseVector", "BlockVector", "BaseMatrix", "BlockMatrix", "IdentityMatrix",
     "SparseMatrix", "DiagonalMatrix", "InnerProduct", "Norm", "Projector", "Vector", "Matrix",
-    "CreateVVector",
+    "CreateVVector", "PermutationMatrix",
 ]
 
 
@@ -529,6 +529,22 @@ class BlockMatrix(BaseMatrix):
         return self.rows[ij[0]][ij[1]]
 
 
+class PermutationMatrix(BaseMatrix):
+    """``PermutationMatrix(width, ind)``: (P x)[i] = x[ind[i]]  (templates/NavierStokesSIMPLE_iterative.py:138-144)."""
+
+    def __init__(self, width, ind):
+        self._w, self._ind = int(width), _np.asarray(ind, dtype=_np.int64)
+
+    def MultAdd(self, s, x, y):
+        y._a += s * x._a[self._ind]
+
+    def Height(self):
+        return len(self._ind)
+
+    def Width(self):
+        return self._w
+
+
 # --------------------------------------------------------------------------- dense (runge_kutta_method.py)
 class Vector:
     """Dense vector (ngsolve.bla.Vector)."""
@@ -606,3 +622,8 @@ class Matrix:
 
 
 from . import la, ngstd  # noqa: E402,F401
+from . import fem  # noqa: E402
+from .fem import (CoefficientFunction, x, y, sin, cos, exp, sqrt, dx, grad, Mesh, H1, BilinearForm, LinearForm,  # noqa: E402,F401
+                  GridFunction, Integrate, TaskManager, Draw, Redraw)
+
+__all__ += fem.FEM_NAMES

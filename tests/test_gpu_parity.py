@@ -422,17 +422,8 @@ def test_launch_counter_counts_kernels(nsb, dev):
 
 
 def _heat_case(cells=(10, 10)):
-    """2D heat problem of heat.py on the unit square: P2 mass / stiffness, zero Dirichlet boundary, initial
-    temperature = the analytic sine series of heat.py:21-27 at t = 0."""
-    import navier_stokes_solver_b200.synthetic as syn
-    S = syn.assemble_stokes(cells, (1.0, 1.0), with_mass2=True)
-    K, M = S.extras["K2"].to_scipy(), S.extras["M2"].to_scipy()
-    nx, ny = 2 * cells[0] + 1, 2 * cells[1] + 1
-    ix, iy = np.divmod(np.arange(nx * ny), ny)
-    free = (ix > 0) & (ix < nx - 1) & (iy > 0) & (iy < ny - 1)
-    x, y = ix / (nx - 1), iy / (ny - 1)
-    kl = [(1, 1), (2, 1), (1, 3), (3, 3), (2, 3), (4, 5), (5, 2)]
-    u0 = sum(2 * np.sin(k * np.pi * x) * np.sin(l * np.pi * y) for k, l in kl) * free
+    from oracle.cases import heat_case
+    K, M, free, _, u0 = heat_case(cells)
     return K, M, free, u0
 
 
@@ -444,7 +435,7 @@ def test_heat_large_step_matches_oracle(nsb, time_step):
     K, M, free, u0 = _heat_case()
     m = 5
     dt = time_step / m
-    H = (M + dt * K).tocsr()                                          # heat.py:52
+    H = (M + time_step * K).tocsr()                                   # heat.py:51-52
     dH = np.where(free, 1.0 / H.diagonal(), 0.0)
     w_ref = ko.RungeKuttaWeights(10)
 
@@ -552,36 +543,31 @@ def test_bpcg_static_condensation_matches_reference_golden(nsb, cases):
     assert relerr(sol, gold["sol_v2"]) < max(SOL_RTOL, 1e3 * float(tol))
 
 
-def _simple_case(mesh_cells=(12, 4), lengths=(2.0, 0.41), dt=1e-3, seed=5):
-    """Synthetic operators with the shapes of NavierStokesSIMPLE_iterative.py:79-144: a, mstar = M + dt a, the mixed
-    projection system [[-Ml, B^T], [B, 0]] condensed onto the pressure (diagonal mass Ml), bproj = [0; B], mapV a
-    permutation between the continuous (V) and the 'broken' (V2) velocity numbering."""
-    import scipy.sparse as sp
-    import navier_stokes_solver_b200.synthetic as syn
-    S = syn.assemble_stokes(mesh_cells, lengths, with_mass2=True)
-    d = S.dim
-    A = S.A.to_scipy()
-    B = S.B.to_scipy()
-    free = S.free_u.numpy()
-    M = sp.kron(sp.identity(d), S.extras["M2"].to_scipy()).tocsr()
-    mstar = (M + dt * A).tocsr()
-    n_u, n_p = S.n_u, S.n_p
-    rng = np.random.default_rng(seed)
-    perm = rng.permutation(n_u)                         # V dof i lives at V2 dof perm[i]
-    Ml = M.diagonal()                                   # (row sums vanish at P2 vertices; the diagonal is positive)
-    Bf = (B @ sp.diags(free.astype(float))).tocsr()
-    P = sp.csr_matrix((np.ones(n_u), (perm, np.arange(n_u))), shape=(n_u, n_u))   # V -> V2
-    B2 = (Bf @ P.T).tocsr()
-    Ml2 = P @ Ml
-    N = n_u + n_p
-    Z = sp.csr_matrix((n_u, n_u))
-    Smat = sp.bmat([[Z, None], [None, B2 @ sp.diags(1.0 / Ml2) @ B2.T]]).tocsr()
-    H = sp.bmat([[Z, sp.diags(1.0 / Ml2) @ B2.T], [sp.csr_matrix((n_p, n_u)), sp.csr_matrix((n_p, n_p))]]).tocsr()
-    inner = sp.bmat([[sp.diags(-1.0 / Ml2), None], [None, sp.csr_matrix((n_p, n_p))]]).tocsr()
-    bproj = sp.bmat([[sp.csr_matrix((n_u, n_u))], [Bf]]).tocsr()
-    dS = Smat.diagonal()
-    return dict(A=A, mstar=mstar, free=free, Bf=Bf, S=Smat, H=H, HT=H.T.tocsr(), inner=inner, bproj=bproj, perm=perm,
-                dS=np.where(dS > 0, 1.0 / np.where(dS > 0, dS, 1.0), 0.0), n_u=n_u, n_p=n_p, N=N, f=S.f.numpy(), u0=S.u0.numpy(), dt=dt)
+@pytest.mark.gpu
+@pytest.mark.parametrize("k", [2, 4])
+def test_heat_steps_match_reference_sweep(nsb, k):
+    """Device time loop against the temperature vectors of the reference's heat.py run unmodified
+    (tests/golden/heat_sweep.npz): 5 steps of 0.01 and 50 steps of 0.001; the reference's direct inverse (:72) is a
+    Jacobi-CG to 1e-13 here."""
+    from oracle.cases import load_golden
+    gold = load_golden("heat_sweep")
+    K, M, free, u0 = _heat_case()
+    time_step, n = float(gold["time_steps"][k]), int(gold["n_steps"][k])
+    H = (M + time_step * K).tocsr()
+    dK, dM_, dHm = nsb.SparseMatrix.from_scipy(K), nsb.SparseMatrix.from_scipy(M), nsb.SparseMatrix.from_scipy(H)
+    pre = nsb.DiagonalPreconditioner.from_diagonal(np.where(free, 1.0 / H.diagonal(), 0.0))
+    w = nsb.ImplicitRungeKuttaMethodWeights(10)
+    u = u0.copy()
+    for step in range(n):
+        nsb.heat_large_step(dK, dM_, dHm, pre, u, time_step, w, 5, cg_tol=1e-13, cg_maxsteps=2000)
+        if step < 3:
+            assert relerr(u, gold["first_%d" % k][step]) < SOL_RTOL
+    assert relerr(u, gold["final_%d" % k]) < 1e-7
+
+
+def _simple_case(*a, **k):
+    from oracle.cases import simple_case
+    return simple_case(*a, **k)
 
 
 @pytest.mark.gpu
@@ -628,6 +614,39 @@ def test_simple_time_step_chain_matches_oracle(nsb, condense_mstar):
     # the projected increment is discretely divergence-free on the free dofs:  B (gfu - u0) = dt * sum B temp2 = 0
     div = T["Bf"] @ (gfu.cpu().numpy() - T["u0"])
     assert np.abs(div).max() < 1e-9 * max(1.0, np.abs(T["Bf"]).sum(axis=1).max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["plain", "cond"])
+def test_simple_time_steps_match_reference_golden(nsb, tag):
+    """Device DoTimeStep / Project chain, with a (linear) convection callback, against three passes of the reference's
+    own method bodies (tests/golden/simple_steps.npz); the reference's direct inverses are device CG to 1e-13 here."""
+    import torch
+    from oracle.cases import load_golden, synthetic_condensation
+    gold = load_golden("simple_steps")
+    T = _simple_case()
+    n_u, n_p, dt = T["n_u"], T["n_p"], T["dt"]
+    up = nsb.SparseMatrix.from_scipy
+    if tag == "cond":
+        cd = synthetic_condensation(T["mstar"], T["free"])
+        dms = cd["mat"].diagonal()
+        dm = np.where(T["free"] & ~cd["interior"] & (dms != 0), 1.0 / np.where(dms != 0, dms, 1.0), 0.0)
+        inv1 = nsb.CGSolver(up(cd["mat"]), nsb.DiagonalPreconditioner.from_diagonal(dm), precision=1e-13, maxsteps=4000)
+        invmstar = nsb.ExtendedInverse(inv1, up(cd["H"]), up(cd["HT"]), up(cd["inner_solve"]))
+    else:
+        dm = np.where(T["free"], 1.0 / T["mstar"].diagonal(), 0.0)
+        invmstar = nsb.ExtendedInverse(nsb.CGSolver(up(T["mstar"]), nsb.DiagonalPreconditioner.from_diagonal(dm),
+                                                    precision=1e-13, maxsteps=4000))
+    invp1 = nsb.CGSolver(up(T["S"]), nsb.DiagonalPreconditioner.from_diagonal(T["dS"]), precision=1e-13, maxsteps=8000)
+    invproj = nsb.ExtendedInverse(invp1, up(T["H"]), up(T["HT"]), up(T["inner"]))
+    C = up((float(gold["conv_scale"]) * (T["mstar"] - dt * T["A"])).tocsr())
+    gfu = torch.as_tensor(T["u0"].copy(), device="cuda")
+    stepper = nsb.SimpleStepper(up(T["A"]), invmstar, up(T["bproj"]), invproj, nsb.PermutationMatrix(T["N"], T["perm"]), gfu,
+                                n_u, (n_u, n_u + n_p), dt, f=torch.as_tensor(T["f"], device="cuda"))
+    for step in range(3):
+        stepper.DoTimeStep(convection=lambda g: C * g)
+        assert relerr(gfu.cpu().numpy(), gold["gfu_" + tag][step]) < SOL_RTOL
+        assert relerr(stepper.gfup.cpu().numpy(), gold["gfup_" + tag][step]) < 1e-6
 
 
 def _blocks_of(c, size=5):

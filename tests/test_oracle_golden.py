@@ -262,3 +262,73 @@ def test_condensed_oracle_matches_reference_golden(cases):
     np.testing.assert_allclose(info["err0"], float(gold["err0_v2"]), rtol=1e-12)
     np.testing.assert_allclose(h[:50], gold["hist_v2"][:50], rtol=HIST_RTOL)
     assert relerr(sol, gold["sol_v2"]) < max(SOL_RTOL, 1e3 * float(tol))
+
+
+def _check_heat_fingerprint(K, M, u0, gold):
+    fp = np.array([K.nnz, float(abs(K).sum()), float(abs(M).sum()), float(np.abs(u0).sum())])
+    np.testing.assert_allclose(fp, gold["fingerprint"], rtol=1e-12)
+
+
+@pytest.mark.parametrize("k", [0, 1, 2, 3, 4, 5])
+def test_heat_oracle_matches_reference_sweep(k):
+    """tests/golden/heat_sweep.npz holds the temperature vectors of the reference's heat.py run unmodified
+    (oracle/make_golden.py::gold_heat): the oracle's restated large step (heat.py:81-146), with the same sparse direct
+    inverse (:72), must retrace them."""
+    import scipy.sparse.linalg as spla
+    from oracle.cases import heat_case
+    gold = load_golden("heat_sweep")
+    K, M, free, _, u0 = heat_case()
+    _check_heat_fingerprint(K, M, u0, gold)
+    time_step, n = float(gold["time_steps"][k]), int(gold["n_steps"][k])
+    idx = np.flatnonzero(free)
+    lu = spla.splu((M + time_step * K).tocsr()[idx][:, idx].tocsc())          # heat.py:52,72
+
+    def heat_solve(r):
+        out = np.zeros_like(r)
+        out[idx] = lu.solve(r[idx])
+        return out
+    w = ko.RungeKuttaWeights(10)
+    u = u0.copy()
+    for step in range(n):
+        u = ko.heat_large_step(K, M, heat_solve, u, time_step, w, 5)
+        if step < 3:
+            assert relerr(u, gold["first_%d" % k][step]) < 1e-9
+    assert relerr(u, gold["final_%d" % k]) < 1e-8
+
+
+@pytest.mark.parametrize("tag", ["plain", "cond"])
+def test_simple_oracle_matches_reference_steps(tag):
+    """tests/golden/simple_steps.npz: three passes of the reference's own DoTimeStep / Project method bodies
+    (templates/NavierStokesSIMPLE_iterative.py:427-443, oracle/make_golden.py::gold_simple)."""
+    import scipy.sparse.linalg as spla
+    from oracle.cases import simple_case, synthetic_condensation
+    gold = load_golden("simple_steps")
+    T = simple_case()
+    fp = np.array([T["A"].nnz, float(abs(T["A"]).sum()), float(abs(T["mstar"]).sum()), float(abs(T["bproj"]).sum()),
+                   float(T["perm"][:7].sum())])
+    np.testing.assert_allclose(fp, gold["fingerprint"], rtol=1e-12)
+    n_u, n_p, dt = T["n_u"], T["n_p"], T["dt"]
+
+    def direct(mat, mask):
+        idx = np.flatnonzero(mask)
+        lu = spla.splu(mat.tocsr()[idx][:, idx].tocsc())
+
+        def solve(r):
+            out = np.zeros_like(r)
+            out[idx] = lu.solve(r[idx])
+            return out
+        return solve
+    if tag == "cond":
+        cd = synthetic_condensation(T["mstar"], T["free"])
+        inv_ms = ko.extended_inverse(direct(cd["mat"], T["free"] & ~cd["interior"]),
+                                     dict(H=cd["H"], HT=cd["HT"], inner_solve=cd["inner_solve"]))
+    else:
+        inv_ms = direct(T["mstar"], T["free"])
+    inv_pr = ko.extended_inverse(direct(T["S"], T["dS"] > 0), dict(H=T["H"], HT=T["HT"], inner_solve=T["inner"]))
+    conv = float(gold["conv_scale"]) * (T["mstar"] - dt * T["A"])
+    gfu = T["u0"].copy()
+    for step in range(3):
+        p = ko.simple_time_step(gfu, T["A"], inv_ms, lambda v: ko.simple_project(v, inv_pr, T["bproj"], T["perm"], (n_u, n_u + n_p)),
+                                dt, n_u, conv=lambda g: conv @ g, f=T["f"])
+        assert relerr(gfu, gold["gfu_" + tag][step]) < 1e-11
+        assert relerr(p, gold["gfup_" + tag][step]) < 1e-9

@@ -85,7 +85,7 @@ def config2():
     w = nsb.ImplicitRungeKuttaMethodWeights(10)
     for time_step in (1e-2, 1e-3):
         m, end = 5, 0.05
-        H = (M + (time_step / m) * K).tocsr()
+        H = (M + time_step * K).tocsr()                       # heat.py:51-52
         dH = np.where(free, 1.0 / H.diagonal(), 0.0)
         dK, dM_, dHm = (nsb.SparseMatrix.from_scipy(a) for a in (K, M, H))
         pre = nsb.DiagonalPreconditioner.from_diagonal(dH)
