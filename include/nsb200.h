@@ -136,6 +136,15 @@ NSB_API int nsb_pre_create_blocks(nsb_ctx ctx, nsb_mat A, int64_t nblocks, const
 /* jacobi.Smooth(y, x) (backward == 0) / jacobi.SmoothBack(y, x) (backward != 0): one block Gauss-Seidel sweep on y for the
  * right-hand side x (:377,:381) */
 NSB_API int nsb_pre_smooth(nsb_ctx ctx, nsb_pre p, const double* x, double* y, int backward);
+/* Auxiliary-space preconditioner MypreA (templates/NavierStokesSIMPLE_iterative.py:364-391):
+ *   gauss_seidel != 0 (:375-381):  y = 0; jacobi.Smooth(y, x); t = x - A y; y += transform coarse transform^T t; jacobi.SmoothBack(y, x)
+ *   gauss_seidel == 0 (:383):      y = (transform coarse transform^T + jacobi) x
+ * smoother: a handle from nsb_pre_create_blocks on A (its matrix is the A of the residual); transform (n x n_c) and its
+ * explicit transpose as device matrices; coarse: any preconditioner handle of size n_c (the reference puts component-wise
+ * h1amg there, which is NGSolve-internal; a Jacobi or block smoother of the H1 matrix, or another composite, goes here).
+ * The handles passed in are not owned and must outlive the result. */
+NSB_API int nsb_pre_create_auxspace(nsb_ctx ctx, nsb_pre smoother, nsb_mat transform, nsb_mat transform_t, nsb_pre coarse,
+                                    int gauss_seidel, nsb_pre* out);
 NSB_API int nsb_pre_destroy(nsb_pre p);
 NSB_API int nsb_pre_apply(nsb_ctx ctx, nsb_pre p, const double* x, double* y);
 

@@ -5,7 +5,7 @@ sm_100a CUDA behind the C ABI of include/nsb200.h); this package is the host-sid
 reference's operator/vector protocol."""
 from . import _lib, la, solvers, simple  # noqa: F401
 from .simple import ExtendedInverse, PermutationMatrix, SimpleStepper  # noqa: F401
-from .la import (BaseVector, BlockMatrix, BlockSmoother, BlockVector, CondensedOperator, Context, DiagonalPreconditioner, IdentityMatrix,  # noqa: F401
+from .la import (AuxiliarySpacePreconditioner, BaseVector, BlockMatrix, BlockSmoother, BlockVector, CondensedOperator, Context, DiagonalPreconditioner, IdentityMatrix,  # noqa: F401
                  InnerProduct, Norm, Preconditioner, SparseMatrix, default_context, set_default_context)
 from .solvers import (BramblePasciakCG, CGSolve, CGSolver, EigenValues_Preconditioner, MinRes,  # noqa: F401
                       ImplicitRungeKuttaMethodWeights, bramble_pasciak_cg, heat_large_step,

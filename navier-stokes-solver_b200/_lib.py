@@ -48,6 +48,7 @@ SIGNATURES = {
     "nsb_pre_create_blockdiag2": (C.c_int, [c_ctx, c_pre, c_pre, P(c_pre)]),
     "nsb_pre_create_blocks": (C.c_int, [c_ctx, c_mat, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, P(c_pre)]),
     "nsb_pre_smooth": (C.c_int, [c_ctx, c_pre, C.c_void_p, C.c_void_p, C.c_int]),
+    "nsb_pre_create_auxspace": (C.c_int, [c_ctx, c_pre, c_mat, c_mat, c_pre, C.c_int, P(c_pre)]),
     "nsb_pre_destroy": (C.c_int, [c_pre]),
     "nsb_pre_apply": (C.c_int, [c_ctx, c_pre, C.c_void_p, C.c_void_p]),
     "nsb_minres": (C.c_int, [c_ctx, c_mat, c_pre, C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p,

@@ -6,7 +6,7 @@
 // Blocks are disjoint dof lists (the facet blocks of :360-362), handed over colour by colour: blocks of one
 // colour are not coupled through A, so a colour is one parallel launch and the sweep equals the sequential
 // sweep in that block order.  Dense inverses are computed once on the device (Gauss-Jordan in shared memory).
-#include "spmv.cuh"
+#include "cond.cuh"
 
 namespace nsb {
 
@@ -116,8 +116,28 @@ int block_gs_sweep(Context& c, nsb_pre_s* p, const double* x, double* y, bool ba
     return NSB_OK;
 }
 
+// MypreA.Mult (:374-383).  x, y: length n, not aliased.
+static int auxspace_apply(Context& c, nsb_pre_s* p, const double* x, double* y) {
+    nsb_pre_s* sm = p->smoother;
+    const double* coarse_in = x;
+    if (p->gs) {
+        NSB_CHECK(vec_set(c, y, 0.0, p->n));                                                  // y[:] = 0
+        NSB_CHECK(block_gs_sweep(c, sm, x, y, false));                                        // jacobi.Smooth(y, x)
+        NSB_CHECK(spmv_launch<0>(c, sm->mat, y, SubInOp{x, p->aux_t.p}));                     // temp = x - mat * y
+        coarse_in = p->aux_t.p;
+    } else {
+        NSB_CHECK(block_jacobi(c, sm, x, y));                                                 // jacobi * x
+    }
+    NSB_CHECK(spmv_launch<0>(c, p->transform_t, coarse_in, PlainRowOp{p->aux_c.p}));          // transform.T * temp
+    NSB_CHECK(pre_apply_device(c, p->coarse, p->aux_c.p, p->aux_z.p));                        // preAh1 * ..
+    NSB_CHECK(spmv_launch<0>(c, p->transform, p->aux_z.p, AddInOp{y, y}));                    // y += transform * ..
+    if (p->gs) NSB_CHECK(block_gs_sweep(c, sm, x, y, true));                                  // jacobi.SmoothBack(y, x)
+    return NSB_OK;
+}
+
 int pre_apply_device(Context& c, nsb_pre_s* p, const double* x, double* y) {
     if (p->kind == 0) return vec_diagmul(c, y, 1.0, p->d.p, x, p->n);
+    if (p->kind == 2) return auxspace_apply(c, p, x, y);
     if (!p->gs) return block_jacobi(c, p, x, y);
     // MypreA.Mult with GS = True and no auxiliary-space term (:375-381): y = 0; Smooth(y, x); SmoothBack(y, x)
     NSB_CHECK(vec_set(c, y, 0.0, p->n));
@@ -209,5 +229,36 @@ extern "C" int nsb_pre_smooth(nsb_ctx ctx, nsb_pre p, const double* x, double* y
     NSB_CHECK(block_gs_sweep(c, p, dx.p, dy.p, backward != 0));
     NSB_CHECK(copy_out(c, y, dy.p, p->n));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
+    return NSB_OK;
+}
+
+extern "C" int nsb_pre_create_auxspace(nsb_ctx ctx, nsb_pre smoother, nsb_mat transform, nsb_mat transform_t, nsb_pre coarse,
+                                       int gauss_seidel, nsb_pre* out) {
+    NSB_REQUIRE(ctx && smoother && transform && transform_t && coarse && out, "nsb_pre_create_auxspace: bad argument");
+    NSB_REQUIRE(smoother->kind == 1, "nsb_pre_create_auxspace: the smoother must come from nsb_pre_create_blocks");
+    NSB_REQUIRE(!gauss_seidel || smoother->ncolors > 0, "nsb_pre_create_auxspace: the multiplicative variant needs a coloured smoother");
+    const int64_t n = smoother->n, nc = coarse->n;
+    NSB_REQUIRE(transform->rows == n && transform->cols == nc && transform_t->rows == nc && transform_t->cols == n,
+                "nsb_pre_create_auxspace: transform must be %lld x %lld and transform_t its transpose", (long long)n, (long long)nc);
+    NSB_REQUIRE(!transform->halo && !transform_t->halo, "nsb_pre_create_auxspace: row-partitioned transforms are not supported");
+    Context& c = ctx->c;
+    NSB_CUDA(cudaSetDevice(c.device));
+    nsb_pre_s* p = new nsb_pre_s();
+    p->ctx = &c;
+    p->n = n;
+    p->kind = 2;
+    p->gs = gauss_seidel ? 1 : 0;
+    p->smoother = smoother;
+    p->coarse = coarse;
+    p->transform = transform;
+    p->transform_t = transform_t;
+    int rc = p->aux_t.alloc(n);
+    if (rc == NSB_OK) rc = p->aux_c.alloc(nc);
+    if (rc == NSB_OK) rc = p->aux_z.alloc(nc);
+    if (rc != NSB_OK) {
+        delete p;
+        return rc;
+    }
+    *out = p;
     return NSB_OK;
 }

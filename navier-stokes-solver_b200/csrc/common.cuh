@@ -199,7 +199,7 @@ struct nsb_mat_s {
 struct nsb_pre_s {
     nsb::Context* ctx = nullptr;
     int64_t n = 0;
-    int kind = 0;           // 0: diagonal (y = d .* x)   1: block smoother (blockpre.cu)
+    int kind = 0;           // 0: diagonal (y = d .* x)   1: block smoother   2: auxiliary-space composite (blockpre.cu)
     nsb::DevBuf<double> d;  // diagonal preconditioner: y = d .* x
     // block smoother, a.mat.CreateBlockSmoother(blocks) (templates/NavierStokesSIMPLE_iterative.py:360-373): disjoint dof
     // blocks listed colour by colour (blocks of one colour are not coupled by the matrix), dense inverse per block
@@ -211,6 +211,12 @@ struct nsb_pre_s {
     nsb::DevBuf<int32_t> block_dofs;
     nsb::DevBuf<int64_t> inv_ptr;          // nblocks + 1, into inv (block b: size^2 entries, row-major)
     nsb::DevBuf<double> inv;
+    // kind 2: auxiliary-space preconditioner MypreA (:364-383) = block smoother + transform coarse transform^T.
+    // Nothing below is owned.  gs selects the multiplicative (:375-381) or the additive (:383) variant.
+    nsb_pre_s* smoother = nullptr;         // kind 1
+    nsb_pre_s* coarse = nullptr;           // any kind, size = transform columns
+    nsb_mat_s *transform = nullptr, *transform_t = nullptr;
+    nsb::DevBuf<double> aux_t, aux_c, aux_z;   // scratch: n, n_coarse, n_coarse
 };
 
 namespace nsb {

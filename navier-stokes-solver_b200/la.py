@@ -605,6 +605,50 @@ class BlockSmoother(BaseMatrix):
             pass
 
 
+class AuxiliarySpacePreconditioner(BaseMatrix):
+    """``MypreA(space, a, jacblocks, GS)`` of templates/NavierStokesSIMPLE_iterative.py:364-391 on the device:
+
+        GS=True   y = 0; jacobi.Smooth(y, x); t = x - a.mat*y; y += (transform @ coarse @ transform.T)*t; jacobi.SmoothBack(y, x)
+        GS=False  y = ((transform @ coarse @ transform.T) + jacobi) * x
+
+    ``smoother``: a BlockSmoother of ``a.mat`` (built with ``pattern`` when GS); ``transform``: device SparseMatrix
+    (X2.ndof x H1.ndof); ``coarse``: any device preconditioner of the auxiliary H1 problem -- the reference puts
+    component-wise h1amg there (:310-357), which is NGSolve-internal; a Jacobi / block smoother of the exported H1 matrix
+    (or another composite) takes its place."""
+
+    def __init__(self, smoother, transform, coarse, GS=True, transform_t=None):
+        if not isinstance(smoother, BlockSmoother):
+            raise TypeError("AuxiliarySpacePreconditioner needs a BlockSmoother")
+        if not isinstance(transform, SparseMatrix):
+            raise TypeError("AuxiliarySpacePreconditioner needs `transform` as a device SparseMatrix")
+        if not hasattr(coarse, "h"):
+            raise TypeError("the coarse preconditioner must be a device preconditioner (Jacobi, BlockSmoother, ...)")
+        self.ctx, self.n = smoother.ctx, smoother.n
+        self.smoother, self.transform, self.coarse = smoother, transform, coarse
+        self.transform_t = transform_t if transform_t is not None else transform.CreateTranspose()
+        h = _lib.c_pre()
+        _lib.check(self.ctx._lib.nsb_pre_create_auxspace(self.ctx.h, smoother.h, transform.h, self.transform_t.h, coarse.h,
+                                                         int(bool(GS)), C.byref(h)), "nsb_pre_create_auxspace")
+        self.h = h
+
+    height = property(lambda self: self.n)
+    width = property(lambda self: self.n)
+
+    def __mul__(self, v):
+        px, nx, keep = buffer_of(v)
+        out = np.empty(self.n) if not _is_torch(keep) else keep.new_empty(self.n)
+        py, _, _ = buffer_of(out)
+        _lib.check(self.ctx._lib.nsb_pre_apply(self.ctx.h, self.h, px, py), "nsb_pre_apply")
+        return BaseVector(out)
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None) and self.ctx.h:
+                self.ctx._lib.nsb_pre_destroy(self.h)
+        except Exception:
+            pass
+
+
 def Preconditioner(mat, type="local", freedofs=None, **kwargs):
     """``Preconditioner(bf, 'local')`` (run.py:62).  Only the Jacobi type can be built from CSR; BDDC,
     h1amg and friends are NGSolve-internal and are refused rather than emulated."""

@@ -17,7 +17,7 @@ import math
 import numpy as np
 
 from . import _lib
-from .la import (BaseVector, BlockMatrix, BlockSmoother, BlockVector, CondensedOperator, DiagonalPreconditioner, SparseMatrix,
+from .la import (AuxiliarySpacePreconditioner, BaseVector, BlockMatrix, BlockSmoother, BlockVector, CondensedOperator, DiagonalPreconditioner, SparseMatrix,
                  _is_torch,
                  buffer_of, default_context)
 
@@ -37,9 +37,9 @@ def _pre_handle(pre, n):
         return None, None
     if isinstance(pre, BlockMatrix):
         pre = pre.blockdiag_preconditioner()
-    if not isinstance(pre, (DiagonalPreconditioner, BlockSmoother)):
+    if not isinstance(pre, (DiagonalPreconditioner, BlockSmoother, AuxiliarySpacePreconditioner)):
         raise TypeError("preconditioner %r cannot run on the device: only diagonal ('local'/Jacobi) preconditioners, "
-                        "2x2 block-diagonals of them and block smoothers are available; there is no CPU fallback" % (type(pre),))
+                        "2x2 block-diagonals of them, block smoothers and auxiliary-space composites are available; there is no CPU fallback" % (type(pre),))
     if pre.n != n:
         raise ValueError("preconditioner size %d != %d" % (pre.n, n))
     return pre.h, pre

@@ -719,3 +719,68 @@ def test_bpcg_with_block_smoother_preconditioner(nsb, cases, gauss_seidel):
     ur, er, _ = ko.pcg(c.A, rhs, pre=pre_ref, tol=1e-10, maxsteps=2000)
     assert abs(len(errs) - len(er)) <= 1
     assert relerr(np.asarray(u), ur) < 1e-7
+
+
+def _aggregation_transform(c, size=6):
+    """Piecewise-constant transform from an auxiliary space of aggregates (consecutive free dofs) to the velocity space;
+    stands where the reference has the H(div) <- H1 `transform` (NavierStokesSIMPLE_iterative.py:282-290)."""
+    import scipy.sparse as sp
+    free_idx = np.nonzero(c.free_u)[0]
+    agg = np.arange(len(free_idx)) // size
+    T = sp.csr_matrix((np.ones(len(free_idx)), (free_idx, agg)), shape=(c.n_u, int(agg.max()) + 1))
+    Ac = (T.T @ c.A @ T).tocsr()
+    return T, Ac
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("GS", [True, False])
+def test_auxiliary_space_preconditioner_matches_oracle(nsb, cases, GS):
+    """MypreA (NavierStokesSIMPLE_iterative.py:364-391): smoother + transform @ coarse @ transform.T, both variants; applied,
+    as CG preconditioner and as preA of BramblePasciakCG, against the oracle restatement."""
+    from oracle import krylov_oracle as ko
+    c = cases("chan2d")
+    T, Ac = _aggregation_transform(c)
+    dc = 1.0 / Ac.diagonal()
+    A, B = nsb.SparseMatrix.from_scipy(c.A), nsb.SparseMatrix.from_scipy(c.B)
+    sm = A.CreateBlockSmoother(_blocks_of(c, 4), pattern=c.A)
+    pre = nsb.AuxiliarySpacePreconditioner(sm, nsb.SparseMatrix.from_scipy(T), nsb.DiagonalPreconditioner.from_diagonal(dc), GS=GS)
+    ref_sm = ko.BlockSmoother(c.A, sm.blocks)
+    pre_ref = lambda v: ko.aux_space_pre(ref_sm, c.A, T, dc, v, GS=GS)
+    x = np.random.default_rng(11).uniform(-1, 1, c.n_u) * c.free_u
+    want = pre_ref(x)
+    np.testing.assert_allclose((pre * x).NumPy(), want, rtol=0, atol=1e-12 * np.abs(want).max())
+    # symmetric: <pre x, z> == <x, pre z>
+    z = np.random.default_rng(12).uniform(-1, 1, c.n_u) * c.free_u
+    assert abs(np.dot((pre * x).NumPy(), z) - np.dot(x, (pre * z).NumPy())) < 1e-10 * abs(np.dot(want, z))
+    # CG
+    rhs = c.A @ (c.free_u * np.random.default_rng(2).uniform(-1, 1, c.n_u)) * c.free_u
+    u, errs = nsb.CGSolve(A, rhs, pre, None, 1e-10, 2000)
+    ur, er, _ = ko.pcg(c.A, rhs, pre=pre_ref, tol=1e-10, maxsteps=2000)
+    assert abs(len(errs) - len(er)) <= 1
+    m = min(30, len(errs), len(er))
+    np.testing.assert_allclose(np.asarray(errs[:m]), np.asarray(er[:m]), rtol=1e-9)
+    assert relerr(np.asarray(u), ur) < 1e-8
+    # the multiplicative composite beats its smoother alone (the additive one, with an unscaled Jacobi on a crude
+    # aggregation space, need not)
+    if GS:
+        _, errs_sm = nsb.CGSolve(A, rhs, A.CreateBlockSmoother(sm.blocks, pattern=c.A, gauss_seidel=True), None, 1e-10, 2000)
+        assert len(errs) < len(errs_sm)
+    # BPCG with the composite as preA (:397)
+    lam = 0.5 * min(nsb.EigenValues_Preconditioner(A, pre, tol=1e-9, maxsteps=2000))
+    sol_ref = c.start()
+    _, h_ref, info = ko.bramble_pasciak_cg_v2(c.A, c.B, c.f, c.g, pre_ref, c.dM, sol=sol_ref, tol=1e-10, maxsteps=20000,
+                                              initialize=False, lam_min=lam, BT=c.BT)
+    sol = c.start()
+    ret = quiet(nsb.BramblePasciakCG, A, B, None, c.f, c.g, pre, nsb.DiagonalPreconditioner.from_diagonal(c.dM), sol, tol=1e-10,
+                maxsteps=20000, initialize=False, lam_min=lam)
+    assert abs(ret[0][0] - info["it"]) <= 2
+    h = nsb.solvers.last_info["history"]
+    m = min(30, len(h), len(h_ref))
+    np.testing.assert_allclose(h[:m], np.array(h_ref[:m]), rtol=1e-9)
+    assert relerr(sol, sol_ref) < 1e-7
+    # wrong shapes / kinds are refused
+    with pytest.raises(TypeError):
+        nsb.AuxiliarySpacePreconditioner(nsb.DiagonalPreconditioner.from_diagonal(c.dA), nsb.SparseMatrix.from_scipy(T),
+                                         nsb.DiagonalPreconditioner.from_diagonal(dc))
+    with pytest.raises(nsb._lib.NsbError):
+        nsb.AuxiliarySpacePreconditioner(sm, nsb.SparseMatrix.from_scipy(T), nsb.DiagonalPreconditioner.from_diagonal(c.dA))
