@@ -179,6 +179,10 @@ def main():
     ap.add_argument("--lanczos-steps", type=int, default=1500)
     ap.add_argument("--no-minres", action="store_true")
     ap.add_argument("--minres-iters", type=int, default=60)
+    ap.add_argument("--solve-to-tol", type=float, default=0.0,
+                    help="also run one full BramblePasciakCG solve to this relative tolerance (the reference's call uses 1e-10, "
+                         "NavierStokesSIMPLE_iterative.py:397) and report time to tolerance; off by default")
+    ap.add_argument("--solve-maxsteps", type=int, default=30000)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -348,10 +352,34 @@ def main():
                        "achieved_gbs": mbytes * mrate / 1e9, "frac_of_measured_peak": mbytes * mrate / 1e9 / peak,
                        "spmv_K_ms": Kb.spmv_bench(warmup=5, reps=20), "spmv_K_format": Kb.format()}
         del Kb
+    ttt = None
+    if args.solve_to_tol > 0:
+        th = np.zeros(args.solve_maxsteps + 2)
+        tsol = u_start.clone()
+        upd, secs, status = C.c_int(), C.c_double(), C.c_int()
+        pf, _, _ = nsb.la.buffer_of(f_d)
+        pg, _, _ = nsb.la.buffer_of(g_d)
+        ps, _, _ = nsb.la.buffer_of(tsol)
+        barrier()
+        t0 = time.perf_counter()
+        _lib.check(lib.nsb_bpcg(ctx.h, A.h, B.h, BTm.h, pA.h, pM.h, k_scale, pf, pg, ps, args.solve_maxsteps, args.solve_to_tol,
+                                0, 1, 2, th.ctypes.data, C.byref(upd), C.byref(secs), C.byref(status)), "nsb_bpcg")
+        barrier()
+        ttt = {"tol": args.solve_to_tol, "rel_err": True, "iterations": upd.value, "loop_seconds": secs.value,
+               "call_seconds": time.perf_counter() - t0, "status": status.value,
+               "final_relative_error": float(th[upd.value] / th[0]) if th[0] > 0 else None}
+        del tsol
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
+    # DRAM bytes per launch of the same kernel from the committed ncu --set full capture (never measured under this run)
+    traffic, traffic_src = None, None
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_spmv_A_traffic.json")
+    if world == 1 and os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if tj.get("dofs") == int(n_u + n_p):
+            traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], "profiles/r1_spmv_A_traffic.json"
     line = {
         "metric": "bpcg_krylov_iterations_per_s", "value": value, "unit": "iterations/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
@@ -366,7 +394,7 @@ def main():
                            "frac_of_nominal_8TBs": iter_gbs / 8000.0 if iter_gbs else None},
         "roofline": {"bound": "hbm", "kernel": "spmv_sell_kernel (A, %d nnz)" % nnzA, "achieved": ach_A, "peak": peak,
                      "peak_source": peak_src, "unit": "GB/s", "frac": ach_A / peak, "frac_of_nominal_8TBs": ach_A / 8000.0,
-                     "algorithmic_bytes": bytes_A, "ms": ms_A, "traffic": None,
+                     "algorithmic_bytes": bytes_A, "ms": ms_A, "traffic": traffic, "traffic_source": traffic_src,
                      "other": {"spmv_B_gbs": B.spmv_bytes() / ms_B / 1e6, "spmv_BT_gbs": BTm.spmv_bytes() / ms_BT / 1e6}},
         "e2e": {"value": e2e_value, "unit": "iterations/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "history_matches_device_leg": bool(same)},
@@ -374,6 +402,8 @@ def main():
     }
     if minres_info:
         line["minres"] = minres_info
+    if ttt:
+        line["time_to_tolerance"] = ttt
     if not args.no_cpu_baseline and world == 1:
         v, info = cpu_oracle_rate(args.dofs, 20)
         line["cpu_baseline"] = {"value": v, "unit": "iterations/s", "cores": info["threads"], "kind": "port",
