@@ -265,18 +265,30 @@ def main():
         torch.cuda.synchronize()
         ctx.sync()
 
-    def timed(nsteps, fn):
+    # every kernel and copy of the library runs on the context's own stream: the timed region is bracketed by CUDA
+    # events recorded on THAT stream (torch.cuda.Event on torch's current stream would see none of it), after a
+    # barrier + synchronize on both sides; max over ranks.  The host clock around the same region is kept as a cross-check.
+    lib_stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local))
+    wall_check = {}
+
+    def timed(nsteps, fn, tag=None):
         barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
+        e0.record(lib_stream)
         loop = 0.0
         for _ in range(nsteps):
             loop += fn()
+        e1.record(lib_stream)
         barrier()
-        dt = time.perf_counter() - t0
+        wall = time.perf_counter() - t0
+        dt = e0.elapsed_time(e1) * 1e-3
         if world > 1:
-            t = torch.tensor([dt, loop], dtype=torch.float64, device="cuda")
+            t = torch.tensor([dt, loop, wall], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt, loop = float(t[0]), float(t[1])
+            dt, loop, wall = float(t[0]), float(t[1]), float(t[2])
+        if tag:
+            wall_check[tag] = wall
         return dt, loop
 
     # ---- device-resident leg
@@ -292,7 +304,7 @@ def main():
     if rank == 0:
         sampler.start()
     l0 = ctx.launch_count()
-    dt, loop = timed(args.steps, dev_step)
+    dt, loop = timed(args.steps, dev_step, 'device')
     launches = ctx.launch_count() - l0
     clocks = sampler.stop() if rank == 0 else None
     its = args.iters * args.steps
@@ -313,7 +325,7 @@ def main():
     s_h.copy_(u_h)
     timed(1, e2e_step)
     same = np.allclose(hist[:args.iters + 1], hist_dev, rtol=1e-12)   # first host step == device leg
-    dt_e, _ = timed(args.steps, e2e_step)
+    dt_e, _ = timed(args.steps, e2e_step, 'e2e')
     e2e_value = its / dt_e
     h2d = 8 * (f_h.numel() + g_h.numel() + s_h.numel())
     d2h = 8 * s_h.numel() + 8 * (args.iters + 1)
@@ -399,6 +411,9 @@ def main():
         "e2e": {"value": e2e_value, "unit": "iterations/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "history_matches_device_leg": bool(same)},
         "gpu_launches": int(launches), "clocks": clocks,
+        "timing": {"how": "CUDA events on the library's stream around the K steps, barrier + synchronize on both sides, max over ranks",
+                   "host_clock_ms_per_step": 1e3 * wall_check.get("device", 0.0) / args.steps,
+                   "host_clock_ms_per_step_e2e": 1e3 * wall_check.get("e2e", 0.0) / args.steps},
     }
     if minres_info:
         line["minres"] = minres_info

@@ -332,24 +332,33 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
 
     BpcgVecs V{u0.p, u1.p, d0.p, d1.p, w0.p, w1.p, s0.p, s1.p, z0.p, tmp0.p, tmp1.p, tmp2.p, tmp3.p, dM, n_u, n_p};
     const int vg = vec_grid(n_u + n_p, c.num_sms);
+    // row-partitioned with the peer-memory path: tmp1 and tmp4 are pushed together and the A and B SpMVs each wait
+    // for their landing area inside the kernel (interior chunks first), no wait/copy kernels in between
+    const bool fused_AB = A->halo && A->halo == B->halo && halo_fused_ok(c, A) && halo_fused_ok(c, B) && !(K || general_pre);
     auto launch_iteration = [&]() -> int {
-        NSB_CHECK(halo_exchange(c, BT->halo, s1.p));
         if (K || general_pre) {
+            NSB_CHECK(halo_exchange(c, BT->halo, s1.p));
             NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1cOp{S, As0.p, z0.p, s0.p, w0.p, tmp0.p}));
             NSB_CHECK(applyPre(tmp0.p, tmp1.p));                                                   // :209
             NSB_CHECK(vec_lincomb(c, tmp4.p, 1.0, tmp1.p, -1.0, s0.p, 0, nullptr, n_u));           // :212
             if (K) NSB_CHECK((cond_apply_A<1>(c, K, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused})));   // :210,:218,:222
             else NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
         } else {
-            NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p}));
+            NSB_CHECK(spmv_exchange_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p}));
             // tmp1 and tmp4 travel in the velocity halo, in one exchange when A and B share the halo plan
-            if (A->halo == B->halo) NSB_CHECK(halo_exchange2(c, A->halo, tmp1.p, tmp4.p));
-            else NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
-            NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
-            if (A->halo != B->halo) NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
+            if (fused_AB) {
+                NSB_CHECK(p2p_halo_push(c, A->halo, tmp1.p, tmp4.p));
+                NSB_CHECK(spmv_launch_halo_in<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}, 0));
+            } else {
+                if (A->halo == B->halo) NSB_CHECK(halo_exchange2(c, A->halo, tmp1.p, tmp4.p));
+                else NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
+                NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
+                if (A->halo != B->halo) NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
+            }
         }
         if (K || general_pre) NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
-        NSB_CHECK(spmv_launch<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, fused}));
+        if (fused_AB) NSB_CHECK(spmv_launch_halo_in<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, fused}, 1));
+        else NSB_CHECK(spmv_launch<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, fused}));
         if (!fused && !p2p_allreduce_then(c, &S->red[0], 2, BpcgPost{S, 0, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[0], 2));
             k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);

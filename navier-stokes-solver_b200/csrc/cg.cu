@@ -168,9 +168,8 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
     NSB_CUDA(cudaEventCreate(&e1));
     NSB_CUDA(cudaEventRecord(e0, c.stream));
     auto launch_iteration = [&]() -> int {
-        NSB_CHECK(halo_exchange(c, A->halo, b.s.p));
-        if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused})));
-        else NSB_CHECK(spmv_launch<1>(c, A, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused}));
+        if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused})));   // condensed: single-GPU
+        else NSB_CHECK(spmv_exchange_launch<1>(c, A, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused}));
         if (!fused && !p2p_allreduce_then(c, &S->red[0], 1, CgPost{S, 0, hist, alphas, betas})) {
             NSB_CHECK(allreduce_sum(c, &S->red[0], 1));
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist, alphas, betas);

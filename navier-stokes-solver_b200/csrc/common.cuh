@@ -156,6 +156,10 @@ struct SellData {
     // the same lists as runs of consecutive columns (used when the mean run is >= 8): first column, position
     int sell_nruns = 0;
     nsb::DevBuf<int32_t> sell_rstart, sell_rpos, sell_rptr;   // nruns, nruns + 1, nchunks + 1
+    // row-partitioned operators (sell.cu: build_halo_order): chunk visiting order with the chunks that touch no halo
+    // column first, so a SpMV can start before the neighbours' interface entries have landed (p2p.cuh: HaloIn)
+    nsb::DevBuf<int32_t> halo_order;
+    int halo_n_interior = -1;   // -1: no order built
 };
 
 }  // namespace nsb
@@ -313,6 +317,10 @@ int halo_exchange2(Context& c, nsb_halo_s* h, double* x1, double* x2);          
 int nccl_allgather_bytes(Context& c, const void* send_dev, void* recv_dev, size_t bytes_per_rank);   // dist.cu
 
 int build_sell(Context& c, nsb_mat_s* m);   // sell.cu
+int build_halo_order(Context& c, nsb_mat_s* m);   // sell.cu: (re)build the interior-first chunk order of every panel for m->halo
+// exchange steps of the fused path (p2p.cu): push only; the consuming SpMV waits inside the kernel
+int p2p_halo_push(Context& c, nsb_halo_s* h, double* x, double* x2 = nullptr);
+bool halo_fused_ok(const Context& c, const nsb_mat_s* m);   // p2p.cu: operator and exchange qualify for the in-kernel wait
 // y = P x for any preconditioner kind, device vectors (blockpre.cu); y must not alias x
 int pre_apply_device(Context& c, nsb_pre_s* p, const double* x, double* y);
 

@@ -210,7 +210,7 @@ int nsb_mat_set_halo(nsb_mat m, nsb_halo h) {
     if (h) NSB_REQUIRE(h->n_owned + h->n_halo == m->cols, "nsb_mat_set_halo: n_owned+n_halo = %lld but matrix has %lld columns",
                        (long long)(h->n_owned + h->n_halo), (long long)m->cols);
     m->halo = h;
-    return NSB_OK;
+    return m->ctx ? build_halo_order(*m->ctx, m) : NSB_OK;
 }
 
 }  // extern "C"

@@ -286,8 +286,7 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
         double* w_new = w[(j + 2) % 3].p;
         double* zc = z[j % 2].p;
         double* z_new = z[(j + 1) % 2].p;
-        NSB_CHECK(halo_exchange(c, K->halo, zc));
-        NSB_CHECK(spmv_launch<1>(c, K, zc, MinresK1Op{S, t.p, zc, fused}));
+        NSB_CHECK(spmv_exchange_launch<1>(c, K, zc, MinresK1Op{S, t.p, zc, fused}));
         if (!fused && !p2p_allreduce_then(c, &S->red[0], 1, MinresPost{S, 0, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[0], 1));
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);

@@ -364,6 +364,33 @@ void p2p_halo_destroy(nsb_halo_s* h) {
     h->p2p = nullptr;
 }
 
+int p2p_halo_push(Context& c, nsb_halo_s* h, double* x, double* x2) {
+    P2PHalo* P = h->p2p;
+    if (P->dev.nnb == 0) return NSB_OK;
+    k_halo_push<<<P->push_grid, kBlock, 0, c.stream>>>(P->dev, x, x2);
+    c.launches++;
+    NSB_CUDA(cudaGetLastError());
+    return NSB_OK;
+}
+
+// View for a SpMV that reads the halo entries of vector `area` (0: x, 1: x2 of the last push) from the landing buffer.
+HaloIn p2p_halo_in(const nsb_halo_s* h, int area, const int* order, int n_interior) {
+    const HaloDev& D = h->p2p->dev;
+    return HaloIn{D.my_ready, D.seq, D.my_land + (area ? D.land2 : 0), h->n_owned, D.nnb, order, n_interior};
+}
+
+bool halo_fused_ok(const Context& c, const nsb_mat_s* m) {
+    static int enabled = -1;
+    if (enabled < 0) {
+        const char* e = getenv("NSB_HALO_FUSED");
+        enabled = (e && atoi(e) == 0) ? 0 : 1;
+    }
+    if (!enabled || c.nranks <= 1 || !m->halo || !m->halo->p2p || m->panels.empty()) return false;
+    for (const auto& p : m->panels)
+        if (p->halo_n_interior < 0) return false;
+    return true;
+}
+
 int p2p_halo_exchange(Context& c, nsb_halo_s* h, double* x, double* x2) {
     P2PHalo* P = h->p2p;
     if (P->dev.nnb == 0) return NSB_OK;

@@ -30,6 +30,20 @@ struct P2PReduceView {
     int me, nranks;
 };
 
+// What a SpMV kernel needs to take the halo entries of x straight from this rank's landing buffer (spmv.cuh): the
+// kernel visits the chunks that touch no halo column first and polls the neighbours' ready flags only when it
+// reaches the others, so the wait for the exchange overlaps the interior rows and no copy kernel is launched.
+struct HaloIn {
+    const u64* my_ready;   // one word per neighbour, released by that neighbour's k_halo_push
+    const u64* seq;        // number of the exchange pushed last on this stream
+    const double* land;    // landing area of the vector being multiplied
+    int64_t n_owned;       // columns >= n_owned are halo entries, in landing-buffer order
+    int nnb;
+    const int* order;      // chunk visiting order of the panel, interior chunks first
+    int n_interior;
+};
+struct NoHaloIn {};
+
 struct NoPost {
     __device__ void operator()() const {}
 };
@@ -67,6 +81,7 @@ __global__ void k_p2p_allreduce(P2PReduceView R, double* vals, int count, Post p
 }
 
 P2PReduceView p2p_reduce_view(Context& c);   // p2p.cu
+HaloIn p2p_halo_in(const nsb_halo_s* h, int area, const int* order, int n_interior);   // p2p.cu
 
 // Sum `count` (<= kArSlots) doubles over the ranks and run `post` on the result in the same kernel.  Returns false
 // (nothing launched) when the context has no peer-memory path: the caller then uses allreduce_sum + its own kernel.

@@ -167,6 +167,21 @@ static int ilog2(int64_t v) {
     return l;
 }
 
+// Nonzeros a chunk should hold.  kSellTargetNnz on large panels (the staging of x amortises best); a panel with few
+// chunks per resident block (a 1/8 slab of the 20M-dof system has ~1.4 chunks of B per block) gets smaller chunks so
+// that the persistent grid's last round is not mostly idle.  NSB_SELL_TARGET_NNZ overrides (tuning sweeps).
+static double sell_target_nnz(int64_t nnz, int num_sms) {
+    const char* env = getenv("NSB_SELL_TARGET_NNZ");
+    if (env && atof(env) >= 256.0) return atof(env);
+    const char* per = getenv("NSB_SELL_CHUNKS_PER_BLOCK");
+    const double chunks_per_block = per ? atof(per) : 0.0;   // 0: fixed target
+    if (chunks_per_block <= 0.0) return kSellTargetNnz;
+    double t = (double)nnz / ((double)num_sms * NSB_SELL_MINBLOCKS * chunks_per_block);
+    if (t > kSellTargetNnz) t = kSellTargetNnz;
+    if (t < 3000.0) t = 3000.0;
+    return t;
+}
+
 static int pick_lanes_per_row(double mean) {
     const char* env = getenv("NSB_SELL_T");
     if (env) {
@@ -201,7 +216,8 @@ static int build_sell_panel(Context& c, nsb_mat_s* m, int64_t row0, int64_t rows
     const int T = pick_lanes_per_row(mean);
     const int rps = 32 / T;
     const int minlog = ilog2((int64_t)rps * kSellWarps);   // at least one slice per warp
-    double want = kSellTargetNnz / (mean > 1.0 ? mean : 1.0);
+    const double target_nnz = sell_target_nnz(nnz, c.num_sms);
+    double want = target_nnz / (mean > 1.0 ? mean : 1.0);
     int log2R = ilog2((int64_t)(want * 1.41421356));        // nearest power of two
     const char* envR = getenv("NSB_SELL_LOG2R");
     if (envR) log2R = atoi(envR);
@@ -365,6 +381,47 @@ static int build_sell_panel(Context& c, nsb_mat_s* m, int64_t row0, int64_t rows
     return NSB_OK;
 }
 
+// ---- interior-first chunk order of a row-partitioned operator ---------------------------------------------
+// A chunk needs the halo exchange iff its largest distinct column is a halo column (>= n_owned; the lists are ascending).
+__global__ void k_sell_halo_flags(const int* __restrict__ uptr, const int* __restrict__ ucol, int nchunks, int64_t n_owned,
+                                  int* __restrict__ flag) {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < nchunks; c += gridDim.x * blockDim.x) {
+        const int u0 = uptr[c], u1 = uptr[c + 1];
+        flag[c] = (u1 > u0 && (int64_t)ucol[u1 - 1] >= n_owned) ? 1 : 0;
+    }
+}
+
+int build_halo_order(Context& c, nsb_mat_s* m) {
+    for (auto& P : m->panels) {
+        P->halo_n_interior = -1;
+        P->halo_order.release();
+    }
+    if (!m->halo || m->panels.empty()) return NSB_OK;
+    for (auto& P : m->panels) {
+        const int nc = P->sell_nchunks;
+        if (nc < 1) continue;
+        DevBuf<int> flag;
+        NSB_CHECK(flag.alloc(nc));
+        k_sell_halo_flags<<<(nc + kBlock - 1) / kBlock, kBlock, 0, c.stream>>>(P->sell_uptr.p, P->sell_ucol.p, nc, m->halo->n_owned, flag.p);
+        NSB_CUDA(cudaGetLastError());
+        std::vector<int> hf(nc), order(nc);
+        NSB_CUDA(cudaMemcpyAsync(hf.data(), flag.p, sizeof(int) * (size_t)nc, cudaMemcpyDeviceToHost, c.stream));
+        NSB_CUDA(cudaStreamSynchronize(c.stream));
+        int k = 0;
+        for (int i = 0; i < nc; ++i)
+            if (!hf[i]) order[k++] = i;
+        const int n_int = k;
+        for (int i = 0; i < nc; ++i)
+            if (hf[i]) order[k++] = i;
+        NSB_CHECK(P->halo_order.alloc(nc));
+        NSB_CUDA(cudaMemcpy(P->halo_order.p, order.data(), sizeof(int) * (size_t)nc, cudaMemcpyHostToDevice));
+        P->halo_n_interior = n_int;
+        if (getenv("NSB_SELL_DEBUG"))
+            fprintf(stderr, "[sell] halo order: %d of %d chunks touch halo columns\n", nc - n_int, nc);
+    }
+    return NSB_OK;
+}
+
 // Build the SELL-LX companion of m, one panel per entry of m->panel_splits (default: the whole matrix).  Leaves
 // m->panels empty when the operator is small or any panel does not qualify (the CSR-vector kernel then runs).
 int build_sell(Context& c, nsb_mat_s* m) {
@@ -389,7 +446,7 @@ int build_sell(Context& c, nsb_mat_s* m) {
         }
         m->panels.push_back(std::move(S));
     }
-    return NSB_OK;
+    return m->halo ? build_halo_order(c, m) : NSB_OK;
 }
 
 }  // namespace nsb

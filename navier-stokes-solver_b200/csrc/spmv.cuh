@@ -19,7 +19,10 @@
 
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "common.cuh"
+#include "p2p.cuh"
 
 namespace nsb {
 
@@ -177,11 +180,25 @@ __device__ __forceinline__ unsigned int ld_stream_b32(const void* p) {
     return r;
 }
 
-template <int T, int NS, class RowOp>
+// x[c] for the staging phase.  Row-partitioned operators with the in-kernel wait (HaloIn) take the halo columns
+// from the landing buffer the neighbours store into (coherent loads: the data arrived while this kernel ran).
+template <class HI>
+__device__ __forceinline__ double ld_x(const double* __restrict__ x, const HI& H, int c) {
+    if constexpr (!std::is_same<HI, NoHaloIn>::value) {
+        if (c >= H.n_owned) return __ldcv(H.land + (c - H.n_owned));
+    }
+    return __ldg(x + c);
+}
+
+template <int T, int NS, class RowOp, class HI>
 __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kernel(SellView S, const double* __restrict__ x, RowOp op,
-                                                               double* partials, unsigned int* ticket) {
+                                                               double* partials, unsigned int* ticket, HI H) {
     extern __shared__ double smem[];
     if (op.skip()) return;
+    constexpr bool HALO = !std::is_same<HI, NoHaloIn>::value;
+    u64 exch = 0;
+    bool landed = false;
+    if constexpr (HALO) exch = *H.seq;   // written by k_halo_push, earlier in the stream
     double* sx = smem;
     double* sy = smem + S.cap;
     unsigned int* soff = reinterpret_cast<unsigned int*>(sy + S.R);
@@ -193,7 +210,20 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
     for (int k = 0; k < NSA; ++k) acc[k] = 0.0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-    for (int chunk = blockIdx.x; chunk < S.nchunks; chunk += gridDim.x) {
+    for (int ci = blockIdx.x; ci < S.nchunks; ci += gridDim.x) {
+        int chunk = ci;
+        if constexpr (HALO) {
+            chunk = __ldg(H.order + ci);
+            if (ci >= H.n_interior && !landed) {
+                // first chunk with halo columns: the neighbours' entries of this exchange must have landed.  The
+                // barrier below orders the other threads of the block behind these acquires.
+                if (threadIdx.x < H.nnb) {
+                    while (ld_acquire_sys(H.my_ready + threadIdx.x) < exch) {
+                    }
+                }
+                landed = true;
+            }
+        }
         const int u0 = __ldg(S.uptr + chunk);
         const int nu = __ldg(S.uptr + chunk + 1) - u0;
         __syncthreads();   // previous chunk: gathers done with sx, epilogue done with sy
@@ -223,7 +253,7 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
 #pragma unroll
                         for (int q = 0; q < 2; ++q)
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) v[q][j] = (l + 32 * j < len[q]) ? __ldg(x + cs[q] + l + 32 * j) : 0.0;
+                            for (int j = 0; j < 4; ++j) v[q][j] = (l + 32 * j < len[q]) ? ld_x(x, H, cs[q] + l + 32 * j) : 0.0;
 #pragma unroll
                         for (int q = 0; q < 2; ++q)
 #pragma unroll
@@ -239,7 +269,7 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
 #pragma unroll
             for (int k = 0; k < 4; ++k) c[k] = (i + k * kSellBlock < nu) ? __ldg(S.ucol + u0 + i + k * kSellBlock) : 0;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) v[k] = (i + k * kSellBlock < nu) ? __ldg(x + c[k]) : 0.0;
+            for (int k = 0; k < 4; ++k) v[k] = (i + k * kSellBlock < nu) ? ld_x(x, H, c[k]) : 0.0;
 #pragma unroll
             for (int k = 0; k < 4; ++k)
                 if (i + k * kSellBlock < nu) sx[i + k * kSellBlock] = v[k];
@@ -303,40 +333,40 @@ inline size_t sell_smem_bytes(const SellData* m) {
     return sizeof(double) * ((size_t)m->sell_cap + m->sell_R) + sizeof(unsigned int) * ((size_t)nsl + 2);
 }
 
-template <int T, int NS, class RowOp>
-int spmv_sell_launch_t(Context& c, const SellData* m, const double* x, RowOp op) {
+template <int T, int NS, class RowOp, class HI>
+int spmv_sell_launch_t(Context& c, const SellData* m, const double* x, RowOp op, HI H) {
     static bool attr_set = false;        // per instantiation
     static size_t cached_smem = ~(size_t)0;
     static int cached_bps = 0;
     const size_t smem = sell_smem_bytes(m);
     if (!attr_set) {
-        NSB_CUDA(cudaFuncSetAttribute(spmv_sell_kernel<T, NS, RowOp>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSellMaxSmem));
+        NSB_CUDA(cudaFuncSetAttribute(spmv_sell_kernel<T, NS, RowOp, HI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSellMaxSmem));
         attr_set = true;
     }
     if (smem != cached_smem) {
         int b = 0;
-        NSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, spmv_sell_kernel<T, NS, RowOp>, kSellBlock, smem));
+        NSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, spmv_sell_kernel<T, NS, RowOp, HI>, kSellBlock, smem));
         cached_bps = b > 0 ? b : 1;
         cached_smem = smem;
     }
     int grid = c.num_sms * cached_bps;
     if (grid > m->sell_nchunks) grid = m->sell_nchunks;
     if (grid > c.max_grid) grid = c.max_grid;
-    spmv_sell_kernel<T, NS, RowOp><<<grid, kSellBlock, smem, c.stream>>>(sell_view_of(m), x, op, c.partials, c.ticket);
+    spmv_sell_kernel<T, NS, RowOp, HI><<<grid, kSellBlock, smem, c.stream>>>(sell_view_of(m), x, op, c.partials, c.ticket, H);
     c.launches++;
     NSB_CUDA(cudaGetLastError());
     return NSB_OK;
 }
 
-template <int NS, class RowOp>
-int spmv_sell_panel(Context& c, const SellData* m, const double* x, RowOp op) {
+template <int NS, class RowOp, class HI = NoHaloIn>
+int spmv_sell_panel(Context& c, const SellData* m, const double* x, RowOp op, HI H = HI{}) {
     switch (m->sell_T) {
-        case 1: return spmv_sell_launch_t<1, NS, RowOp>(c, m, x, op);
-        case 2: return spmv_sell_launch_t<2, NS, RowOp>(c, m, x, op);
-        case 4: return spmv_sell_launch_t<4, NS, RowOp>(c, m, x, op);
-        case 8: return spmv_sell_launch_t<8, NS, RowOp>(c, m, x, op);
-        case 16: return spmv_sell_launch_t<16, NS, RowOp>(c, m, x, op);
-        default: return spmv_sell_launch_t<32, NS, RowOp>(c, m, x, op);
+        case 1: return spmv_sell_launch_t<1, NS, RowOp, HI>(c, m, x, op, H);
+        case 2: return spmv_sell_launch_t<2, NS, RowOp, HI>(c, m, x, op, H);
+        case 4: return spmv_sell_launch_t<4, NS, RowOp, HI>(c, m, x, op, H);
+        case 8: return spmv_sell_launch_t<8, NS, RowOp, HI>(c, m, x, op, H);
+        case 16: return spmv_sell_launch_t<16, NS, RowOp, HI>(c, m, x, op, H);
+        default: return spmv_sell_launch_t<32, NS, RowOp, HI>(c, m, x, op, H);
     }
 }
 
@@ -390,6 +420,37 @@ int spmv_launch(Context& c, const nsb_mat_s* m, const double* x, RowOp op) {
     c.launches++;
     NSB_CUDA(cudaGetLastError());
     return NSB_OK;
+}
+
+// SpMV of a row-partitioned SELL operator whose halo entries were PUSHED (p2p_halo_push) but not yet waited for: the
+// kernel takes them from landing area `area` and waits for the neighbours inside (requires halo_fused_ok(c, m)).
+template <int NS, class RowOp>
+int spmv_launch_halo_in(Context& c, const nsb_mat_s* m, const double* x, RowOp op, int area) {
+    const size_t np = m->panels.size();
+    for (size_t k = 0; k < np; ++k) {
+        const SellData* P = m->panels[k].get();
+        const HaloIn H = p2p_halo_in(m->halo, area, P->halo_order.p, P->halo_n_interior);
+        if constexpr (NS > 0) {
+            if (np > 1) {
+                NSB_CHECK((spmv_sell_panel<NS, ChainOp<RowOp, NS>, HaloIn>(c, P, x, ChainOp<RowOp, NS>{op, c.chain, k == 0, k + 1 == np}, H)));
+                continue;
+            }
+        }
+        NSB_CHECK((spmv_sell_panel<NS, RowOp, HaloIn>(c, P, x, op, H)));
+    }
+    return NSB_OK;
+}
+
+// The operator's halo exchange followed by its SpMV.  With the peer-memory path and SELL storage: push + SpMV with
+// the wait inside the kernel; otherwise exchange (push + wait/copy kernels, or NCCL) + SpMV.
+template <int NS, class RowOp>
+int spmv_exchange_launch(Context& c, const nsb_mat_s* m, double* x, RowOp op) {
+    if (halo_fused_ok(c, m)) {
+        NSB_CHECK(p2p_halo_push(c, m->halo, x));
+        return spmv_launch_halo_in<NS>(c, m, x, op, 0);
+    }
+    NSB_CHECK(halo_exchange(c, m->halo, x));
+    return spmv_launch<NS>(c, m, x, op);
 }
 
 // y = M x

@@ -69,6 +69,11 @@ class Context:
     def launch_count(self):
         return int(self._lib.nsb_ctx_launch_count(self.h))
 
+    def stream(self):
+        """Raw ``cudaStream_t`` every kernel of this context is launched on (for CUDA-event timing from the
+        caller: ``torch.cuda.ExternalStream(ctx.stream())``)."""
+        return int(self._lib.nsb_ctx_stream(self.h) or 0)
+
     def set_graphs(self, enabled):
         _lib.check(self._lib.nsb_ctx_set_graphs(self.h, int(bool(enabled))), "nsb_ctx_set_graphs")
 

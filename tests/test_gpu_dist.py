@@ -20,12 +20,15 @@ def _free_port():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("sell", ["0", "200000"])
-def test_two_rank_bpcg_and_minres_match_single_gpu(sell):
+@pytest.mark.parametrize("sell,fused_halo", [("0", "1"), ("0", "0"), ("200000", "1")])
+def test_two_rank_bpcg_and_minres_match_single_gpu(sell, fused_halo):
+    """sell = NSB_SELL_MIN_NNZ ("0": every operator in SELL-LX storage, "200000": these small ones stay CSR);
+    fused_halo = NSB_HALO_FUSED ("1": interface entries are pushed and the SELL SpMV waits for them inside the kernel,
+    interior chunks first; "0": push + wait/copy kernels before the SpMV)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
-    env = dict(os.environ, NSB_SELL_MIN_NNZ=sell)
+    env = dict(os.environ, NSB_SELL_MIN_NNZ=sell, NSB_HALO_FUSED=fused_halo)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "dist_worker.py")]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
