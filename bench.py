@@ -304,8 +304,14 @@ def main():
     if rank == 0:
         sampler.start()
     l0 = ctx.launch_count()
+    ctx.sync_stats(reset=True)
     dt, loop = timed(args.steps, dev_step, 'device')
     launches = ctx.launch_count() - l0
+    sync_stats = ctx.sync_stats()
+    if world > 1 and any(v["count"] for v in sync_stats.values()):   # -DNSB_SYNC_STATS builds (tools/sync_stats.sh)
+        print("SYNCSTATS " + json.dumps({"rank": rank, "loop_s": loop, "iterations": args.iters * args.steps,
+                                         "us_per_iteration": {k: 1e-3 * v["ns"] / (args.iters * args.steps) for k, v in sync_stats.items()},
+                                         "counts": {k: v["count"] for k, v in sync_stats.items()}}), file=sys.stderr, flush=True)
     clocks = sampler.stop() if rank == 0 else None
     its = args.iters * args.steps
     value = its / dt

@@ -73,6 +73,10 @@ NSB_API int nsb_ctx_sync(nsb_ctx ctx);
 NSB_API void* nsb_ctx_stream(nsb_ctx ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches claim) */
 NSB_API int64_t nsb_ctx_launch_count(nsb_ctx ctx);
+/* diagnostic, row-partitioned contexts: nanoseconds the exchange kernels spent polling peer flags, and how often
+ * ([0,1] scalar all-reduce, [2,3] halo push waiting for "consumed", [4,5] SpMV waiting for the halo, [6,7] wait/copy
+ * kernel).  All zero unless the library was built with -DNSB_SYNC_STATS (tools/sync_stats.sh). */
+NSB_API int nsb_ctx_sync_stats(nsb_ctx ctx, uint64_t out[16], int reset);
 /* capture the per-iteration kernel sequence in CUDA graphs (default on for single-GPU contexts and for
  * row-partitioned contexts whose exchanges run over NVLink peer memory; NSB_P2P=0 forces the NCCL path) */
 NSB_API int nsb_ctx_set_graphs(nsb_ctx ctx, int enabled);

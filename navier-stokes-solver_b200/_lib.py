@@ -29,6 +29,7 @@ SIGNATURES = {
     "nsb_ctx_sync": (C.c_int, [c_ctx]),
     "nsb_ctx_stream": (C.c_void_p, [c_ctx]),
     "nsb_ctx_launch_count": (C.c_int64, [c_ctx]),
+    "nsb_ctx_sync_stats": (C.c_int, [c_ctx, C.POINTER(C.c_uint64), C.c_int]),
     "nsb_ctx_set_graphs": (C.c_int, [c_ctx, C.c_int]),
     "nsb_csr_create": (C.c_int, [c_ctx, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, P(c_mat)]),
     "nsb_csr_transpose": (C.c_int, [c_ctx, c_mat, P(c_mat)]),

@@ -377,8 +377,6 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
         return NSB_OK;
     };
 
-    int* h_flags = (int*)c.h_mail;
-    h_flags[0] = 0;
     const int chunk = (n_u + n_p) < 200000 ? 16 : 4;   // iterations in flight between host checks
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t gexec = nullptr;
@@ -397,24 +395,20 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
         }
         if (rc == NSB_OK) NSB_CUDA(cudaGraphInstantiate(&gexec, graph, 0));
     }
-    int launched = 0;
-    while (rc == NSB_OK && launched < maxsteps) {
-        if (gexec) {
-            cudaError_t ge = cudaGraphLaunch(gexec, c.stream);
-            if (ge != cudaSuccess) {
-                set_error("nsb_bpcg: graph launch failed: %s", cudaGetErrorString(ge));
-                rc = NSB_ERR_CUDA;
+    if (rc == NSB_OK)
+        rc = drive_batches(c, &S->stop, maxsteps, chunk, [&]() -> int {
+            if (gexec) {
+                cudaError_t ge = cudaGraphLaunch(gexec, c.stream);
+                if (ge != cudaSuccess) {
+                    set_error("nsb_bpcg: graph launch failed: %s", cudaGetErrorString(ge));
+                    return NSB_ERR_CUDA;
+                }
+                c.launches += graph_launches;
+                return NSB_OK;
             }
-            c.launches += graph_launches;
-        } else {
-            for (int j = 0; j < chunk && rc == NSB_OK; ++j) rc = launch_iteration();
-        }
-        launched += chunk;
-        if (rc != NSB_OK) break;
-        NSB_CUDA(cudaMemcpyAsync(h_flags, &S->stop, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
-        NSB_CUDA(cudaStreamSynchronize(c.stream));
-        if (h_flags[0]) break;
-    }
+            for (int j = 0; j < chunk; ++j) NSB_CHECK(launch_iteration());
+            return NSB_OK;
+        });
     if (gexec) cudaGraphExecDestroy(gexec);
     if (graph) cudaGraphDestroy(graph);
     NSB_CHECK(rc);

@@ -211,17 +211,27 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
     }
     CgState hs;
     memset(&hs, 0, sizeof(hs));
-    int launched = 0;
-    while (rc == NSB_OK && launched < maxsteps) {
+    auto batch = [&]() -> int {
         if (gexec) {
             if (cudaGraphLaunch(gexec, c.stream) != cudaSuccess) {
                 set_error("cg: graph launch failed");
-                rc = NSB_ERR_CUDA;
+                return NSB_ERR_CUDA;
             }
             c.launches += graph_launches;
-        } else {
-            for (int j = 0; j < chunk && rc == NSB_OK; ++j) rc = launch_iteration();
+            return NSB_OK;
         }
+        for (int j = 0; j < chunk; ++j) NSB_CHECK(launch_iteration());
+        return NSB_OK;
+    };
+    int launched = 0;
+    // plain CG: one batch ahead of the stop test (common.cuh).  Lanczos keeps the batch-by-batch loop: its host-side
+    // Ritz-value test decides after every batch and the number of steps it takes is part of the result.
+    if (rc == NSB_OK && !host_check) {
+        rc = drive_batches(c, &S->stop, maxsteps, chunk, batch);
+        launched = maxsteps;
+    }
+    while (rc == NSB_OK && launched < maxsteps) {
+        rc = batch();
         launched += chunk;
         if (rc != NSB_OK) break;
         NSB_CUDA(cudaMemcpyAsync(&hs, S, sizeof(CgState), cudaMemcpyDeviceToHost, c.stream));

@@ -90,6 +90,9 @@ struct Context {
     void* nccl_comm = nullptr;
     NcclApi* nccl = nullptr;
     P2PReduce* p2p = nullptr;   // peer-memory scalar all-reduce (p2p.cu); null: NCCL all-reduce
+    // -DNSB_SYNC_STATS builds only (tools/sync_stats.sh): nanoseconds spent polling peer flags and poll counts,
+    // [0,1] all-reduce  [2,3] push waiting for "consumed"  [4,5] SpMV block 0 waiting for the halo  [6,7] wait/copy kernel
+    unsigned long long* sync_stats = nullptr;
 };
 
 // device buffer with RAII (host-side owner).  alloc(): cudaMalloc, for long-lived storage (operators, IPC
@@ -315,6 +318,45 @@ void p2p_halo_destroy(nsb_halo_s* h);
 int p2p_halo_exchange(Context& c, nsb_halo_s* h, double* x, double* x2 = nullptr);   // x2: a second vector in the same exchange
 int halo_exchange2(Context& c, nsb_halo_s* h, double* x1, double* x2);             // dist.cu
 int nccl_allgather_bytes(Context& c, const void* send_dev, void* recv_dev, size_t bytes_per_rank);   // dist.cu
+
+// Host side of an iteration loop whose stop test runs on the device.  `batch()` enqueues `batch_iters` iterations
+// (one graph launch, or plain launches); batches are enqueued until the device-side stop flag is seen set or
+// `maxsteps` iterations are in the stream.  The flag of batch k is read only after batch k+1 has been enqueued:
+// the kernels of an iteration are no-ops once the flag is set, so running one batch ahead costs a few empty
+// launches at the end of a solve and the device never idles on the host round trip in between.  In row-partitioned
+// runs every rank reads the same flag values in the same order, so all ranks enqueue the same number of batches.
+template <class Batch>
+int drive_batches(Context& c, const int* stop_dev, int maxsteps, int batch_iters, Batch batch) {
+    volatile int* h_flags = (volatile int*)c.h_mail;   // pinned
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    NSB_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+    NSB_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+    int rc = NSB_OK, launched = 0, slot = 0;
+    bool stop = false, have_prev = false;
+    cudaError_t e = cudaSuccess;
+    while (rc == NSB_OK && e == cudaSuccess && !stop && launched < maxsteps) {
+        rc = batch();
+        if (rc != NSB_OK) break;
+        launched += batch_iters;
+        h_flags[slot] = 0;
+        e = cudaMemcpyAsync((void*)&h_flags[slot], stop_dev, sizeof(int), cudaMemcpyDeviceToHost, c.stream);
+        if (e == cudaSuccess) e = cudaEventRecord(ev[slot], c.stream);
+        if (e == cudaSuccess && have_prev) {
+            e = cudaEventSynchronize(ev[slot ^ 1]);
+            stop = h_flags[slot ^ 1] != 0;
+        }
+        have_prev = true;
+        slot ^= 1;
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+    cudaEventDestroy(ev[0]);
+    cudaEventDestroy(ev[1]);
+    if (rc == NSB_OK && e != cudaSuccess) {
+        set_error("iteration loop: %s", cudaGetErrorString(e));
+        rc = NSB_ERR_CUDA;
+    }
+    return rc;
+}
 
 int build_sell(Context& c, nsb_mat_s* m);   // sell.cu
 int build_halo_order(Context& c, nsb_mat_s* m);   // sell.cu: (re)build the interior-first chunk order of every panel for m->halo

@@ -58,6 +58,10 @@ int ctx_init(Context& c, int device) {
     NSB_CUDA(cudaMallocHost((void**)&c.h_mail, sizeof(double) * 64));
     NSB_CUDA(cudaMalloc((void**)&c.d_mail, sizeof(double) * 64));
     NSB_CUDA(cudaMemset(c.d_mail, 0, sizeof(double) * 64));
+#ifdef NSB_SYNC_STATS
+    NSB_CUDA(cudaMalloc((void**)&c.sync_stats, sizeof(unsigned long long) * 16));
+    NSB_CUDA(cudaMemset(c.sync_stats, 0, sizeof(unsigned long long) * 16));
+#endif
     return NSB_OK;
 }
 
@@ -121,6 +125,7 @@ int nsb_ctx_destroy(nsb_ctx ctx) {
     if (c.ticket) cudaFree(c.ticket);
     if (c.chain) cudaFree(c.chain);
     if (c.d_mail) cudaFree(c.d_mail);
+    if (c.sync_stats) cudaFree(c.sync_stats);
     if (c.h_mail) cudaFreeHost(c.h_mail);
     if (c.stream) cudaStreamDestroy(c.stream);
     delete ctx;
@@ -136,6 +141,18 @@ int nsb_ctx_sync(nsb_ctx ctx) {
 void* nsb_ctx_stream(nsb_ctx ctx) { return ctx ? (void*)ctx->c.stream : nullptr; }
 
 int64_t nsb_ctx_launch_count(nsb_ctx ctx) { return ctx ? ctx->c.launches : 0; }
+
+int nsb_ctx_sync_stats(nsb_ctx ctx, uint64_t out[16], int reset) {
+    NSB_REQUIRE(ctx && out, "nsb_ctx_sync_stats: NULL argument");
+    memset(out, 0, sizeof(uint64_t) * 16);
+    Context& c = ctx->c;
+    if (!c.sync_stats) return NSB_OK;   // library built without -DNSB_SYNC_STATS
+    NSB_CUDA(cudaSetDevice(c.device));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    NSB_CUDA(cudaMemcpy(out, c.sync_stats, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost));
+    if (reset) NSB_CUDA(cudaMemset(c.sync_stats, 0, sizeof(uint64_t) * 16));
+    return NSB_OK;
+}
 
 int nsb_ctx_set_graphs(nsb_ctx ctx, int enabled) {
     NSB_REQUIRE(ctx, "nsb_ctx_set_graphs: NULL context");

@@ -305,8 +305,6 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
         return NSB_OK;
     };
 
-    int* h_flags = (int*)c.h_mail;  // pinned: [stop, nhist]
-    h_flags[0] = 0;
     const int period = 6;
     const int reps = n < 200000 ? 4 : 1;   // iterations in flight between host checks: period * reps
     cudaGraph_t graph = nullptr;
@@ -326,26 +324,22 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
         }
         if (rc == NSB_OK) NSB_CUDA(cudaGraphInstantiate(&gexec, graph, 0));
     }
-    int launched = 0;
-    while (rc == NSB_OK && launched < maxsteps) {
-        for (int r = 0; r < reps && launched < maxsteps && rc == NSB_OK; ++r) {
-            if (gexec) {
-                cudaError_t ge = cudaGraphLaunch(gexec, c.stream);
-                if (ge != cudaSuccess) {
-                    set_error("nsb_minres: graph launch failed: %s", cudaGetErrorString(ge));
-                    rc = NSB_ERR_CUDA;
+    if (rc == NSB_OK)
+        rc = drive_batches(c, &S->stop, maxsteps, period * reps, [&]() -> int {
+            for (int r = 0; r < reps; ++r) {
+                if (gexec) {
+                    cudaError_t ge = cudaGraphLaunch(gexec, c.stream);
+                    if (ge != cudaSuccess) {
+                        set_error("nsb_minres: graph launch failed: %s", cudaGetErrorString(ge));
+                        return NSB_ERR_CUDA;
+                    }
+                    c.launches += graph_launches;
+                } else {
+                    for (int j = 0; j < period; ++j) NSB_CHECK(launch_iteration(j));
                 }
-                c.launches += graph_launches;
-            } else {
-                for (int j = 0; j < period && rc == NSB_OK; ++j) rc = launch_iteration(j);
             }
-            launched += period;
-        }
-        if (rc != NSB_OK) break;
-        NSB_CUDA(cudaMemcpyAsync(h_flags, &S->stop, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
-        NSB_CUDA(cudaStreamSynchronize(c.stream));
-        if (h_flags[0]) break;
-    }
+            return NSB_OK;
+        });
     if (gexec) cudaGraphExecDestroy(gexec);
     if (graph) cudaGraphDestroy(graph);
     NSB_CHECK(rc);

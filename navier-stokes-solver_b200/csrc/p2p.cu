@@ -113,7 +113,7 @@ struct P2PReduce {
 
 P2PReduceView p2p_reduce_view(Context& c) {
     P2PReduce* P = c.p2p;
-    return P2PReduceView{P->peer_box.p, P->peer_flag.p, P->my_box, P->my_flag, P->seq, c.rank, c.nranks};
+    return P2PReduceView{P->peer_box.p, P->peer_flag.p, P->my_box, P->my_flag, P->seq, c.rank, c.nranks, c.sync_stats};
 }
 
 int p2p_reduce_init(Context& c) {
@@ -183,6 +183,7 @@ struct HaloDev {
     const u64* my_consumed;     // written by the neighbours
     u64* seq;
     unsigned int* ticket;
+    u64* stats;   // NSB_SYNC_STATS builds; else null
 };
 
 struct P2PHalo {
@@ -201,8 +202,10 @@ __global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* _
     // until they have moved out what I pushed last time
     if (blockIdx.x == 0 && threadIdx.x < H.nnb) st_release_sys(H.peer_consumed[threadIdx.x], e - 1);
     if (threadIdx.x < H.nnb) {
+        NSB_STATS_T0();
         while (ld_acquire_sys(H.my_consumed + threadIdx.x) < e - 1) {
         }
+        if (blockIdx.x == 0 && threadIdx.x == 0) NSB_STATS_ADD(H.stats, 2);
     }
     __syncthreads();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < H.n_send; i += (int64_t)gridDim.x * blockDim.x) {
@@ -230,8 +233,10 @@ __global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* _
 __global__ void __launch_bounds__(kBlock) k_halo_wait_copy(HaloDev H, double* __restrict__ tail, double* __restrict__ tail2) {
     const u64 e = *H.seq;   // the push of this exchange is earlier in the stream
     if (threadIdx.x < H.nnb) {
+        NSB_STATS_T0();
         while (ld_acquire_sys(H.my_ready + threadIdx.x) < e) {
         }
+        if (blockIdx.x == 0 && threadIdx.x == 0) NSB_STATS_ADD(H.stats, 6);
     }
     __syncthreads();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < H.n_halo; i += (int64_t)gridDim.x * blockDim.x)
@@ -339,6 +344,7 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     D.my_consumed = flags + nnb;
     D.seq = flags + 2 * nnb;
     D.ticket = (unsigned int*)(flags + 2 * nnb + 1);
+    D.stats = c.sync_stats;
     auto grid_for = [&](int64_t n) {
         int64_t g = (n + (int64_t)kBlock * 4 - 1) / ((int64_t)kBlock * 4);
         if (g < 1) g = 1;
@@ -376,7 +382,7 @@ int p2p_halo_push(Context& c, nsb_halo_s* h, double* x, double* x2) {
 // View for a SpMV that reads the halo entries of vector `area` (0: x, 1: x2 of the last push) from the landing buffer.
 HaloIn p2p_halo_in(const nsb_halo_s* h, int area, const int* order, int n_interior) {
     const HaloDev& D = h->p2p->dev;
-    return HaloIn{D.my_ready, D.seq, D.my_land + (area ? D.land2 : 0), h->n_owned, D.nnb, order, n_interior};
+    return HaloIn{D.my_ready, D.seq, D.my_land + (area ? D.land2 : 0), h->n_owned, D.nnb, order, n_interior, D.stats};
 }
 
 bool halo_fused_ok(const Context& c, const nsb_mat_s* m) {

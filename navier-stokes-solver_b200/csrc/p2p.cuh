@@ -21,6 +21,25 @@ __device__ __forceinline__ void st_sys_f64(double* p, double v) {
     asm volatile("st.volatile.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
 
+#ifdef NSB_SYNC_STATS
+__device__ __forceinline__ u64 global_ns() {
+    u64 t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define NSB_STATS_T0() const u64 stats_t0__ = global_ns()
+#define NSB_STATS_ADD(ptr, slot)                                        \
+    do {                                                                \
+        if (ptr) {                                                      \
+            atomicAdd((ptr) + (slot), global_ns() - stats_t0__);        \
+            atomicAdd((ptr) + (slot) + 1, 1ull);                        \
+        }                                                               \
+    } while (0)
+#else
+#define NSB_STATS_T0() do { } while (0)
+#define NSB_STATS_ADD(ptr, slot) do { } while (0)
+#endif
+
 struct P2PReduceView {
     double* const* peer_box;   // per rank: that rank's mailbox
     u64* const* peer_flag;     // per rank: that rank's flag array
@@ -28,6 +47,7 @@ struct P2PReduceView {
     const u64* my_flag;
     u64* seq;
     int me, nranks;
+    u64* stats;   // NSB_SYNC_STATS builds; else null
 };
 
 // What a SpMV kernel needs to take the halo entries of x straight from this rank's landing buffer (spmv.cuh): the
@@ -41,6 +61,7 @@ struct HaloIn {
     int nnb;
     const int* order;      // chunk visiting order of the panel, interior chunks first
     int n_interior;
+    u64* stats;            // NSB_SYNC_STATS builds; else null
 };
 struct NoHaloIn {};
 
@@ -64,10 +85,14 @@ __global__ void k_p2p_allreduce(P2PReduceView R, double* vals, int count, Post p
         for (int k = 0; k < count; ++k) st_sys_f64(dst + k, mine[k]);
         __threadfence_system();
         st_release_sys(R.peer_flag[r] + R.me, e);
+    }
+    NSB_STATS_T0();
+    if (r < R.nranks) {
         while (ld_acquire_sys(R.my_flag + r) < e) {
         }
     }
     __syncthreads();
+    if (threadIdx.x == 0) NSB_STATS_ADD(R.stats, 0);
     if (threadIdx.x < count) {
         double s = 0.0;
         for (int q = 0; q < R.nranks; ++q) s += __ldcv(R.my_box + ((size_t)par * R.nranks + q) * kArSlots + threadIdx.x);

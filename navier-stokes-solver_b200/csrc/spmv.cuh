@@ -218,8 +218,10 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
                 // first chunk with halo columns: the neighbours' entries of this exchange must have landed.  The
                 // barrier below orders the other threads of the block behind these acquires.
                 if (threadIdx.x < H.nnb) {
+                    NSB_STATS_T0();
                     while (ld_acquire_sys(H.my_ready + threadIdx.x) < exch) {
                     }
+                    if (blockIdx.x == 0 && threadIdx.x == 0) NSB_STATS_ADD(H.stats, 4);
                 }
                 landed = true;
             }

@@ -69,6 +69,14 @@ class Context:
     def launch_count(self):
         return int(self._lib.nsb_ctx_launch_count(self.h))
 
+    def sync_stats(self, reset=False):
+        """Diagnostic (library built with -DNSB_SYNC_STATS, else zeros): (nanoseconds, polls) the exchange kernels of
+        this rank spent waiting on peer flags, by kind."""
+        out = (C.c_uint64 * 16)()
+        _lib.check(self._lib.nsb_ctx_sync_stats(self.h, out, int(bool(reset))), "nsb_ctx_sync_stats")
+        names = ["allreduce", "push_wait_consumed", "spmv_wait_halo", "wait_copy"]
+        return {n: {"ns": int(out[2 * i]), "count": int(out[2 * i + 1])} for i, n in enumerate(names)}
+
     def stream(self):
         """Raw ``cudaStream_t`` every kernel of this context is launched on (for CUDA-event timing from the
         caller: ``torch.cuda.ExternalStream(ctx.stream())``)."""
