@@ -158,6 +158,7 @@ struct BpcgVecs {
 
 __global__ void __launch_bounds__(kBlock) k_bpcg_b4(BpcgState* S, BpcgVecs V, double* hist, double* partials,
                                                     unsigned int* ticket, bool fused) {
+    pdl_enter();
     if (S->stop) return;
     const double a = S->alpha;
     double acc[1] = {0.0};
@@ -193,6 +194,7 @@ __global__ void __launch_bounds__(kBlock) k_bpcg_b4(BpcgState* S, BpcgVecs V, do
 
 // s1 = beta s1 + w1 (:240-241, pressure part; the velocity part rides in B1's epilogue of the next pass)
 __global__ void __launch_bounds__(kBlock) k_bpcg_b5(const BpcgState* S, BpcgVecs V) {
+    pdl_enter();
     if (S->stop) return;
     const double b = S->beta;
     for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < V.n_p; j += (int64_t)gridDim.x * blockDim.x)
@@ -364,14 +366,14 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
             k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
             c.launches++;
         }
-        k_bpcg_b4<<<vg, kBlock, 0, c.stream>>>(S, V, hist.p, c.partials, c.ticket, fused);
+        NSB_CUDA(launch_k(c, k_bpcg_b4, vg, kBlock, 0, S, V, hist.p, c.partials, c.ticket, fused));
         c.launches++;
         if (!fused && !p2p_allreduce_then(c, &S->red[2], 1, BpcgPost{S, 1, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[2], 1));
             k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;
         }
-        k_bpcg_b5<<<vec_grid(n_p > 0 ? n_p : 1, c.num_sms), kBlock, 0, c.stream>>>(S, V);
+        NSB_CUDA(launch_k(c, k_bpcg_b5, vec_grid(n_p > 0 ? n_p : 1, c.num_sms), kBlock, 0, S, V));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;

@@ -79,6 +79,7 @@ __global__ void __launch_bounds__(kBlock) k_cg_c2(CgState* S, double* __restrict
                                                   const double* __restrict__ dinv, double* __restrict__ w, int64_t n,
                                                   double* hist, double* betas, double* partials, unsigned int* ticket,
                                                   bool fused) {
+    pdl_enter();
     if (S->stop) return;
     const double a = S->alpha;
     double acc[1] = {0.0};
@@ -100,6 +101,7 @@ __global__ void __launch_bounds__(kBlock) k_cg_c2(CgState* S, double* __restrict
 
 __global__ void __launch_bounds__(kBlock) k_cg_c3(const CgState* S, double* __restrict__ s, const double* __restrict__ w,
                                                   int64_t n) {
+    pdl_enter();
     if (S->stop) return;
     const double b = S->beta;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -175,7 +177,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist, alphas, betas);
             c.launches++;
         }
-        k_cg_c2<<<vg, kBlock, 0, c.stream>>>(S, u, b.s.p, b.d.p, b.q.p, dinv, b.w.p, n, hist, betas, c.partials, c.ticket, fused);
+        NSB_CUDA(launch_k(c, k_cg_c2, vg, kBlock, 0, S, u, b.s.p, b.d.p, b.q.p, dinv, b.w.p, n, hist, betas, c.partials, c.ticket, fused));
         c.launches++;
         if (general_pre) {   // w = P d, then <w,d>
             NSB_CHECK(pre_apply_device(c, pre, b.d.p, b.w.p));
@@ -187,7 +189,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
             c.launches++;
         }
-        k_cg_c3<<<vg, kBlock, 0, c.stream>>>(S, b.s.p, b.w.p, n);
+        NSB_CUDA(launch_k(c, k_cg_c3, vg, kBlock, 0, S, b.s.p, b.w.p, n));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;

@@ -77,6 +77,10 @@ struct Context {
     cudaStream_t stream = nullptr;
     int64_t launches = 0;
     bool use_graphs = true;
+    // programmatic dependent launch (NSB_PDL, default on): the kernels of an iteration loop are launched with
+    // cudaLaunchAttributeProgrammaticStreamSerialization, so the next kernel's blocks become resident while the
+    // previous kernel drains, fetch their immutable matrix structure and park in griddepcontrol.wait
+    bool pdl = true;
     // reduction scratch: per-block partials and the arrival ticket of the last-block pattern
     double* partials = nullptr;  // kMaxRed * max grid
     double* chain = nullptr;     // kMaxRed: totals handed from one row panel's launch to the next (spmv.cuh: ChainOp)
@@ -233,6 +237,24 @@ namespace nsb {
 // ---------------------------------------------------------------------------------------------
 #ifdef __CUDACC__
 
+// Programmatic dependent launch (sm_90+).  pdl_trigger(): the next kernel in the stream may be scheduled as soon as
+// every block of this grid has executed it (its blocks then fill the SMs this grid frees while it drains).
+// pdl_wait(): returns when the preceding grid has completed and its writes are visible; everything a kernel reads or
+// writes that an earlier kernel may have written comes after it.  EVERY block of a kernel launched through
+// launch_k() executes pdl_wait() before it exits, so "this grid completed" implies "its predecessor completed".
+// Both are no-ops in a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// The fence behind the wait compiles to MEMBAR + CCTL.IVALL: a block that became resident early shares its SM's L1 with
+// blocks of the two previous grids, which may have pulled in lines (plain or ld.global.nc loads) that the previous
+// grid overwrote afterwards; the invalidate makes the loads behind the wait miss L1 like they do after an ordinary
+// kernel boundary.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n\tfence.acq_rel.gpu;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() {
+    pdl_trigger();
+    pdl_wait();
+}
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -293,6 +315,25 @@ __device__ __forceinline__ bool grid_sum(double (&v)[NS], double* partials, unsi
 }
 
 #endif  // __CUDACC__
+
+#ifdef __CUDACC__
+// Launch of a kernel that takes part in the programmatic-dependent-launch protocol above (it calls pdl_wait()
+// before touching mutable data).  With c.pdl off this is an ordinary stream-ordered launch.
+template <class... KArgs, class... Args>
+inline cudaError_t launch_k(Context& c, void (*kern)(KArgs...), int grid, int block, size_t smem, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid, 1, 1);
+    cfg.blockDim = dim3((unsigned)block, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = c.stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = c.pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // host-side utilities implemented in context.cu / vecops.cu

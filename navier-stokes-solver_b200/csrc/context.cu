@@ -1,5 +1,6 @@
 // context.cu -- context lifetime, error text, host<->device staging.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -42,6 +43,10 @@ int ctx_init(Context& c, int device) {
     cudaDeviceProp prop;
     NSB_CUDA(cudaGetDeviceProperties(&prop, device));
     c.num_sms = prop.multiProcessorCount;
+    {
+        const char* e = getenv("NSB_PDL");
+        c.pdl = (e ? atoi(e) != 0 : true) && prop.major >= 9;
+    }
     NSB_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
     {   // keep freed work vectors in the device's default pool between solves
         cudaMemPool_t pool;

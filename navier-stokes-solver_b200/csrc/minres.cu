@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(kBlock) k_minres_k2(MinresState* S, const doub
                                                       const double* __restrict__ dinv, double* __restrict__ vh_new,
                                                       double* __restrict__ zh_new, int64_t n, double* hist,
                                                       double* partials, unsigned int* ticket, bool fused_scalar) {
+    pdl_enter();
     if (S->stop) return;
     const double ig = S->ig;
     const double c1 = S->delta * ig;            // delta * v      = delta * ig * vh
@@ -150,6 +151,7 @@ __global__ void __launch_bounds__(kBlock) k_minres_k2(MinresState* S, const doub
 __global__ void __launch_bounds__(kBlock) k_minres_k3(const MinresState* S, const double* __restrict__ zh,
                                                       const double* __restrict__ w_old, const double* __restrict__ w,
                                                       double* __restrict__ w_new, double* __restrict__ u, int64_t n) {
+    pdl_enter();
     if (S->done) return;
     const double igz = S->igz, a3 = S->a3, a2 = S->a2, a1inv = S->a1inv, cu = S->coef_u;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -292,14 +294,14 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
             c.launches++;
         }
-        k_minres_k2<<<vg, kBlock, 0, c.stream>>>(S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, fused);
+        NSB_CUDA(launch_k(c, k_minres_k2, vg, kBlock, 0, S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, fused));
         c.launches++;
         if (!fused && !p2p_allreduce_then(c, &S->red[1], 1, MinresPost{S, 1, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;
         }
-        k_minres_k3<<<vg, kBlock, 0, c.stream>>>(S, zc, w_old, wc, w_new, u.p, n);
+        NSB_CUDA(launch_k(c, k_minres_k3, vg, kBlock, 0, S, zc, w_old, wc, w_new, u.p, n));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;

@@ -49,6 +49,7 @@ inline CsrView view_of(const nsb_mat_s* m) { return CsrView{m->rows, m->rowptr.p
 template <int TPR, int NS, class RowOp>
 __global__ void __launch_bounds__(kBlock) spmv_csrvec_kernel(CsrView A, const double* __restrict__ x, RowOp op,
                                                              double* partials, unsigned int* ticket, int chunk_steps) {
+    pdl_enter();
     if (op.skip()) return;
     constexpr int NSA = NS > 0 ? NS : 1;
     constexpr int GPB = kBlock / TPR;  // row groups per block
@@ -194,8 +195,35 @@ template <int T, int NS, class RowOp, class HI>
 __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kernel(SellView S, const double* __restrict__ x, RowOp op,
                                                                double* partials, unsigned int* ticket, HI H) {
     extern __shared__ double smem[];
-    if (op.skip()) return;
     constexpr bool HALO = !std::is_same<HI, NoHaloIn>::value;
+    pdl_trigger();
+    // Before the dependency wait: pull the structure and the head of the value / index streams of this block's first
+    // chunk towards L2.  None of it is ever written after the operator was built, so it may be fetched while the
+    // previous kernel of the stream is still draining; x, the row-op operands and the reduction scratch come after.
+    if (blockIdx.x < S.nchunks) {
+        int chunk0 = blockIdx.x;
+        if constexpr (HALO) chunk0 = __ldg(H.order + blockIdx.x);
+        const unsigned int* offp = S.off + (size_t)chunk0 * S.nsl;
+        const unsigned int b0 = __ldg(offp), b1 = __ldg(offp + S.nsl);   // pair-blocks: 512 B of values, 128 B of indices each
+        const size_t line = threadIdx.x;                                 // one 128-byte line per thread
+        if (line * 8 < (size_t)(b1 - b0) * 32) prefetch_l2(S.vals + (size_t)b0 * 64 + line * 16);
+        if (line < 64 && line * 32 < (size_t)(b1 - b0) * 32) prefetch_l2(S.lcol + (size_t)b0 * 64 + line * 64);
+        if (line * 32 <= (size_t)S.nsl) prefetch_l2(offp + line * 32);
+        if (line * 64 < (size_t)S.R) prefetch_l2(S.perm + ((size_t)chunk0 << S.log2R) + line * 64);
+        if (threadIdx.x == 0) prefetch_l2(S.uptr + chunk0);
+        if (S.rptr != nullptr) {
+            const int q0 = __ldg(S.rptr + chunk0), q1 = __ldg(S.rptr + chunk0 + 1);
+            if ((int)line * 32 < q1 - q0) {
+                prefetch_l2(S.rstart + q0 + line * 32);
+                prefetch_l2(S.rpos + q0 + line * 32);
+            }
+        } else {
+            const int q0 = __ldg(S.uptr + chunk0), q1 = __ldg(S.uptr + chunk0 + 1);
+            for (int i = (int)line * 32; i < q1 - q0; i += kSellBlock * 32) prefetch_l2(S.ucol + q0 + i);
+        }
+    }
+    pdl_wait();
+    if (op.skip()) return;
     u64 exch = 0;
     bool landed = false;
     if constexpr (HALO) exch = *H.seq;   // written by k_halo_push, earlier in the stream
@@ -354,9 +382,8 @@ int spmv_sell_launch_t(Context& c, const SellData* m, const double* x, RowOp op,
     int grid = c.num_sms * cached_bps;
     if (grid > m->sell_nchunks) grid = m->sell_nchunks;
     if (grid > c.max_grid) grid = c.max_grid;
-    spmv_sell_kernel<T, NS, RowOp, HI><<<grid, kSellBlock, smem, c.stream>>>(sell_view_of(m), x, op, c.partials, c.ticket, H);
+    NSB_CUDA(launch_k(c, spmv_sell_kernel<T, NS, RowOp, HI>, grid, kSellBlock, smem, sell_view_of(m), x, op, c.partials, c.ticket, H));
     c.launches++;
-    NSB_CUDA(cudaGetLastError());
     return NSB_OK;
 }
 
@@ -413,14 +440,13 @@ int spmv_launch(Context& c, const nsb_mat_s* m, const double* x, RowOp op) {
     const int grid = spmv_grid(m->rows, m->threads_per_row, c.num_sms);
     const int cs = spmv_chunk_steps(m->rows, m->threads_per_row, c.num_sms);
     switch (m->threads_per_row) {
-        case 2: spmv_csrvec_kernel<2, NS, RowOp><<<grid, kBlock, 0, c.stream>>>(A, x, op, c.partials, c.ticket, cs); break;
-        case 4: spmv_csrvec_kernel<4, NS, RowOp><<<grid, kBlock, 0, c.stream>>>(A, x, op, c.partials, c.ticket, cs); break;
-        case 8: spmv_csrvec_kernel<8, NS, RowOp><<<grid, kBlock, 0, c.stream>>>(A, x, op, c.partials, c.ticket, cs); break;
-        case 16: spmv_csrvec_kernel<16, NS, RowOp><<<grid, kBlock, 0, c.stream>>>(A, x, op, c.partials, c.ticket, cs); break;
-        default: spmv_csrvec_kernel<32, NS, RowOp><<<grid, kBlock, 0, c.stream>>>(A, x, op, c.partials, c.ticket, cs); break;
+        case 2: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<2, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        case 4: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<4, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        case 8: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<8, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        case 16: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<16, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        default: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<32, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
     }
     c.launches++;
-    NSB_CUDA(cudaGetLastError());
     return NSB_OK;
 }
 
