@@ -85,17 +85,22 @@ struct BpcgB1Op {
     double* __restrict__ tmp1;
     double* __restrict__ tmp4;
     __device__ bool skip() const { return S->stop != 0; }
-    __device__ void row(int64_t i, double ax, double (&)[1]) const {
-        const double as0 = S->beta * As0[i] + z0[i];
+    struct Pre {
+        double as0, z, d, s, w;
+    };
+    __device__ Pre load(int64_t i) const { return Pre{As0[i], z0[i], dA[i], s0[i], w0[i]}; }
+    __device__ void apply(int64_t i, double ax, const Pre& p, double (&)[1]) const {
+        const double as0 = S->beta * p.as0 + p.z;
         const double t0 = as0 + ax;
-        const double t1 = S->k * (dA[i] * t0);
-        const double sn = S->beta * s0[i] + w0[i];   // :240-241 of the previous pass, velocity part (s0 = w0 before
+        const double t1 = S->k * (p.d * t0);
+        const double sn = S->beta * p.s + p.w;       // :240-241 of the previous pass, velocity part (s0 = w0 before
         s0[i] = sn;                                  // the first pass and beta = 0 then, so this is the identity)
         As0[i] = as0;
         tmp0[i] = t0;
         tmp1[i] = t1;
         tmp4[i] = t1 - sn;
     }
+    __device__ void row(int64_t i, double ax, double (&acc)[1]) const { apply(i, ax, load(i), acc); }
     __device__ void finish(const double (&)[1]) const {}
 };
 
@@ -124,10 +129,15 @@ struct BpcgB2Op {
     const double* __restrict__ s0;
     bool fused;
     __device__ bool skip() const { return S->stop != 0; }
-    __device__ void row(int64_t i, double ax, double (&acc)[1]) const {
+    struct Pre {
+        double s, t0;
+    };
+    __device__ Pre load(int64_t i) const { return Pre{s0[i], tmp0[i]}; }
+    __device__ void apply(int64_t i, double ax, const Pre& p, double (&acc)[1]) const {
         tmp2[i] = ax;
-        acc[0] = fma(s0[i], ax - tmp0[i], acc[0]);
+        acc[0] = fma(p.s, ax - p.t0, acc[0]);
     }
+    __device__ void row(int64_t i, double ax, double (&acc)[1]) const { apply(i, ax, load(i), acc); }
     __device__ void finish(const double (&tot)[1]) const {
         if (fused) S->as_part = tot[0];
         else S->red[0] = tot[0];
@@ -140,10 +150,15 @@ struct BpcgB3Op {
     const double* __restrict__ s1;
     bool fused;
     __device__ bool skip() const { return S->stop != 0; }
-    __device__ void row(int64_t j, double ax, double (&acc)[1]) const {
+    struct Pre {
+        double s;
+    };
+    __device__ Pre load(int64_t j) const { return Pre{s1[j]}; }
+    __device__ void apply(int64_t j, double ax, const Pre& p, double (&acc)[1]) const {
         tmp3[j] = ax;
-        acc[0] = fma(s1[j], ax, acc[0]);
+        acc[0] = fma(p.s, ax, acc[0]);
     }
+    __device__ void row(int64_t j, double ax, double (&acc)[1]) const { apply(j, ax, load(j), acc); }
     __device__ void finish(const double (&tot)[1]) const {
         if (fused) bpcg_after_as(S, S->as_part, tot[0]);
         else S->red[1] = tot[0];
@@ -366,14 +381,14 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
             k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
             c.launches++;
         }
-        NSB_CUDA(launch_k(c, k_bpcg_b4, vg, kBlock, 0, S, V, hist.p, c.partials, c.ticket, fused));
+        NSB_CUDA(launch_k(c, 2, k_bpcg_b4, vg, kBlock, 0, S, V, hist.p, c.partials, c.ticket, fused));
         c.launches++;
         if (!fused && !p2p_allreduce_then(c, &S->red[2], 1, BpcgPost{S, 1, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[2], 1));
             k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;
         }
-        NSB_CUDA(launch_k(c, k_bpcg_b5, vec_grid(n_p > 0 ? n_p : 1, c.num_sms), kBlock, 0, S, V));
+        NSB_CUDA(launch_k(c, 2, k_bpcg_b5, vec_grid(n_p > 0 ? n_p : 1, c.num_sms), kBlock, 0, S, V));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;

@@ -64,10 +64,15 @@ struct CgC1Op {
     double* alphas;
     bool fused;
     __device__ bool skip() const { return S->stop != 0; }
-    __device__ void row(int64_t i, double ax, double (&acc)[1]) const {
+    struct Pre {
+        double s;
+    };
+    __device__ Pre load(int64_t i) const { return Pre{s[i]}; }
+    __device__ void apply(int64_t i, double ax, const Pre& p, double (&acc)[1]) const {
         q[i] = ax;
-        acc[0] = fma(s[i], ax, acc[0]);
+        acc[0] = fma(p.s, ax, acc[0]);
     }
+    __device__ void row(int64_t i, double ax, double (&acc)[1]) const { apply(i, ax, load(i), acc); }
     __device__ void finish(const double (&tot)[1]) const {
         if (fused) cg_after_as(S, tot[0], alphas);
         else S->red[0] = tot[0];
@@ -177,7 +182,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist, alphas, betas);
             c.launches++;
         }
-        NSB_CUDA(launch_k(c, k_cg_c2, vg, kBlock, 0, S, u, b.s.p, b.d.p, b.q.p, dinv, b.w.p, n, hist, betas, c.partials, c.ticket, fused));
+        NSB_CUDA(launch_k(c, 2, k_cg_c2, vg, kBlock, 0, S, u, b.s.p, b.d.p, b.q.p, dinv, b.w.p, n, hist, betas, c.partials, c.ticket, fused));
         c.launches++;
         if (general_pre) {   // w = P d, then <w,d>
             NSB_CHECK(pre_apply_device(c, pre, b.d.p, b.w.p));
@@ -189,7 +194,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
             c.launches++;
         }
-        NSB_CUDA(launch_k(c, k_cg_c3, vg, kBlock, 0, S, b.s.p, b.w.p, n));
+        NSB_CUDA(launch_k(c, 2, k_cg_c3, vg, kBlock, 0, S, b.s.p, b.w.p, n));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;

@@ -80,7 +80,12 @@ struct Context {
     // programmatic dependent launch (NSB_PDL, default on): the kernels of an iteration loop are launched with
     // cudaLaunchAttributeProgrammaticStreamSerialization, so the next kernel's blocks become resident while the
     // previous kernel drains, fetch their immutable matrix structure and park in griddepcontrol.wait
-    bool pdl = true;
+    bool pdl = false;
+    int pdl_mask = 3;    // NSB_PDL = 1 | 2 | 3: bit 0 SpMV kernels, bit 1 vector kernels launched with the attribute
+    // SELL kernel options (NSB_SELL_FLAGS): 1 trigger dependents at entry, 2 prefetch the first chunk's structure
+    // before the dependency wait (both only matter under NSB_PDL), 4 epilogue with the operand loads of two rows per
+    // thread in flight
+    int sell_flags = 7;
     // reduction scratch: per-block partials and the arrival ticket of the last-block pattern
     double* partials = nullptr;  // kMaxRed * max grid
     double* chain = nullptr;     // kMaxRed: totals handed from one row panel's launch to the next (spmv.cuh: ChainOp)
@@ -320,7 +325,7 @@ __device__ __forceinline__ bool grid_sum(double (&v)[NS], double* partials, unsi
 // Launch of a kernel that takes part in the programmatic-dependent-launch protocol above (it calls pdl_wait()
 // before touching mutable data).  With c.pdl off this is an ordinary stream-ordered launch.
 template <class... KArgs, class... Args>
-inline cudaError_t launch_k(Context& c, void (*kern)(KArgs...), int grid, int block, size_t smem, Args&&... args) {
+inline cudaError_t launch_k(Context& c, int kind, void (*kern)(KArgs...), int grid, int block, size_t smem, Args&&... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid, 1, 1);
     cfg.blockDim = dim3((unsigned)block, 1, 1);
@@ -330,7 +335,7 @@ inline cudaError_t launch_k(Context& c, void (*kern)(KArgs...), int grid, int bl
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = c.pdl ? 1 : 0;
+    cfg.numAttrs = (c.pdl && (c.pdl_mask & kind)) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 #endif

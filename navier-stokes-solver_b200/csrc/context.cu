@@ -45,7 +45,12 @@ int ctx_init(Context& c, int device) {
     c.num_sms = prop.multiProcessorCount;
     {
         const char* e = getenv("NSB_PDL");
-        c.pdl = (e ? atoi(e) != 0 : true) && prop.major >= 9;
+        c.pdl = (e ? atoi(e) != 0 : false) && prop.major >= 9;
+        if (e && atoi(e) > 0) c.pdl_mask = atoi(e) & 3;
+        const char* f = getenv("NSB_SELL_FLAGS");
+        if (f) c.sell_flags = atoi(f);
+        const char* g = getenv("NSB_GRAPHS");
+        if (g) c.use_graphs = atoi(g) != 0;
     }
     NSB_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
     {   // keep freed work vectors in the device's default pool between solves

@@ -110,10 +110,15 @@ struct MinresK1Op {
         if (st && blockIdx.x == 0 && threadIdx.x == 0) S->done = 1;
         return st;
     }
-    __device__ void row(int64_t r, double ax, double (&acc)[1]) const {
+    struct Pre {
+        double z;
+    };
+    __device__ Pre load(int64_t r) const { return Pre{zh[r]}; }
+    __device__ void apply(int64_t r, double ax, const Pre& p, double (&acc)[1]) const {
         t[r] = ax;
-        acc[0] = fma(ax, zh[r], acc[0]);
+        acc[0] = fma(ax, p.z, acc[0]);
     }
+    __device__ void row(int64_t r, double ax, double (&acc)[1]) const { apply(r, ax, load(r), acc); }
     __device__ void finish(const double (&tot)[1]) const {
         if (fused_scalar) minres_after_delta(S, tot[0]);
         else S->red[0] = tot[0];
@@ -294,14 +299,14 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
             c.launches++;
         }
-        NSB_CUDA(launch_k(c, k_minres_k2, vg, kBlock, 0, S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, fused));
+        NSB_CUDA(launch_k(c, 2, k_minres_k2, vg, kBlock, 0, S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, fused));
         c.launches++;
         if (!fused && !p2p_allreduce_then(c, &S->red[1], 1, MinresPost{S, 1, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;
         }
-        NSB_CUDA(launch_k(c, k_minres_k3, vg, kBlock, 0, S, zc, w_old, wc, w_new, u.p, n));
+        NSB_CUDA(launch_k(c, 2, k_minres_k3, vg, kBlock, 0, S, zc, w_old, wc, w_new, u.p, n));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;

@@ -163,6 +163,7 @@ struct SellView {
     int64_t row0;   // first operator row of the panel
     int R, log2R, nchunks, nsl;   // rows per chunk, chunks, slices per chunk (R * T / 32)
     int cap;                      // staged x entries a chunk may need (max distinct columns, padded)
+    int sell_flags;               // Context::sell_flags
     const double* __restrict__ vals;
     const unsigned short* __restrict__ lcol;
     const unsigned int* __restrict__ off;      // per slice, in pair-blocks (64 elements)
@@ -191,16 +192,34 @@ __device__ __forceinline__ double ld_x(const double* __restrict__ x, const HI& H
     return __ldg(x + c);
 }
 
+// Optional parts of a RowOp the SELL kernel uses when present:
+//   Pre / load(i) / apply(i, ax, pre, acc)   row(i, ax, acc) == apply(i, ax, load(i), acc), split so that the epilogue
+//                          can have the operand loads of two rows per thread in flight before the first use (the
+//                          epilogue is latency-bound: +1.5 % BPCG iterations/s at 20M dofs, +2 % at 2.5M; touching the
+//                          operand lines with prefetch.global.L2 while x is staged was measured too and LOSES 1.3 %)
+template <class Op, class = void>
+struct has_load : std::false_type {};
+template <class Op>
+struct has_load<Op, std::void_t<typename Op::Pre>> : std::true_type {};
+template <class Op, class = void>
+struct pre_of {
+    using type = int;
+};
+template <class Op>
+struct pre_of<Op, std::void_t<typename Op::Pre>> {
+    using type = typename Op::Pre;
+};
+
 template <int T, int NS, class RowOp, class HI>
 __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kernel(SellView S, const double* __restrict__ x, RowOp op,
                                                                double* partials, unsigned int* ticket, HI H) {
     extern __shared__ double smem[];
     constexpr bool HALO = !std::is_same<HI, NoHaloIn>::value;
-    pdl_trigger();
+    if (S.sell_flags & 1) pdl_trigger();
     // Before the dependency wait: pull the structure and the head of the value / index streams of this block's first
     // chunk towards L2.  None of it is ever written after the operator was built, so it may be fetched while the
     // previous kernel of the stream is still draining; x, the row-op operands and the reduction scratch come after.
-    if (blockIdx.x < S.nchunks) {
+    if ((S.sell_flags & 2) && blockIdx.x < S.nchunks) {
         int chunk0 = blockIdx.x;
         if constexpr (HALO) chunk0 = __ldg(H.order + blockIdx.x);
         const unsigned int* offp = S.off + (size_t)chunk0 * S.nsl;
@@ -340,6 +359,21 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
         }
         __syncthreads();
         const int64_t r0 = (int64_t)chunk << S.log2R;
+        if constexpr (has_load<RowOp>::value) {
+            if (S.sell_flags & 4) {
+                using Pre = typename pre_of<RowOp>::type;
+                for (int t = threadIdx.x; t < S.R; t += 2 * kSellBlock) {
+                    const int64_t ra = r0 + t, rb = ra + kSellBlock;
+                    const bool va = ra < S.rows, vb = t + kSellBlock < S.R && rb < S.rows;
+                    Pre pa{}, pb{};
+                    if (va) pa = op.load(S.row0 + ra);
+                    if (vb) pb = op.load(S.row0 + rb);
+                    if (va) op.apply(S.row0 + ra, sy[t], pa, acc);
+                    if (vb) op.apply(S.row0 + rb, sy[t + kSellBlock], pb, acc);
+                }
+                continue;
+            }
+        }
         for (int t = threadIdx.x; t < S.R; t += kSellBlock) {
             const int64_t r = r0 + t;
             if (r < S.rows) op.row(S.row0 + r, sy[t], acc);
@@ -353,7 +387,7 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
 }
 
 inline SellView sell_view_of(const SellData* m) {
-    return SellView{m->nrows, m->row0, m->sell_R, m->sell_log2R, m->sell_nchunks, m->sell_R * m->sell_T / 32, m->sell_cap,
+    return SellView{m->nrows, m->row0, m->sell_R, m->sell_log2R, m->sell_nchunks, m->sell_R * m->sell_T / 32, m->sell_cap, 0,
                     m->sell_vals.p, m->sell_lcol.p, m->sell_off.p, m->sell_perm.p, m->sell_uptr.p, m->sell_ucol.p,
                     m->sell_nruns > 0 ? m->sell_rptr.p : nullptr, m->sell_rstart.p, m->sell_rpos.p};
 }
@@ -382,7 +416,9 @@ int spmv_sell_launch_t(Context& c, const SellData* m, const double* x, RowOp op,
     int grid = c.num_sms * cached_bps;
     if (grid > m->sell_nchunks) grid = m->sell_nchunks;
     if (grid > c.max_grid) grid = c.max_grid;
-    NSB_CUDA(launch_k(c, spmv_sell_kernel<T, NS, RowOp, HI>, grid, kSellBlock, smem, sell_view_of(m), x, op, c.partials, c.ticket, H));
+    SellView V = sell_view_of(m);
+    V.sell_flags = c.sell_flags;
+    NSB_CUDA(launch_k(c, 1, spmv_sell_kernel<T, NS, RowOp, HI>, grid, kSellBlock, smem, V, x, op, c.partials, c.ticket, H));
     c.launches++;
     return NSB_OK;
 }
@@ -408,6 +444,10 @@ struct ChainOp {
     int first, last;
     __device__ bool skip() const { return in.skip(); }
     __device__ void row(int64_t r, double ax, double (&acc)[NSA]) const { in.row(r, ax, acc); }
+    template <class I = Inner>
+    __device__ typename pre_of<I>::type load(int64_t r) const { return in.load(r); }
+    template <class P>
+    __device__ void apply(int64_t r, double ax, const P& p, double (&acc)[NSA]) const { in.apply(r, ax, p, acc); }
     __device__ void finish(const double (&tot)[NSA]) const {
         double t[NSA];
 #pragma unroll
@@ -419,6 +459,11 @@ struct ChainOp {
         }
     }
 };
+
+template <class Inner, int NSA>
+struct has_load<ChainOp<Inner, NSA>, void> : has_load<Inner> {};
+template <class Inner, int NSA>
+struct pre_of<ChainOp<Inner, NSA>, void> : pre_of<Inner> {};
 
 // Launch with the matrix's storage.  x must cover cols (+ halo tail when partitioned).
 template <int NS, class RowOp>
@@ -440,11 +485,11 @@ int spmv_launch(Context& c, const nsb_mat_s* m, const double* x, RowOp op) {
     const int grid = spmv_grid(m->rows, m->threads_per_row, c.num_sms);
     const int cs = spmv_chunk_steps(m->rows, m->threads_per_row, c.num_sms);
     switch (m->threads_per_row) {
-        case 2: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<2, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
-        case 4: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<4, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
-        case 8: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<8, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
-        case 16: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<16, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
-        default: NSB_CUDA(launch_k(c, spmv_csrvec_kernel<32, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        case 2: NSB_CUDA(launch_k(c, 1, spmv_csrvec_kernel<2, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        case 4: NSB_CUDA(launch_k(c, 1, spmv_csrvec_kernel<4, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        case 8: NSB_CUDA(launch_k(c, 1, spmv_csrvec_kernel<8, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        case 16: NSB_CUDA(launch_k(c, 1, spmv_csrvec_kernel<16, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
+        default: NSB_CUDA(launch_k(c, 1, spmv_csrvec_kernel<32, NS, RowOp>, grid, kBlock, 0, A, x, op, c.partials, c.ticket, cs)); break;
     }
     c.launches++;
     return NSB_OK;
