@@ -416,6 +416,9 @@ def main():
                      "other": {"spmv_B_gbs": B.spmv_bytes() / ms_B / 1e6, "spmv_BT_gbs": BTm.spmv_bytes() / ms_BT / 1e6}},
         "e2e": {"value": e2e_value, "unit": "iterations/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "history_matches_device_leg": bool(same)},
+        # residual-history fingerprint of the device leg: equal (to reduction-order rounding) at every N for the same --dofs
+        "history_checkpoints": {"err0": float(hist_dev[0]), "err_%d" % (args.iters // 2): float(hist_dev[args.iters // 2]),
+                                "err_%d" % args.iters: float(hist_dev[args.iters])},
         "gpu_launches": int(launches), "clocks": clocks,
         "timing": {"how": "CUDA events on the library's stream around the K steps, barrier + synchronize on both sides, max over ranks",
                    "host_clock_ms_per_step": 1e3 * wall_check.get("device", 0.0) / args.steps,

@@ -84,8 +84,8 @@ struct Context {
     int pdl_mask = 3;    // NSB_PDL = 1 | 2 | 3: bit 0 SpMV kernels, bit 1 vector kernels launched with the attribute
     // SELL kernel options (NSB_SELL_FLAGS): 1 trigger dependents at entry, 2 prefetch the first chunk's structure
     // before the dependency wait (both only matter under NSB_PDL), 4 epilogue with the operand loads of two rows per
-    // thread in flight
-    int sell_flags = 7;
+    // thread in flight, 8 x staged with cp.async, 16 the next chunk staged under the current chunk's epilogue
+    int sell_flags = 31;
     // reduction scratch: per-block partials and the arrival ticket of the last-block pattern
     double* partials = nullptr;  // kMaxRed * max grid
     double* chain = nullptr;     // kMaxRed: totals handed from one row panel's launch to the next (spmv.cuh: ChainOp)

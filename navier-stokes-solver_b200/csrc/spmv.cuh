@@ -182,6 +182,18 @@ __device__ __forceinline__ unsigned int ld_stream_b32(const void* p) {
     return r;
 }
 
+// 8-byte asynchronous copy global -> shared (LDGSTS through L1, like the __ldg it replaces) and the wait for all copies this
+// thread issued; the block barrier after the wait publishes them to the other threads
+__device__ __forceinline__ void cp_async_f64(double* smem_dst, const double* gmem_src) {
+    const unsigned int d = (unsigned int)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_b32(unsigned int* smem_dst, const unsigned int* gmem_src) {
+    const unsigned int d = (unsigned int)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // x[c] for the staging phase.  Row-partitioned operators with the in-kernel wait (HaloIn) take the halo columns
 // from the landing buffer the neighbours store into (coherent loads: the data arrived while this kernel ran).
 template <class HI>
@@ -257,6 +269,62 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
     for (int k = 0; k < NSA; ++k) acc[k] = 0.0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
+    // Asynchronous staging of one chunk (slice offsets and x entries): every copy global -> shared is a cp.async (LDGSTS)
+    // that occupies no register and nothing waits on, so a warp issues the copies of ALL its runs back to back and the
+    // chunk pays one memory latency for its x entries instead of one per pair of runs.
+    auto stage_async = [&](int ch) {
+        const int u0 = __ldg(S.uptr + ch);
+        for (int i = threadIdx.x; i <= S.nsl; i += kSellBlock) cp_async_b32(soff + i, S.off + (size_t)ch * S.nsl + i);
+        if (S.rptr != nullptr) {
+            const int r0 = __ldg(S.rptr + ch), r1 = __ldg(S.rptr + ch + 1);
+            for (int rb = r0 + warp; rb < r1; rb += 32 * kSellWarps) {
+                const int mine = rb + lane * kSellWarps;
+                const int cs_l = mine < r1 ? __ldg(S.rstart + mine) : 0;
+                const int p0_l = mine < r1 ? __ldg(S.rpos + mine) : 0;
+                const int p1_l = mine < r1 ? __ldg(S.rpos + mine + 1) : 0;
+                const int cnt = min(32, (r1 - rb + kSellWarps - 1) / kSellWarps);
+                for (int k = 0; k < cnt; ++k) {
+                    const int cs = __shfl_sync(0xffffffffu, cs_l, k);
+                    const int p0 = __shfl_sync(0xffffffffu, p0_l, k) - u0;
+                    const int len = __shfl_sync(0xffffffffu, p1_l, k) - u0 - p0;
+                    for (int l = lane; l < len; l += 32) {
+                        if constexpr (HALO) {
+                            // halo columns come from the landing buffer the neighbours store into: coherent loads, no L1
+                            if (cs + l >= H.n_owned) {
+                                sx[p0 + l] = __ldcv(H.land + (cs + l - H.n_owned));
+                                continue;
+                            }
+                        }
+                        cp_async_f64(sx + p0 + l, x + cs + l);
+                    }
+                }
+            }
+        } else {
+            const int nu = __ldg(S.uptr + ch + 1) - u0;
+            for (int i = threadIdx.x; i < nu; i += 4 * kSellBlock) {
+                int c[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) c[k] = (i + k * kSellBlock < nu) ? __ldg(S.ucol + u0 + i + k * kSellBlock) : 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (i + k * kSellBlock < nu) {
+                        if constexpr (HALO) {
+                            if (c[k] >= H.n_owned) {
+                                sx[i + k * kSellBlock] = __ldcv(H.land + (c[k] - H.n_owned));
+                                continue;
+                            }
+                        }
+                        cp_async_f64(sx + i + k * kSellBlock, x + c[k]);
+                    }
+            }
+        }
+    };
+    const bool async_stage = (S.sell_flags & 8) != 0;
+    // with bit 4 the next chunk of the block is staged right behind the compute phase, so its latency runs under the
+    // (latency-bound) row epilogue of the current chunk; one buffer is enough: the compute phase is done with sx
+    const bool pipelined = !HALO && async_stage && (S.sell_flags & 16);   // row-partitioned: the wait for the halo sits at the loop top
+    bool staged = false;   // this chunk's copies were issued during the previous chunk's epilogue
+
     for (int ci = blockIdx.x; ci < S.nchunks; ci += gridDim.x) {
         int chunk = ci;
         if constexpr (HALO) {
@@ -273,6 +341,12 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
                 landed = true;
             }
         }
+        if (staged) {
+            // nothing to issue
+        } else if (async_stage) {
+            __syncthreads();   // previous chunk: gathers done with sx, epilogue done with sy
+            stage_async(chunk);
+        } else {
         const int u0 = __ldg(S.uptr + chunk);
         const int nu = __ldg(S.uptr + chunk + 1) - u0;
         __syncthreads();   // previous chunk: gathers done with sx, epilogue done with sy
@@ -323,7 +397,9 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
             for (int k = 0; k < 4; ++k)
                 if (i + k * kSellBlock < nu) sx[i + k * kSellBlock] = v[k];
         }
-        __syncthreads();
+        }
+        if (async_stage) cp_async_wait_all();
+        __syncthreads();   // x and the slice offsets of this chunk are in shared memory; the previous epilogue is done with sy
         for (int base = 0, pass = 0; base < S.nsl; base += kSellWarps, ++pass) {
             // snake order over the length-sorted slices
             const int cnt = min(kSellWarps, S.nsl - base);
@@ -358,6 +434,13 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
             if ((lane & (T - 1)) == 0) sy[lr] = s;
         }
         __syncthreads();
+        staged = false;
+        if constexpr (!HALO) {
+            if (pipelined && ci + (int)gridDim.x < S.nchunks) {
+                stage_async(ci + (int)gridDim.x);
+                staged = true;
+            }
+        }
         const int64_t r0 = (int64_t)chunk << S.log2R;
         if constexpr (has_load<RowOp>::value) {
             if (S.sell_flags & 4) {

@@ -1,4 +1,4 @@
-# SELL epilogue variants (NSB_SELL_FLAGS bit 2: operand prefetch to L2 during staging, bit 3: two rows per thread in flight)
+# SELL kernel variants by NSB_SELL_FLAGS (bit 2: two epilogue rows in flight, bit 3: x staged with cp.async); FLAGS="7 15" selects the list
 mkdir -p gpurun_out
 B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --lanczos-steps 60"
 run() { # name, dofs, env...
@@ -15,7 +15,7 @@ except Exception as e:
 PY
 }
 for D in 20e6 2.55e6; do
-for F in 3 7 11 15 3 15; do
+for F in ${FLAGS:-7 15 7 15}; do
 run f${F}_$D $D NSB_SELL_FLAGS=$F
 done
 done
