@@ -393,11 +393,11 @@ def main():
         return
     # DRAM bytes per launch of the same kernel from the committed ncu --set full capture (never measured under this run)
     traffic, traffic_src = None, None
-    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_spmv_A_traffic.json")
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1c_spmv_A_traffic.json")
     if world == 1 and os.path.exists(tpath):
         tj = json.load(open(tpath))
         if tj.get("dofs") == int(n_u + n_p):
-            traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], "profiles/r1_spmv_A_traffic.json"
+            traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], "profiles/r1c_spmv_A_traffic.json"
     line = {
         "metric": "bpcg_krylov_iterations_per_s", "value": value, "unit": "iterations/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
