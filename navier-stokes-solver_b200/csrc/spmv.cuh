@@ -482,13 +482,14 @@ inline size_t sell_smem_bytes(const SellData* m) {
 
 template <int T, int NS, class RowOp, class HI>
 int spmv_sell_launch_t(Context& c, const SellData* m, const double* x, RowOp op, HI H) {
-    static bool attr_set = false;        // per instantiation
+    static unsigned long long attr_devices = 0;   // per instantiation: devices (bit = ordinal) the attribute was set on
     static size_t cached_smem = ~(size_t)0;
     static int cached_bps = 0;
     const size_t smem = sell_smem_bytes(m);
-    if (!attr_set) {
+    const unsigned long long dev_bit = 1ull << (c.device & 63);
+    if (!(attr_devices & dev_bit)) {   // function attributes are per device: a second context on another GPU sets its own
         NSB_CUDA(cudaFuncSetAttribute(spmv_sell_kernel<T, NS, RowOp, HI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSellMaxSmem));
-        attr_set = true;
+        attr_devices |= dev_bit;
     }
     if (smem != cached_smem) {
         int b = 0;
