@@ -179,9 +179,9 @@ def main():
     ap.add_argument("--lanczos-steps", type=int, default=1500)
     ap.add_argument("--no-minres", action="store_true")
     ap.add_argument("--minres-iters", type=int, default=60)
-    ap.add_argument("--solve-to-tol", type=float, default=0.0,
-                    help="also run one full BramblePasciakCG solve to this relative tolerance (the reference's call uses 1e-10, "
-                         "NavierStokesSIMPLE_iterative.py:397) and report time to tolerance; off by default")
+    ap.add_argument("--solve-to-tol", type=float, default=1e-10,
+                    help="after the timed legs, run one full BramblePasciakCG solve to this relative tolerance (the reference's call "
+                         "uses 1e-10, NavierStokesSIMPLE_iterative.py:397) and report time to tolerance (single-GPU runs; 0 = skip)")
     ap.add_argument("--solve-maxsteps", type=int, default=30000)
     args = ap.parse_args()
     if args.impl == "reference":
@@ -371,7 +371,7 @@ def main():
                        "spmv_K_ms": Kb.spmv_bench(warmup=20, reps=200), "spmv_K_format": Kb.format()}
         del Kb
     ttt = None
-    if args.solve_to_tol > 0:
+    if args.solve_to_tol > 0 and world == 1:
         th = np.zeros(args.solve_maxsteps + 2)
         tsol = u_start.clone()
         upd, secs, status = C.c_int(), C.c_double(), C.c_int()
@@ -380,12 +380,15 @@ def main():
         ps, _, _ = nsb.la.buffer_of(tsol)
         barrier()
         t0 = time.perf_counter()
-        _lib.check(lib.nsb_bpcg(ctx.h, A.h, B.h, BTm.h, pA.h, pM.h, k_scale, pf, pg, ps, args.solve_maxsteps, args.solve_to_tol,
-                                0, 1, 2, th.ctypes.data, C.byref(upd), C.byref(secs), C.byref(status)), "nsb_bpcg")
-        barrier()
-        ttt = {"tol": args.solve_to_tol, "rel_err": True, "iterations": upd.value, "loop_seconds": secs.value,
-               "call_seconds": time.perf_counter() - t0, "status": status.value,
-               "final_relative_error": float(th[upd.value] / th[0]) if th[0] > 0 else None}
+        try:   # an extra leg after the timed ones: a failure here is reported, it does not take the headline line down
+            _lib.check(lib.nsb_bpcg(ctx.h, A.h, B.h, BTm.h, pA.h, pM.h, k_scale, pf, pg, ps, args.solve_maxsteps, args.solve_to_tol,
+                                    0, 1, 2, th.ctypes.data, C.byref(upd), C.byref(secs), C.byref(status)), "nsb_bpcg")
+            barrier()
+            ttt = {"tol": args.solve_to_tol, "rel_err": True, "iterations": upd.value, "loop_seconds": secs.value,
+                   "call_seconds": time.perf_counter() - t0, "status": _lib.STATUS_NAMES.get(status.value, status.value),
+                   "final_relative_error": float(th[upd.value] / th[0]) if th[0] > 0 else None}
+        except Exception as ex:   # noqa: BLE001  (NsbError or a CUDA error surfaced by torch)
+            ttt = {"tol": args.solve_to_tol, "error": str(ex)[:200]}
         del tsol
     if rank != 0:
         if world > 1:

@@ -4,7 +4,7 @@ mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
 set -x
-B="python bench.py --steps 1 --warmup 1 --iters 8 --lanczos-steps 6 --no-cpu-baseline --minres-iters 6"
+B="python bench.py --steps 1 --warmup 1 --iters 8 --lanczos-steps 6 --no-cpu-baseline --minres-iters 6 --solve-to-tol 0"
 $B > gpurun_out/prof_plain.json 2> gpurun_out/prof_plain.err || exit 1
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -k regex:"spmv|bpcg|minres|k_" -c 600 --csv --log-file gpurun_out/r1c_launches.csv $B > gpurun_out/ncu_list.log 2>&1
 tail -2 gpurun_out/ncu_list.log

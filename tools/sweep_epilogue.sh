@@ -1,6 +1,6 @@
 # SELL kernel variants by NSB_SELL_FLAGS (bit 2: two epilogue rows in flight, bit 3: x staged with cp.async); FLAGS="7 15" selects the list
 mkdir -p gpurun_out
-B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --lanczos-steps 60"
+B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --lanczos-steps 60 --solve-to-tol 0"
 run() { # name, dofs, env...
   local name=$1 dofs=$2; shift 2
   env "$@" timeout 300 $B --dofs $dofs > gpurun_out/epi_$name.json 2> gpurun_out/epi_$name.err

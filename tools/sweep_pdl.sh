@@ -1,6 +1,6 @@
 # programmatic-dependent-launch variants of the BPCG iteration (bench.py, short run): attribute mask, trigger / prefetch flags, graphs
 mkdir -p gpurun_out
-B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-minres --lanczos-steps 60"
+B="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-minres --lanczos-steps 60 --solve-to-tol 0"
 run() { # name, dofs, env...
   local name=$1 dofs=$2; shift 2
   env "$@" timeout 300 $B --dofs $dofs > gpurun_out/pdl_$name.json 2> gpurun_out/pdl_$name.err
