@@ -101,3 +101,59 @@ def test_index_space_and_plans_single_process():
     assert plans[0].localize(sp, torch.tensor([0, 5, 13, 11])).tolist() == [0, 6, 7, 5]
     with pytest.raises(ValueError):
         plans[0].localize(sp, torch.tensor([6]))
+
+
+def _exchange_in_process(plans, owned_vectors):
+    """The halo exchange of all ranks emulated in one process: rank r's tail is filled neighbour by neighbour with the
+    entries the neighbour's send list names (the order nsb_halo_create / k_halo_push use)."""
+    out = []
+    for r, plan in enumerate(plans):
+        tail = []
+        for k, nb in enumerate(plan.neighbors):
+            nb = int(nb)
+            other = plans[nb]
+            j = list(other.neighbors).index(r)
+            so = int(other.send_counts[:j].sum())
+            sc = int(other.send_counts[j])
+            assert sc == int(plan.recv_counts[k])               # what nb ships to r is what r expects from nb
+            idx = torch.as_tensor(other.send_idx[so:so + sc].astype(np.int64))
+            tail.append(owned_vectors[nb][idx])
+        out.append(torch.cat([owned_vectors[r]] + tail) if tail else owned_vectors[r].clone())
+    return out
+
+
+@pytest.mark.parametrize("world", [4, 8])
+def test_row_partition_plans_at_the_bench_world_sizes(world):
+    """World sizes 4 and 8 (what the scaling bench runs) planned in one process: every rank's local blocks applied to
+    [owned | exchanged halo] reproduce its rows of the global operators, slabs have two neighbours, send and receive
+    counts pair up, and the owned ranges tile the index spaces."""
+    import navier_stokes_solver_b200.partition as P
+    import navier_stokes_solver_b200.synthetic as syn
+    cells = (2 * world + 1, 2, 2)        # at least two vertex planes per slab
+    G = syn.assemble_stokes(cells, LENGTHS)
+    slabs = [syn.assemble_stokes(cells, LENGTHS, slab=r, nslabs=world) for r in range(world)]
+    su, sp = P.stokes_slab_spaces(cells, world)
+    plans_u = P.make_plans_single_process(su, [torch.cat([S.A.colidx, S.B.colidx]) for S in slabs])
+    plans_p = P.make_plans_single_process(sp, [S.BT.colidx for S in slabs])
+    locs = [P.localize_stokes(slabs[r], r, world, plans=(plans_u[r], plans_p[r])) for r in range(world)]
+    assert sum(L.n_u for L in locs) == G.n_u and sum(L.n_p for L in locs) == G.n_p
+    assert torch.equal(torch.sort(torch.cat([L.owned_u for L in locs]))[0], torch.arange(G.n_u))
+    assert torch.equal(torch.sort(torch.cat([L.owned_p for L in locs]))[0], torch.arange(G.n_p))
+    rng = np.random.default_rng(11)
+    xu = torch.as_tensor(rng.uniform(-1, 1, G.n_u))
+    xp = torch.as_tensor(rng.uniform(-1, 1, G.n_p))
+    xu_loc = _exchange_in_process(plans_u, [xu[L.owned_u] for L in locs])
+    xp_loc = _exchange_in_process(plans_p, [xp[L.owned_p] for L in locs])
+    A, B, BT = G.A.to_scipy(), G.B.to_scipy(), G.BT.to_scipy()
+    yA, yB, yBT = A @ xu.numpy(), B @ xu.numpy(), BT @ xp.numpy()
+    for r, L in enumerate(locs):
+        assert [int(x) for x in L.plan_u.neighbors] == [x for x in (r - 1, r + 1) if 0 <= x < world]
+        ou, op_ = L.owned_u.numpy(), L.owned_p.numpy()
+        assert np.abs(L.A.to_scipy() @ xu_loc[r].numpy() - yA[ou]).max() < 1e-12
+        assert np.abs(L.B.to_scipy() @ xu_loc[r].numpy() - yB[op_]).max() < 1e-12
+        assert np.abs(L.BT.to_scipy() @ xp_loc[r].numpy() - yBT[ou]).max() < 1e-12
+        # the stacked saddle rows with the stacked plan
+        K, plan = P.local_saddle(L)
+        assert K.shape[0] == L.n_u + L.n_p
+    # a partial dot product per rank sums to the global one
+    assert abs(sum(float(xu[L.owned_u] @ xu[L.owned_u]) for L in locs) - float(xu @ xu)) < 1e-10 * float(xu @ xu)
