@@ -7,10 +7,17 @@ channel of templates/NavierStokesSIMPLE_test_3D.py refined to ~20M Taylor-Hood u
     python bench.py --impl reference ...                      (CPU oracle port on the host cores)
 
 A step = one BramblePasciakCG call of exactly --iters iterations (tol = 0 never triggers) from the same
-start vector on the same assembled system.  `value` times K steps with every input resident in HBM;
-`e2e` times the same call with host (pinned) f, g, sol buffers, copies inside the timed region.
+start vector on the same assembled system, through the Python mirror of the reference signature
+(navier_stokes_solver_b200.solvers.BramblePasciakCG, printrates=False).  `value` times K steps with every
+input resident in HBM; `e2e` times the same call with host (pinned) f, g, sol buffers, copies inside the
+timed region.  Beside the headline the line carries: the MINRES iteration on the merged saddle operator,
+time to tolerance, a SIMPLE time step (DoTimeStep/Project) on the same mesh, Gram-Schmidt, a solution
+fingerprint that is comparable across N, and parity objects (device vs the C oracle at N = 1, row-partitioned
+vs single-GPU at N > 1).
 """
 import argparse
+import contextlib
+import io
 import json
 import os
 import subprocess
@@ -30,8 +37,15 @@ BPCG_VEC_PASSES_U = 24
 BPCG_VEC_PASSES_P = 13
 # MINRES iteration beyond the SpMV's own x/y: re-read z (1) + K2 r4 w2 (6) + K3 r4 w2 (6) = 13 passes of N
 MINRES_VEC_PASSES = 13
+# Jacobi-PCG iteration (NGSolve CGSolver) beyond the SpMV's own x/y: C1 epilogue re-reads s (1); C2 r(u,s,d,q,dinv) w(u,d,w) = 8;
+# C3 r(s,w) w(s) = 3
+CG_VEC_PASSES = 12
+# modified Gram-Schmidt, m = 5, 3 sweeps: 195 passes of N
+GS_BYTES_PER_ROW = 1560
 WORKLOAD = ("3D Stokes channel [0,2.5]x[0,0.41]^2 (NavierStokesSIMPLE_test_3D.py), Taylor-Hood P2/P1, "
             "BramblePasciakCG (bramblepasciak_new.py) with Jacobi preA/preM, %d iterations per step")
+LENGTHS = (2.5, 0.41, 0.41)
+REF_ITERS_PER_STEP = 5   # reference arm: iterations of the CPU port per timed step (bounded sample of the 100-iteration step)
 
 
 def spmv_bytes(rows, cols, nnz):
@@ -49,6 +63,21 @@ def measured_peaks():
         with open(p) as f:
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def config_dict(iters, cells, n_u, n_p, nnzA, nnzB, world):
+    """The `config` object; both arms print the same one for the same command line."""
+    return {"workload": WORKLOAD % iters, "cells": list(cells), "dofs": int(n_u + n_p), "n_u": int(n_u), "n_p": int(n_p),
+            "nnz_A": int(nnzA), "nnz_B": int(nnzB), "iters_per_step": iters, "row_partition": "x-slabs" if world > 1 else "none",
+            "l2_policy": "inputs larger than L2 (%.1f GB of CSR per iteration)" % (12e-9 * (nnzA + 2 * nnzB))}
+
+
+@contextlib.contextmanager
+def quiet():
+    """The Python mirrors print the reference's own lines (condition, err0, warnings); this script prints ONE line."""
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        yield buf
 
 
 class ClockSampler:
@@ -97,76 +126,121 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-def cpu_oracle_rate(target_dofs, iters, sample_dofs=4.0e6):
-    """Reference arm / cpu_baseline: the C + OpenMP oracle port of solvers/bramblepasciak_new.py
-    (oracle/c/krylov_omp.c: one multi-threaded primitive per reference line, as NGSolve executes them
-    under TaskManager) on a bounded coarser refinement of the same channel, on all host cores.
-    Returns (its_per_s_scaled_to_full, info)."""
+# CPU side: the C + OpenMP oracle port (oracle/c/krylov_omp.c) on the SAME assembled blocks
+# ------------------------------------------------------------------------------------------------
+class HostSystem:
+    """Host (numpy) copy of an assembled Stokes system in the layout the C oracle takes."""
+
+    def __init__(self, S, syn):
+        from oracle import cbuild
+
+        def trip(csr):
+            return (np.ascontiguousarray(csr.rowptr.cpu().numpy(), dtype=np.int64),
+                    np.ascontiguousarray(csr.colidx.cpu().numpy(), dtype=np.int32),
+                    np.ascontiguousarray(csr.values.cpu().numpy(), dtype=np.float64))
+        self.n_u, self.n_p = S.n_u, S.n_p
+        self.cells = tuple(S.cells)
+        self.nnzA, self.nnzB = S.A.nnz, S.B.nnz
+        self.blocks = cbuild.Blocks.__new__(cbuild.Blocks)
+        self.blocks.n_u, self.blocks.n_p = S.n_u, S.n_p
+        self.blocks.A, self.blocks.B, self.blocks.BT = trip(S.A), trip(S.B), trip(S.BT)
+        self.dA = syn.jacobi_inverse(S.A, free=S.free_u).cpu().numpy()
+        self.dM = syn.jacobi_inverse(S.Mp).cpu().numpy()
+        self.f, self.g = S.f.cpu().numpy(), S.g.cpu().numpy()
+        self.u_start = np.concatenate([S.u0.cpu().numpy(), np.zeros(S.n_p)])
+
+
+def assemble_host(dofs, cells=None):
     import torch
-    from oracle import cbuild
-    from oracle import krylov_oracle as ko
     import navier_stokes_solver_b200.synthetic as syn
-    sample_dofs = min(target_dofs, sample_dofs)
-    cells = syn.stokes_cells_for_dofs(sample_dofs)
+    cells = cells or syn.stokes_cells_for_dofs(dofs)
     dev = "cuda" if torch.cuda.is_available() else "cpu"
-    S = syn.assemble_stokes(cells, (2.5, 0.41, 0.41), device=dev)
-    A, B, BT = S.A.to_scipy(), S.B.to_scipy(), S.BT.to_scipy()
-    dA = syn.jacobi_inverse(S.A, free=S.free_u).cpu().numpy()
-    dM = syn.jacobi_inverse(S.Mp).cpu().numpy()
-    f, g = S.f.cpu().numpy(), S.g.cpu().numpy()
-    u0 = np.concatenate([S.u0.cpu().numpy(), np.zeros(S.n_p)])
-    n = S.n_u + S.n_p
+    S = syn.assemble_stokes(cells, LENGTHS, device=dev)
+    H = HostSystem(S, syn)
     del S
     if dev == "cuda":
         torch.cuda.empty_cache()
-    ritz = ko.lanczos_eigs(A, dA, A.shape[0], maxsteps=40, tol=1e-2)
-    lam = float(ritz[0]) * 0.5   # safe under-estimate: the sample only times the loop
-    blocks = cbuild.Blocks(A, B, BT)
-    best = None
-    for _ in range(3):           # best of 3 (BASELINE.md 3)
-        sol = u0.copy()
-        t0 = time.perf_counter()
-        it, hist, err0, loop_s = cbuild.bpcg_v2(blocks, f, g, dA, dM, ko.bpcg_scale(lam), sol, tol=0.0, maxsteps=iters,
-                                                initialize=False)
-        wall = time.perf_counter() - t0
-        if best is None or loop_s < best[0]:
-            best = (loop_s, wall)
-    loop_s, wall = best
-    rate_sample = iters / loop_s
-    scaled = rate_sample * (n / float(target_dofs)) if target_dofs > n else rate_sample
-    return scaled, dict(sample_dofs=int(n), iters=iters, loop_seconds=loop_s, wall_seconds=wall,
-                        rate_at_sample=rate_sample, threads=cbuild.num_threads())
+    return H
+
+
+def cpu_bpcg(H, k_scale, iters, tol=0.0, threads=None):
+    """One call of the C port of BramblePasciakCG on the host cores -> (it, history, loop_seconds, sol, threads)."""
+    from oracle import cbuild
+    nt = cbuild.set_threads(threads)
+    sol = H.u_start.copy()
+    it, hist, err0, loop_s = cbuild.bpcg_v2(H.blocks, H.f, H.g, H.dA, H.dM, k_scale, sol, tol=tol, maxsteps=iters, initialize=False)
+    return it, hist, loop_s, sol, nt
+
+
+def cpu_lambda(H, steps=12):
+    """A safe under-estimate of lambda_min(dA A) for the CPU arm (the loop's speed does not depend on it): a few steps of the
+    oracle's Lanczos with the threaded C SpMV, halved."""
+    from oracle import cbuild
+    from oracle import krylov_oracle as ko
+    import ctypes as C
+    lib = cbuild.load()
+    rp, ci, va = H.blocks.A
+    n = H.n_u
+
+    def A_mul(x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.empty(n)
+        lib.ko_spmv(C.c_int64(n), C.c_int64(n), rp.ctypes.data_as(C.c_void_p), ci.ctypes.data_as(C.c_void_p),
+                    va.ctypes.data_as(C.c_void_p), x.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p))
+        return y
+    ritz = ko.lanczos_eigs(A_mul, H.dA, n, maxsteps=steps, tol=1e-2)
+    return 0.5 * float(ritz[0])
 
 
 def run_reference(args):
+    """`--impl reference`: the reference's CPU implementation of the path (C + OpenMP port, one threaded primitive per
+    reference statement; NGSolve itself is absent) on the SAME 20.4M-dof blocks, every host core, rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    iters = min(args.iters, 20)
-    rates, info = [], None
+    from oracle import cbuild
+    from oracle import krylov_oracle as ko
+    import torch
+    full = torch.cuda.is_available()          # no GPU: assembling 20M dofs on the host is out of reach; say so
+    dofs = args.dofs if full else min(args.dofs, 1.0e6)
+    H = assemble_host(dofs)
+    threads = cbuild.set_threads()
+    k = ko.bpcg_scale(cpu_lambda(H))
+    its = REF_ITERS_PER_STEP
+    times = []
     t_all = time.perf_counter()
     for i in range(args.warmup + args.steps):
-        r, info = cpu_oracle_rate(args.dofs, iters)
+        _, _, loop_s, _, _ = cpu_bpcg(H, k, its, threads=threads)
         if i >= args.warmup:
-            rates.append(r)
-        if time.perf_counter() - t_all > 150:   # keep the whole arm within minutes
-            rates = rates or [r]
+            times.append(loop_s)
+        if time.perf_counter() - t_all > 240 and len(times) >= 1:   # keep the whole arm within minutes
             break
-    v = float(np.mean(rates))
-    sample = ("C+OpenMP oracle port (oracle/c/krylov_omp.c: ko_bpcg_v2) of solvers/bramblepasciak_new.py, unfused like the "
-              "reference's NGSolve statements; %d iterations on a %d-dof refinement of the same 3D channel, best of 3, "
-              "iterations/s scaled by the dof ratio to the %.3g-dof workload (rate at sample %.2f it/s); NGSolve absent"
-              % (iters, info["sample_dofs"], args.dofs, info["rate_at_sample"]))
+    steps_done = len(times)
+    v = its * steps_done / float(np.sum(times))
+    sample = ("C+OpenMP port (oracle/c/krylov_omp.c: ko_bpcg_v2) of solvers/bramblepasciak_new.py, unfused like the reference's "
+              "NGSolve statements; each timed step = %d iterations of the loop on the SAME %d-dof system as the device arm "
+              "(no dof scaling), %d threads set explicitly; NGSolve absent" % (its, H.n_u + H.n_p, threads))
+    cfg = config_dict(args.iters, H.cells, H.n_u, H.n_p, H.nnzA, H.nnzB, args.gpus)
     line = {"impl": "reference", "metric": "bpcg_krylov_iterations_per_s", "value": v, "unit": "iterations/s",
-            "n_gpus": args.gpus, "steps": len(rates), "warmup": args.warmup, "ms_per_step": 1e3 * args.iters / (v if v else 1),
+            "n_gpus": args.gpus, "steps": steps_done, "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(times)),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD % args.iters, "dofs_target": args.dofs},
-            "cpu_baseline": {"value": v, "unit": "iterations/s", "cores": info["threads"], "kind": "port", "sample": sample},
+            "config": cfg, "sample_dofs": int(H.n_u + H.n_p), "same_system_as_device_arm": bool(full),
+            "cpu_baseline": {"value": v, "unit": "iterations/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
 # ------------------------------------------------------------------------------------------------
+def sell_stream_bytes(fmt, rows, cols):
+    """Bytes one SpMV of a SELL-LX operator moves by construction (sell.cu): 10 B per stored nonzero, 12 B per column run (or 4 B
+    per distinct column), 4 B per slice offset, 2 B per row (perm), x once, y once."""
+    if fmt["rows_per_chunk"] <= 0:
+        return None
+    slices = fmt["chunks"] * fmt["rows_per_chunk"] * fmt["lanes_per_row"] // 32
+    idx = 12 * fmt["column_runs"] if fmt["column_runs"] > 0 else 4 * fmt["total_distinct"]
+    return 10 * fmt["stored_nnz"] + idx + 4 * slices + 2 * fmt["chunks"] * fmt["rows_per_chunk"] + 8 * cols + 8 * rows
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -181,8 +255,14 @@ def main():
     ap.add_argument("--minres-iters", type=int, default=60)
     ap.add_argument("--solve-to-tol", type=float, default=1e-10,
                     help="after the timed legs, run one full BramblePasciakCG solve to this relative tolerance (the reference's call "
-                         "uses 1e-10, NavierStokesSIMPLE_iterative.py:397) and report time to tolerance (single-GPU runs; 0 = skip)")
+                         "uses 1e-10, NavierStokesSIMPLE_iterative.py:397) and report time to tolerance (0 = skip)")
     ap.add_argument("--solve-maxsteps", type=int, default=30000)
+    ap.add_argument("--no-parity", action="store_true", help="skip parity_at_sample (N = 1) / parity_vs_single (N > 1)")
+    ap.add_argument("--parity-dofs", type=float, default=2.0e6)
+    ap.add_argument("--no-simple", action="store_true", help="skip the SIMPLE time-step leg")
+    ap.add_argument("--simple-steps", type=int, default=2)
+    ap.add_argument("--simple-proj-maxsteps", type=int, default=200)
+    ap.add_argument("--no-gs", action="store_true", help="skip the Gram-Schmidt leg")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -192,6 +272,7 @@ def main():
     import navier_stokes_solver_b200 as nsb
     import navier_stokes_solver_b200.synthetic as syn
     from navier_stokes_solver_b200 import _lib
+    import benchlegs
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -207,10 +288,13 @@ def main():
     nsb.set_default_context(ctx)
 
     cells = syn.stokes_cells_for_dofs(args.dofs)
-    lengths = (2.5, 0.41, 0.41)
     t_asm = time.perf_counter()
+    host = None
+    from navier_stokes_solver_b200 import partition
     if world == 1:
-        S = syn.assemble_stokes(cells, lengths, device="cuda")
+        S = syn.assemble_stokes(cells, LENGTHS, device="cuda")
+        if not args.no_cpu_baseline:
+            host = HostSystem(S, syn)           # the CPU baseline runs on these very blocks
         A = nsb.SparseMatrix.from_csr(S.A, ctx)
         B = nsb.SparseMatrix.from_csr(S.B, ctx)
         BT = nsb.SparseMatrix.from_csr(S.BT, ctx)
@@ -223,17 +307,20 @@ def main():
         u_start = torch.cat([S.u0, torch.zeros(n_p, dtype=torch.float64, device="cuda")])
         S.A = S.B = S.BT = None
         start_vec = None
+        space_u, space_p = partition.stokes_slab_spaces(cells, 1)
+        P = None
     else:
-        from navier_stokes_solver_b200 import partition
-        P = partition.build_distributed_stokes(cells, lengths, ctx, rank, world)
+        P = partition.build_distributed_stokes(cells, LENGTHS, ctx, rank, world, keep_local=not args.no_minres)
         A, B, BT, dA, dM = P.A, P.B, P.BT, P.dA, P.dM
         n_u, n_p, nnzA, nnzB = P.n_u_global, P.n_p_global, P.nnzA_global, P.nnzB_global
         f_d, g_d, u_start, start_vec = P.f, P.g, P.u_start, P.lanczos_start
+        space_u, space_p = P.local.space_u, P.local.space_p
     torch.cuda.synchronize()
     t_asm = time.perf_counter() - t_asm
     pA = nsb.DiagonalPreconditioner.from_diagonal(dA, ctx)
     pM = nsb.DiagonalPreconditioner.from_diagonal(dM, ctx)
     torch.cuda.empty_cache()
+    n_u_loc = int(f_d.numel())
 
     # scale factor k = 1/lambda_min + 1e-3 by device Lanczos (bramblepasciak_new.py:115-118), once per assembly
     t_l = time.perf_counter()
@@ -241,23 +328,19 @@ def main():
     lanczos_steps = nsb.solvers.last_info["iterations"]
     t_l = time.perf_counter() - t_l
     lam_min = min(lams)
-
     lib = ctx._lib
     import ctypes as C
     BTm = B.CreateTranspose()
     k_scale = 1.0 / lam_min + 1e-3
-    n_loc = int(f_d.numel() + g_d.numel())
-    hist = np.zeros(args.iters + 2)
 
-    def step(f_buf, g_buf, sol_buf):
-        upd, secs, status = C.c_int(), C.c_double(), C.c_int()
-        pf, _, _ = nsb.la.buffer_of(f_buf)
-        pg, _, _ = nsb.la.buffer_of(g_buf)
-        ps, _, _ = nsb.la.buffer_of(sol_buf)
-        _lib.check(lib.nsb_bpcg(ctx.h, A.h, B.h, BTm.h, pA.h, pM.h, k_scale, pf, pg, ps, args.iters, 0.0, 0, 1, 2,
-                                hist.ctypes.data, C.byref(upd), C.byref(secs), C.byref(status)), "nsb_bpcg")
-        assert upd.value == args.iters, (upd.value, status.value)
-        return secs.value
+    def step(f_buf, g_buf, sol_buf, iters=args.iters, tol=0.0):
+        """One solve through the reference-facing wrapper (solvers.BramblePasciakCG, printrates=False)."""
+        with quiet():
+            it, secs = nsb.BramblePasciakCG(A, B, None, f_buf, g_buf, pA, pM, sol_buf, tol=tol, maxsteps=iters, printrates=False,
+                                            initialize=False, rel_err=True, lam_min=lam_min)
+        if tol == 0.0:
+            assert it == iters - 1, (it, nsb.solvers.last_info)
+        return secs
 
     def barrier():
         if world > 1:
@@ -291,6 +374,9 @@ def main():
             wall_check[tag] = wall
         return dt, loop
 
+    env = benchlegs.Env(args=args, nsb=nsb, syn=syn, partition=partition, ctx=ctx, world=world, rank=rank, local=local, dist=dist,
+                        timed=timed, barrier=barrier, quiet=quiet, lib_stream=lib_stream, cells=cells, lengths=LENGTHS)
+
     # ---- device-resident leg
     sol_d = u_start.clone()
 
@@ -315,7 +401,8 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     its = args.iters * args.steps
     value = its / dt
-    hist_dev = hist[:args.iters + 1].copy()
+    hist_dev = nsb.solvers.last_info["history"].copy()
+    finger_100 = benchlegs.fingerprint(env, sol_d, n_u_loc, space_u, space_p, n_u, n_p)
 
     # ---- end-to-end leg: host pinned f, g, sol; H2D/D2H inside the timed region
     f_h = torch.empty(f_d.numel(), dtype=torch.float64).pin_memory()
@@ -330,11 +417,12 @@ def main():
 
     s_h.copy_(u_h)
     timed(1, e2e_step)
-    same = np.allclose(hist[:args.iters + 1], hist_dev, rtol=1e-12)   # first host step == device leg
+    same = np.allclose(nsb.solvers.last_info["history"], hist_dev, rtol=1e-12)   # first host step == device leg
     dt_e, _ = timed(args.steps, e2e_step, 'e2e')
     e2e_value = its / dt_e
     h2d = 8 * (f_h.numel() + g_h.numel() + s_h.numel())
     d2h = 8 * s_h.numel() + 8 * (args.iters + 1)
+    del f_h, g_h, s_h
 
     # ---- roofline of the dominant kernel (SpMV with A): CUDA events on the context's stream
     ms_A = A.spmv_bench(warmup=20, reps=200)   # 200 timed repetitions after 20 warm-up
@@ -345,86 +433,115 @@ def main():
     ach_A = bytes_A / (ms_A * 1e-3) / 1e9
     iter_bytes = bpcg_iter_bytes(n_u, n_p, nnzA, nnzB)
     iter_gbs = iter_bytes * (its / loop) / 1e9 / world if loop > 0 else None
+    fmtA = A.format()
+    stream_A = sell_stream_bytes(fmtA, A.shape[0], A.shape[1])
 
-    # ---- MINRES on the merged saddle-point operator K = [[A, B^T], [B, 0]] (minres.py; BASELINE metric names both)
+    # ---- MINRES on the merged saddle-point operator K = [[A, B^T], [B, 0]] (minres.py; BASELINE metric names both), every N
     minres_info = None
-    if world == 1 and not args.no_minres:
-        Kb = nsb.BlockMatrix([[A, BTm], [B, None]]).saddle()
-        pK = nsb.BlockMatrix([[pA, None], [None, pM]]).blockdiag_preconditioner()
-        rhs_d = torch.cat([f_d, g_d])
-        mh = np.zeros(args.minres_iters + 2)
-        best = None
-        for rep in range(3):
-            msol = u_start.clone()
-            its_m, secs_m, st_m = C.c_int(), C.c_double(), C.c_int()
-            pr, _, _ = nsb.la.buffer_of(rhs_d)
-            pz, _, _ = nsb.la.buffer_of(msol)
-            _lib.check(lib.nsb_minres(ctx.h, Kb.h, pK.h, pr, pz, args.minres_iters, 0.0, 0, mh.ctypes.data, C.byref(its_m),
-                                      C.byref(secs_m), C.byref(st_m)), "nsb_minres")
-            if rep > 0 and (best is None or secs_m.value < best):
-                best = secs_m.value
-        Nk = n_u + n_p
-        mbytes = spmv_bytes(Nk, Nk, nnzA + 2 * nnzB) + 8 * MINRES_VEC_PASSES * Nk
-        mrate = its_m.value / best
-        minres_info = {"iterations_per_s": mrate, "iterations": its_m.value, "algorithmic_bytes_per_iteration": mbytes,
-                       "achieved_gbs": mbytes * mrate / 1e9, "frac_of_measured_peak": mbytes * mrate / 1e9 / peak,
-                       "spmv_K_ms": Kb.spmv_bench(warmup=20, reps=200), "spmv_K_format": Kb.format()}
-        del Kb
+    if not args.no_minres:
+        minres_info = benchlegs.minres_leg(env, A, B, BTm, pA, pM, dA, dM, f_d, g_d, u_start, P, n_u, n_p, nnzA, nnzB, peak,
+                                           spmv_bytes, MINRES_VEC_PASSES)
+    if P is not None:
+        P.local.A = P.local.B = P.local.BT = None
+        torch.cuda.empty_cache()
+
+    # ---- time to tolerance (the reference's call: tol 1e-10 relative), every N; the solution's fingerprint
     ttt = None
-    if args.solve_to_tol > 0 and world == 1:
-        th = np.zeros(args.solve_maxsteps + 2)
+    if args.solve_to_tol > 0:
         tsol = u_start.clone()
-        upd, secs, status = C.c_int(), C.c_double(), C.c_int()
-        pf, _, _ = nsb.la.buffer_of(f_d)
-        pg, _, _ = nsb.la.buffer_of(g_d)
-        ps, _, _ = nsb.la.buffer_of(tsol)
         barrier()
         t0 = time.perf_counter()
         try:   # an extra leg after the timed ones: a failure here is reported, it does not take the headline line down
-            _lib.check(lib.nsb_bpcg(ctx.h, A.h, B.h, BTm.h, pA.h, pM.h, k_scale, pf, pg, ps, args.solve_maxsteps, args.solve_to_tol,
-                                    0, 1, 2, th.ctypes.data, C.byref(upd), C.byref(secs), C.byref(status)), "nsb_bpcg")
+            with quiet():
+                it_t, secs_t = nsb.BramblePasciakCG(A, B, None, f_d, g_d, pA, pM, tsol, tol=args.solve_to_tol, maxsteps=args.solve_maxsteps,
+                                                    printrates=False, initialize=False, rel_err=True, lam_min=lam_min)
             barrier()
-            ttt = {"tol": args.solve_to_tol, "rel_err": True, "iterations": upd.value, "loop_seconds": secs.value,
-                   "call_seconds": time.perf_counter() - t0, "status": _lib.STATUS_NAMES.get(status.value, status.value),
-                   "final_relative_error": float(th[upd.value] / th[0]) if th[0] > 0 else None}
+            info = dict(nsb.solvers.last_info)
+            th = info["history"]
+            ttt = {"tol": args.solve_to_tol, "rel_err": True, "preA": "Jacobi", "iterations": int(info["updates"]), "loop_seconds": secs_t,
+                   "call_seconds": time.perf_counter() - t0, "status": info["status"],
+                   "final_relative_error": float(th[-1] / th[0]) if th[0] > 0 else None,
+                   "solution_fingerprint": benchlegs.fingerprint(env, tsol, n_u_loc, space_u, space_p, n_u, n_p)}
         except Exception as ex:   # noqa: BLE001  (NsbError or a CUDA error surfaced by torch)
             ttt = {"tol": args.solve_to_tol, "error": str(ex)[:200]}
         del tsol
+
+    # ---- Gram-Schmidt (orthonormalization.py) at the bench's vector length
+    gs_info = None
+    if not args.no_gs:
+        gs_info = benchlegs.guarded(benchlegs.gram_schmidt_leg, env, n_u_loc + int(g_d.numel()), n_u + n_p, peak, GS_BYTES_PER_ROW)
+
+    # ---- the operators of the headline are no longer needed: free them before the legs that assemble their own
+    del A, B, BT, BTm, pA, pM, sol_d
+    if P is not None:
+        P.A = P.B = P.BT = None
+    P = None
+    torch.cuda.empty_cache()
+
+    # ---- SIMPLE time step (DoTimeStep / Project, NavierStokesSIMPLE_iterative.py:427-443) on the same mesh, every N
+    simple_info = None
+    if not args.no_simple:
+        simple_info = benchlegs.guarded(benchlegs.simple_step_leg, env, peak, spmv_bytes, CG_VEC_PASSES)
+
+    # ---- parity where the driver can see it
+    parity = None
+    if not args.no_parity:
+        if world == 1:
+            parity = benchlegs.guarded(benchlegs.parity_at_sample, env, assemble_host, cpu_bpcg)
+        else:
+            parity = benchlegs.guarded(benchlegs.parity_vs_single, env)
+
+    cpu_line = None
+    if host is not None and rank == 0:
+        from oracle import krylov_oracle as ko
+        best, nt = None, None
+        for _ in range(3):
+            _, _, loop_s, _, nt = cpu_bpcg(host, k_scale, 20)
+            best = loop_s if best is None or loop_s < best else best
+        cpu_line = {"value": 20 / best, "unit": "iterations/s", "cores": nt, "kind": "port",
+                    "sample": "C+OpenMP oracle port of bramblepasciak_new.py (oracle/c/krylov_omp.c), 20 iterations on the SAME "
+                              "%d-dof blocks the device solves (no dof scaling), best of 3, %d threads set explicitly" % (n_u + n_p, nt)}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    # DRAM bytes per launch of the same kernel from the committed ncu --set full capture (never measured under this run)
+    # DRAM bytes per launch of the same kernel from a committed ncu --set full capture (never measured under this run); used only
+    # when the capture was taken on the same storage format (fingerprint), else null -- the by-construction stream bytes stand in
     traffic, traffic_src = None, None
-    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1c_spmv_A_traffic.json")
-    if world == 1 and os.path.exists(tpath):
-        tj = json.load(open(tpath))
-        if tj.get("dofs") == int(n_u + n_p):
-            traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], "profiles/r1c_spmv_A_traffic.json"
+    for name in ("r2_spmv_A_traffic.json", "r1c_spmv_A_traffic.json"):
+        tpath = os.path.join(ROOT, "profiles", name)
+        if world == 1 and traffic is None and os.path.exists(tpath):
+            tj = json.load(open(tpath))
+            fp_ok = tj.get("format") is None or all(tj["format"].get(k) == fmtA.get(k) for k in ("stored_nnz", "column_runs", "chunks"))
+            if tj.get("dofs") == int(n_u + n_p) and fp_ok:
+                traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], "profiles/" + name
     line = {
         "metric": "bpcg_krylov_iterations_per_s", "value": value, "unit": "iterations/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD % args.iters,
-                   "cells": list(cells), "dofs": int(n_u + n_p), "n_u": int(n_u), "n_p": int(n_p), "nnz_A": int(nnzA),
-                   "nnz_B": int(nnzB), "iters_per_step": args.iters, "row_partition": "x-slabs" if world > 1 else "none",
-                   "l2_policy": "inputs larger than L2 (%.1f GB of CSR per iteration)" % (12e-9 * (nnzA + 2 * nnzB)),
-                   "lambda_min": lam_min, "lanczos_steps": lanczos_steps, "assembly_s": t_asm, "lanczos_s": t_l},
+        "config": config_dict(args.iters, cells, n_u, n_p, nnzA, nnzB, world),
+        "setup": {"lambda_min": lam_min, "lanczos_steps": lanczos_steps, "assembly_s": t_asm, "lanczos_s": t_l},
         "iteration_loop": {"iterations_per_s": its / loop if loop else None, "algorithmic_bytes_per_iteration": iter_bytes,
                            "achieved_gbs_per_gpu": iter_gbs, "frac_of_measured_peak": iter_gbs / peak if iter_gbs else None,
                            "frac_of_nominal_8TBs": iter_gbs / 8000.0 if iter_gbs else None},
-        "roofline": {"bound": "hbm", "kernel": "spmv_sell_kernel (A, %d nnz)" % nnzA, "achieved": ach_A, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "spmv_sell_kernel (A, %d nnz%s)" % (nnzA, "" if world == 1 else ", this rank's rows"),
+                     "achieved": ach_A, "peak": peak,
                      "peak_source": peak_src, "unit": "GB/s", "frac": ach_A / peak, "frac_of_nominal_8TBs": ach_A / 8000.0,
                      "algorithmic_bytes": bytes_A, "ms": ms_A, "traffic": traffic, "traffic_source": traffic_src,
                      # algorithmic bytes follow the 12 B/nnz CSR model; the kernel's SELL-LX stream is ~10 B/nnz, so `frac` can
-                     # exceed 1 -- the same launch time against the DRAM bytes ncu counted:
+                     # exceed 1 -- the same launch time against the bytes the format moves by construction / ncu counted:
+                     "format": fmtA, "stream_bytes_by_construction": stream_A,
+                     "frac_by_stream_bytes": (stream_A / (ms_A * 1e-3) / 1e9 / peak) if stream_A else None,
                      "frac_by_traffic": (traffic / (ms_A * 1e-3) / 1e9 / peak) if traffic else None,
-                     "other": {"spmv_B_gbs": B.spmv_bytes() / ms_B / 1e6, "spmv_BT_gbs": BTm.spmv_bytes() / ms_BT / 1e6}},
+                     "other": {"spmv_B_gbs": spmv_bytes(*_shape_nnz(n_p, n_u, nnzB, world)) / ms_B / 1e6 if world == 1 else None,
+                               "spmv_BT_gbs": spmv_bytes(*_shape_nnz(n_u, n_p, nnzB, world)) / ms_BT / 1e6 if world == 1 else None,
+                               "spmv_B_ms": ms_B, "spmv_BT_ms": ms_BT}},
         "e2e": {"value": e2e_value, "unit": "iterations/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "history_matches_device_leg": bool(same)},
+                "history_matches_device_leg": bool(same), "through": "solvers.BramblePasciakCG(..., printrates=False) with pinned host f, g, sol"},
         # residual-history fingerprint of the device leg: equal (to reduction-order rounding) at every N for the same --dofs
         "history_checkpoints": {"err0": float(hist_dev[0]), "err_%d" % (args.iters // 2): float(hist_dev[args.iters // 2]),
                                 "err_%d" % args.iters: float(hist_dev[args.iters])},
+        "solution_fingerprint_after_%d_iterations" % args.iters: finger_100,
         "gpu_launches": int(launches), "clocks": clocks,
         "timing": {"how": "CUDA events on the library's stream around the K steps, barrier + synchronize on both sides, max over ranks",
                    "host_clock_ms_per_step": 1e3 * wall_check.get("device", 0.0) / args.steps,
@@ -434,15 +551,21 @@ def main():
         line["minres"] = minres_info
     if ttt:
         line["time_to_tolerance"] = ttt
-    if not args.no_cpu_baseline and world == 1:
-        v, info = cpu_oracle_rate(args.dofs, 20)
-        line["cpu_baseline"] = {"value": v, "unit": "iterations/s", "cores": info["threads"], "kind": "port",
-                                "sample": "C+OpenMP oracle port of bramblepasciak_new.py (oracle/c/krylov_omp.c), 20 iterations at "
-                                          "%d dofs (same channel, coarser), best of 3, it/s scaled by dof ratio; rate at sample "
-                                          "%.2f it/s" % (info["sample_dofs"], info["rate_at_sample"])}
+    if gs_info:
+        line["gram_schmidt"] = gs_info
+    if simple_info:
+        line["simple_step"] = simple_info
+    if parity:
+        line["parity_at_sample" if world == 1 else "parity_vs_single"] = parity
+    if cpu_line:
+        line["cpu_baseline"] = cpu_line
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def _shape_nnz(r, c, z, world):
+    return r, c, z
 
 
 if __name__ == "__main__":

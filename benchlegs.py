@@ -1,0 +1,253 @@
+"""Legs of bench.py beside the headline (kept out of bench.py so that file stays readable): MINRES on the merged saddle
+operator, Gram-Schmidt, the SIMPLE time step, the solution fingerprint and the two parity objects.  Every device
+computation goes through the package's public API / C ABI; `oracle/` is used by the parity and CPU-baseline legs only."""
+from __future__ import annotations
+
+import time
+import traceback
+from dataclasses import dataclass
+
+import numpy as np
+
+
+@dataclass
+class Env:
+    args: object
+    nsb: object
+    syn: object
+    partition: object
+    ctx: object
+    world: int
+    rank: int
+    local: int
+    dist: object
+    timed: object
+    barrier: object
+    quiet: object
+    lib_stream: object
+    cells: tuple
+    lengths: tuple
+
+
+def guarded(fn, env, *a, **k):
+    """An extra leg must not take the headline line down: a failure is reported in its place."""
+    try:
+        return fn(env, *a, **k)
+    except Exception as ex:   # noqa: BLE001
+        return {"error": ("%s: %s" % (type(ex).__name__, ex))[:300], "where": traceback.format_exc().strip().splitlines()[-2][:200]}
+
+
+def _allreduce(env, t, op="sum"):
+    if env.world > 1:
+        env.dist.all_reduce(t, op=env.dist.ReduceOp.SUM if op == "sum" else env.dist.ReduceOp.MAX)
+    return t
+
+
+# ------------------------------------------------------------------------------------------------
+def fingerprint(env, sol, n_u_loc, space_u, space_p, n_u, n_p):
+    """||u||_2, ||p||_2 and 8 fixed GLOBAL entries (6 velocity, 2 pressure) of a (u | p) solution held row-partitioned:
+    the same numbers at every N for the same system, comparable to 1e-8."""
+    import torch
+    u, p = sol[:n_u_loc], sol[n_u_loc:]
+    acc = torch.zeros(10, dtype=torch.float64, device=sol.device)
+    acc[0], acc[1] = (u * u).sum(), (p * p).sum()
+    ids_u = torch.tensor([(k + 1) * n_u // 7 for k in range(6)], dtype=torch.int64)
+    ids_p = torch.tensor([(k + 1) * n_p // 3 for k in range(2)], dtype=torch.int64)
+    for off, ids, space, part in ((2, ids_u, space_u, u), (8, ids_p, space_p, p)):
+        owner, loc = space.lookup(ids)
+        for k in range(len(ids)):
+            if int(owner[k]) == env.rank:
+                acc[off + k] = part[int(loc[k])]
+    _allreduce(env, acc)
+    a = acc.cpu().numpy()
+    return {"norm_u": float(np.sqrt(a[0])), "norm_p": float(np.sqrt(a[1])), "global_ids_u": ids_u.tolist(), "global_ids_p": ids_p.tolist(),
+            "entries_u": a[2:8].tolist(), "entries_p": a[8:10].tolist()}
+
+
+# ------------------------------------------------------------------------------------------------
+def minres_leg(env, A, B, BTm, pA, pM, dA, dM, f_d, g_d, u_start, P, n_u, n_p, nnzA, nnzB, peak, spmv_bytes, vec_passes):
+    """MinRes (minres.py) on K = [[A, B^T], [B, 0]] merged into one operator (two row panels), Jacobi block preconditioner,
+    --minres-iters iterations from the headline's start vector; row-partitioned at N > 1 (stacked local rows + stacked halo)."""
+    import torch
+    nsb, args = env.nsb, env.args
+    if env.world == 1:
+        K = nsb.BlockMatrix([[A, BTm], [B, None]]).saddle()
+        pK = nsb.BlockMatrix([[pA, None], [None, pM]]).blockdiag_preconditioner()
+        keep = None
+    else:
+        Kl, plan = env.partition.local_saddle(P.local)
+        keep = env.partition.upload_halo(env.ctx, plan)
+        K = nsb.SparseMatrix.from_csr(Kl, env.ctx)
+        K.set_row_panels([0, P.local.n_u, P.local.n_u + P.local.n_p])
+        keep.attach(K)
+        del Kl
+        pK = nsb.DiagonalPreconditioner.from_diagonal(torch.cat([dA, dM]), env.ctx)
+    rhs_d = torch.cat([f_d, g_d])
+    best, its_m, errs = None, 0, None
+    for rep in range(3):
+        msol = u_start.clone()
+        env.barrier()
+        with env.quiet():
+            _, errs = nsb.MinRes(K, rhs_d, pK, msol, args.minres_iters, False, False, 0.0)
+        info = nsb.solvers.last_info
+        secs = torch.tensor([info["seconds"]], dtype=torch.float64, device="cuda")
+        _allreduce(env, secs, "max")
+        its_m = info["iterations"]
+        if rep > 0 and (best is None or float(secs[0]) < best):
+            best = float(secs[0])
+    Nk = n_u + n_p
+    mbytes = spmv_bytes(Nk, Nk, nnzA + 2 * nnzB) + 8 * vec_passes * Nk
+    mrate = its_m / best
+    out = {"iterations_per_s": mrate, "iterations": its_m, "algorithmic_bytes_per_iteration": mbytes,
+           "achieved_gbs_per_gpu": mbytes * mrate / 1e9 / env.world, "frac_of_measured_peak": mbytes * mrate / 1e9 / env.world / peak,
+           "frac_of_nominal_8TBs": mbytes * mrate / 1e9 / env.world / 8000.0,
+           "history_checkpoints": {"rel_err_%d" % k: float(errs[k]) for k in (its_m // 2, its_m) if k < len(errs)},
+           "spmv_K_format": K.format()}
+    if env.world == 1:
+        out["spmv_K_ms"] = K.spmv_bench(warmup=20, reps=200)
+    del K, pK, keep
+    torch.cuda.empty_cache()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+def gram_schmidt_leg(env, n_loc, n_glob, peak, bytes_per_row):
+    """orthonormalize(basis, tries=3) (orthonormalization.py:5-16) on m = 5 device-resident vectors of the bench's length;
+    GB/s against the modified Gram-Schmidt pass count of SURVEY.md 8(d) (1560 bytes per row)."""
+    import ctypes as C
+    import torch
+    from navier_stokes_solver_b200 import _lib
+    m, tries = 5, 3
+    g = torch.Generator(device="cuda")
+    g.manual_seed(1234 + env.rank)
+    base = torch.rand((m, n_loc), dtype=torch.float64, device="cuda", generator=g) - 0.5
+    Q = base.clone()
+    lib, ctx = env.ctx._lib, env.ctx
+
+    evs = []
+
+    def run():
+        Q.copy_(base)
+        torch.cuda.current_stream().synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(env.lib_stream)     # CUDA events on the library's stream around the call alone (the restoring copy is outside)
+        _lib.check(lib.nsb_orthonormalize(ctx.h, Q.data_ptr(), n_loc, m, tries), "nsb_orthonormalize")
+        e1.record(env.lib_stream)
+        evs.append((e0, e1))
+        return 0.0
+
+    env.timed(2, run)
+    evs.clear()
+    l0 = ctx.launch_count()
+    reps = 5
+    env.timed(reps, run)
+    launches = (ctx.launch_count() - l0) // reps
+    torch.cuda.synchronize()
+    t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs) / reps], dtype=torch.float64, device="cuda")
+    _allreduce(env, t, "max")
+    ms = float(t[0])
+    gram = Q @ Q.T
+    _allreduce(env, gram)
+    dev = float((gram - torch.eye(m, dtype=torch.float64, device="cuda")).abs().max())
+    gbs = bytes_per_row * n_loc / (ms * 1e-3) / 1e9
+    return {"m": m, "tries": tries, "rows": int(n_glob), "ms": ms, "launches": int(launches), "algorithmic_bytes_per_gpu": bytes_per_row * n_loc,
+            "achieved_gbs_per_gpu": gbs, "frac_of_measured_peak": gbs / peak, "max_abs_QtQ_minus_I": dev}
+
+
+# ------------------------------------------------------------------------------------------------
+def parity_at_sample(env, assemble_host, cpu_bpcg):
+    """Device vs the C oracle (oracle/c/krylov_omp.c, the restatement of bramblepasciak_new.py pinned on the reference-generated
+    fixtures) on a --parity-dofs refinement of the same channel: same blocks, same lambda_min, same start vector.
+    (a) 60 updates with tol = 0: first 50 residuals and the iterate; (b) solve to 1e-6 relative: iteration counts."""
+    import torch
+    from oracle import krylov_oracle as ko
+    nsb, args = env.nsb, env.args
+    H = assemble_host(args.parity_dofs)
+    ctx = env.ctx
+    rpA, ciA, vaA = H.blocks.A
+    rpB, ciB, vaB = H.blocks.B
+    A = nsb.SparseMatrix(rpA, ciA, vaA, (H.n_u, H.n_u), ctx)
+    B = nsb.SparseMatrix(rpB, ciB, vaB, (H.n_p, H.n_u), ctx)
+    pA = nsb.DiagonalPreconditioner.from_diagonal(H.dA, ctx)
+    pM = nsb.DiagonalPreconditioner.from_diagonal(H.dM, ctx)
+    with env.quiet():
+        lam = 0.9 * min(nsb.EigenValues_Preconditioner(A, pA, tol=1e-6, maxsteps=800))   # margin: Ritz values approach from above
+    k = ko.bpcg_scale(lam)
+    out = {"dofs": int(H.n_u + H.n_p), "cells": list(H.cells), "lambda_min_used": lam, "format_A": A.format(), "format_B": B.format(),
+           "oracle": "oracle/c/krylov_omp.c ko_bpcg_v2", "contract": "iterations +-1, residual history 1e-10 over 50, solution 1e-8"}
+    # (a) fixed number of updates
+    n_fix = 60
+    sol = H.u_start.copy()
+    with env.quiet():
+        nsb.BramblePasciakCG(A, B, None, H.f, H.g, pA, pM, sol, tol=0.0, maxsteps=n_fix, printrates=False, initialize=False, lam_min=lam)
+    hd = nsb.solvers.last_info["history"].copy()
+    _, ho, _, sol_o, nt = cpu_bpcg(H, k, n_fix)
+    m = min(50, len(hd), len(ho))
+    out["hist_rel_max_50"] = float(np.max(np.abs(hd[:m] - ho[:m]) / np.abs(ho[:m])))
+    out["sol_rel_after_%d_updates" % n_fix] = float(np.linalg.norm(sol - sol_o) / np.linalg.norm(sol_o))
+    # (b) to tolerance
+    tol = 1e-6
+    sol = H.u_start.copy()
+    with env.quiet():
+        it_d, _ = nsb.BramblePasciakCG(A, B, None, H.f, H.g, pA, pM, sol, tol=tol, maxsteps=3000, printrates=False, initialize=False,
+                                       lam_min=lam)
+    it_o, _, _, sol_o, _ = cpu_bpcg(H, k, 3000, tol=tol)
+    out.update(tol=tol, iterations_dev=int(it_d), iterations_oracle=int(it_o),
+               sol_rel=float(np.linalg.norm(sol - sol_o) / np.linalg.norm(sol_o)), oracle_threads=nt)
+    out["within_contract"] = bool(abs(it_d - it_o) <= 1 and out["hist_rel_max_50"] < 1e-10 and out["sol_rel_after_%d_updates" % n_fix] < 1e-8)
+    del A, B, pA, pM
+    torch.cuda.empty_cache()
+    return out
+
+
+def parity_vs_single(env, dofs=0.8e6):
+    """Inside the N-rank run: a <= 1M-dof refinement of the same channel solved row-partitioned over the N ranks and, by every
+    rank on its own GPU, alone; iteration counts, first 50 residuals, and each rank's owned rows of the solution (max over ranks)."""
+    import torch
+    nsb, syn, P = env.nsb, env.syn, env.partition
+    cells = syn.stokes_cells_for_dofs(dofs)
+    dev = "cuda:%d" % env.local
+    ctx1 = nsb.Context(device=env.local)
+    G = syn.assemble_stokes(cells, env.lengths, device=dev)
+    A1, B1 = nsb.SparseMatrix.from_csr(G.A, ctx1), nsb.SparseMatrix.from_csr(G.B, ctx1)
+    pA1 = nsb.DiagonalPreconditioner.from_diagonal(syn.jacobi_inverse(G.A, free=G.free_u), ctx1)
+    pM1 = nsb.DiagonalPreconditioner.from_diagonal(syn.jacobi_inverse(G.Mp), ctx1)
+    with env.quiet():
+        lam = 0.9 * min(nsb.EigenValues_Preconditioner(A1, pA1, tol=1e-6, maxsteps=600))
+    out = {"dofs": int(G.n_u + G.n_p), "cells": list(cells), "contract": "iterations +-1, residual history 1e-10 over 50, solution 1e-8"}
+    D = P.build_distributed_stokes(cells, env.lengths, env.ctx, env.rank, env.world, device=dev)
+    pA = nsb.DiagonalPreconditioner.from_diagonal(D.dA, env.ctx)
+    pM = nsb.DiagonalPreconditioner.from_diagonal(D.dM, env.ctx)
+    ou, op_ = D.local.owned_u, D.local.owned_p
+    res = {}
+    for tag, tol, maxsteps in (("fixed_60", 0.0, 60), ("tol_1e-8", 1e-8, 4000)):
+        sol1 = torch.cat([G.u0, torch.zeros(G.n_p, dtype=torch.float64, device=dev)])
+        with env.quiet():
+            it1, _ = nsb.BramblePasciakCG(A1, B1, None, G.f, G.g, pA1, pM1, sol1, tol=tol, maxsteps=maxsteps, printrates=False,
+                                          initialize=False, lam_min=lam)
+        h1 = nsb.solvers.last_info["history"].copy()
+        sol = D.u_start.clone()
+        env.barrier()
+        with env.quiet():
+            it, _ = nsb.BramblePasciakCG(D.A, D.B, None, D.f, D.g, pA, pM, sol, tol=tol, maxsteps=maxsteps, printrates=False,
+                                         initialize=False, lam_min=lam)
+        h = nsb.solvers.last_info["history"].copy()
+        ref_own = torch.cat([sol1[:G.n_u][ou], sol1[G.n_u:][op_]])
+        m = min(50, len(h), len(h1))
+        num = torch.stack([((sol - ref_own) ** 2).sum(), (ref_own ** 2).sum()])
+        _allreduce(env, num)
+        res[tag] = dict(it=int(it), it_single=int(it1), hist_rel=float(np.max(np.abs(h[:m] - h1[:m]) / np.abs(h1[:m]))),
+                        sol_rel=float(torch.sqrt(num[0] / num[1])))
+    out.update(iterations=res["tol_1e-8"]["it"], iterations_single=res["tol_1e-8"]["it_single"], hist_rel=res["fixed_60"]["hist_rel"],
+               sol_rel_after_60_updates=res["fixed_60"]["sol_rel"], sol_rel_at_tol_1e8=res["tol_1e-8"]["sol_rel"])
+    out["within_contract"] = bool(abs(out["iterations"] - out["iterations_single"]) <= 1 and out["hist_rel"] < 1e-10
+                                  and out["sol_rel_after_60_updates"] < 1e-8)
+    del A1, B1, pA1, pM1, D, pA, pM
+    ctx1.close()
+    torch.cuda.empty_cache()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+def simple_step_leg(env, peak, spmv_bytes, cg_vec_passes):
+    raise NotImplementedError("simple_step leg: see benchlegs_simple")

@@ -342,10 +342,9 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     NSB_CHECK(applyA(s0.p, As0.p));                                                // :202
     NSB_CHECK(vec_lincomb(c, z0.p, 1.0, As0.p, 0, nullptr, 0, nullptr, n_u));     // :203
 
-    cudaEvent_t e0, e1;
-    NSB_CUDA(cudaEventCreate(&e0));
-    NSB_CUDA(cudaEventCreate(&e1));
-    NSB_CUDA(cudaEventRecord(e0, c.stream));                                       // timer_its (:195-196)
+    EventPair ev;
+    NSB_CHECK(ev.create());
+    NSB_CUDA(cudaEventRecord(ev.e0, c.stream));                                    // timer_its (:195-196)
 
     BpcgVecs V{u0.p, u1.p, d0.p, d1.p, w0.p, w1.p, s0.p, s1.p, z0.p, tmp0.p, tmp1.p, tmp2.p, tmp3.p, dM, n_u, n_p};
     const int vg = vec_grid(n_u + n_p, c.num_sms);
@@ -395,23 +394,12 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     };
 
     const int chunk = (n_u + n_p) < 200000 ? 16 : 4;   // iterations in flight between host checks
-    cudaGraph_t graph = nullptr;
-    cudaGraphExec_t gexec = nullptr;
+    GraphExecHolder gh;
     int64_t graph_launches = 0;
     int rc = NSB_OK;
-    if (c.use_graphs && maxsteps > 0) {
-        const int64_t before = c.launches;
-        NSB_CUDA(cudaStreamBeginCapture(c.stream, cudaStreamCaptureModeThreadLocal));
-        for (int j = 0; j < chunk && rc == NSB_OK; ++j) rc = launch_iteration();
-        cudaError_t ce = cudaStreamEndCapture(c.stream, &graph);
-        graph_launches = c.launches - before;
-        c.launches = before;
-        if (rc == NSB_OK && ce != cudaSuccess) {
-            set_error("nsb_bpcg: graph capture failed: %s", cudaGetErrorString(ce));
-            rc = NSB_ERR_CUDA;
-        }
-        if (rc == NSB_OK) NSB_CUDA(cudaGraphInstantiate(&gexec, graph, 0));
-    }
+    if (c.use_graphs && maxsteps > 0)
+        rc = capture_batch(c, chunk, [&](int) { return launch_iteration(); }, &gh.exec, &graph_launches, "nsb_bpcg");
+    cudaGraphExec_t gexec = gh.exec;
     if (rc == NSB_OK)
         rc = drive_batches(c, &S->stop, maxsteps, chunk, [&]() -> int {
             if (gexec) {
@@ -426,18 +414,14 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
             for (int j = 0; j < chunk; ++j) NSB_CHECK(launch_iteration());
             return NSB_OK;
         });
-    if (gexec) cudaGraphExecDestroy(gexec);
-    if (graph) cudaGraphDestroy(graph);
     NSB_CHECK(rc);
 
-    NSB_CUDA(cudaEventRecord(e1, c.stream));
+    NSB_CUDA(cudaEventRecord(ev.e1, c.stream));
     BpcgState hs;
     NSB_CUDA(cudaMemcpyAsync(&hs, S, sizeof(BpcgState), cudaMemcpyDeviceToHost, c.stream));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
+    cudaEventElapsedTime(&ms, ev.e0, ev.e1);
     NSB_CHECK(copy_out(c, sol, u0.p, n_u));
     NSB_CHECK(copy_out(c, sol + n_u, u1.p, n_p));
     NSB_CHECK(copy_out(c, history, hist.p, hs.nupd + 1));

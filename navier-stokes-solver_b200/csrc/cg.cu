@@ -9,16 +9,11 @@
 
 #include <algorithm>
 
+#include "cg.cuh"
 #include "cond.cuh"
 #include "p2p.cuh"
 
 namespace nsb {
-
-struct CgState {
-    double wd, wdn, alpha, beta, err0, tol_abs;
-    double red[2];
-    int it, maxsteps, stop, status, record;
-};
 
 __device__ void cg_after_as(CgState* S, double as_s, double* alphas) {
     S->alpha = S->wd / as_s;
@@ -143,15 +138,9 @@ struct ResidualOp2 {  // d = rhs - A u
     __device__ void finish(const double (&)[1]) const {}
 };
 
-// shared driver: CG on (A, dinv) from residual d (already on device); u may be null (Lanczos)
-struct CgBuffers {
-    DevBuf<double> u, d, w, s, q, hist, alphas, betas;
-    DevBuf<CgState> st;
-};
-
 static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool want_u, int maxsteps, double tol,
                   bool lanczos, int chunk, bool (*host_check)(void*, const CgState&), void* check_arg, CgState* out_state,
-                  float* out_ms, nsb_cond_s* K = nullptr) {
+                  float* out_ms, nsb_cond_s* K = nullptr, CgGraph* cache = nullptr) {
     const int64_t n = A->rows;
     // a block smoother as preconditioner is applied between the update kernel and the <w,d> reduction (unfused)
     const bool general_pre = pre != nullptr && pre->kind != 0;
@@ -170,10 +159,9 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
     NSB_CHECK(vec_dot(c, b.w.p, b.d.p, n, &S->red[0]));
     k_cg_init_scalar<<<1, 1, 0, c.stream>>>(S, maxsteps, tol, hist, lanczos ? 1 : 0);
     c.launches++;
-    cudaEvent_t e0, e1;
-    NSB_CUDA(cudaEventCreate(&e0));
-    NSB_CUDA(cudaEventCreate(&e1));
-    NSB_CUDA(cudaEventRecord(e0, c.stream));
+    EventPair ev;
+    NSB_CHECK(ev.create());
+    NSB_CUDA(cudaEventRecord(ev.e0, c.stream));
     auto launch_iteration = [&]() -> int {
         if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused})));   // condensed: single-GPU
         else NSB_CHECK(spmv_exchange_launch<1>(c, A, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused}));
@@ -199,23 +187,33 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;
     };
-    cudaGraph_t graph = nullptr;
-    cudaGraphExec_t gexec = nullptr;
-    int64_t graph_launches = 0;
+    // the captured batch of `chunk` iterations; a caller that solves repeatedly on the same buffers (time stepper) keeps it
+    CgGraph local_graph;
+    CgGraph& G = cache ? *cache : local_graph;
     int rc = NSB_OK;
-    if (c.use_graphs && maxsteps > 0) {
+    if (c.use_graphs && maxsteps > 0 && (!G.exec || G.chunk != chunk)) {
+        G.reset();
         const int64_t before = c.launches;
+        cudaGraph_t graph = nullptr;
         NSB_CUDA(cudaStreamBeginCapture(c.stream, cudaStreamCaptureModeThreadLocal));
         for (int j = 0; j < chunk && rc == NSB_OK; ++j) rc = launch_iteration();
         cudaError_t ce = cudaStreamEndCapture(c.stream, &graph);
-        graph_launches = c.launches - before;
+        G.launches = c.launches - before;
+        G.chunk = chunk;
         c.launches = before;
         if (rc == NSB_OK && ce != cudaSuccess) {
             set_error("cg: graph capture failed: %s", cudaGetErrorString(ce));
             rc = NSB_ERR_CUDA;
         }
-        if (rc == NSB_OK) NSB_CUDA(cudaGraphInstantiate(&gexec, graph, 0));
+        if (rc == NSB_OK && (ce = cudaGraphInstantiate(&G.exec, graph, 0)) != cudaSuccess) {
+            set_error("cg: graph instantiation failed: %s", cudaGetErrorString(ce));
+            G.exec = nullptr;
+            rc = NSB_ERR_CUDA;
+        }
+        if (graph) cudaGraphDestroy(graph);
     }
+    cudaGraphExec_t gexec = (c.use_graphs && maxsteps > 0) ? G.exec : nullptr;
+    const int64_t graph_launches = G.launches;
     CgState hs;
     memset(&hs, 0, sizeof(hs));
     auto batch = [&]() -> int {
@@ -246,16 +244,12 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
         if (hs.stop) break;
         if (host_check && host_check(check_arg, hs)) break;
     }
-    if (gexec) cudaGraphExecDestroy(gexec);
-    if (graph) cudaGraphDestroy(graph);
     NSB_CHECK(rc);
-    NSB_CUDA(cudaEventRecord(e1, c.stream));
+    NSB_CUDA(cudaEventRecord(ev.e1, c.stream));
     NSB_CUDA(cudaMemcpyAsync(&hs, S, sizeof(CgState), cudaMemcpyDeviceToHost, c.stream));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
+    cudaEventElapsedTime(&ms, ev.e0, ev.e1);
     *out_state = hs;
     if (out_ms) *out_ms = ms;
     return NSB_OK;
@@ -367,7 +361,8 @@ __global__ void __launch_bounds__(kBlock) k_gs_scale(double* __restrict__ bj, co
 
 using namespace nsb;
 
-static int cg_alloc(Context& c, CgBuffers& b, nsb_mat A, int maxsteps, bool lanczos) {
+namespace nsb {
+int cg_alloc(Context& c, CgBuffers& b, nsb_mat_s* A, int maxsteps, bool lanczos) {
     const int64_t n = A->rows, nx = A->cols;
     NSB_CHECK(b.u.allocs(c, nx));
     NSB_CHECK(b.s.allocs(c, nx));
@@ -384,8 +379,8 @@ static int cg_alloc(Context& c, CgBuffers& b, nsb_mat A, int maxsteps, bool lanc
 }
 
 // CG on device-resident rhs (in b.q) -> b.u; used by nsb_cg and the heat stepper
-static int cg_solve_device(Context& c, nsb_mat A, nsb_pre pre, CgBuffers& b, bool initialize, int maxsteps, double tol,
-                           CgState* hs, float* ms) {
+int cg_solve_device(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool initialize, int maxsteps, double tol,
+                    CgState* hs, float* ms, CgGraph* cache) {
     const int64_t n = A->rows;
     if (initialize) {
         NSB_CHECK(vec_set(c, b.u.p, 0.0, A->cols));
@@ -395,8 +390,9 @@ static int cg_solve_device(Context& c, nsb_mat A, nsb_pre pre, CgBuffers& b, boo
         NSB_CHECK(spmv_launch<0>(c, A, b.u.p, ResidualOp2{b.q.p, b.d.p}));
     }
     const int chunk = n < 200000 ? 16 : 4;
-    return cg_run(c, A, pre, b, true, maxsteps, tol, false, chunk, nullptr, nullptr, hs, ms);
+    return cg_run(c, A, pre, b, true, maxsteps, tol, false, chunk, nullptr, nullptr, hs, ms, nullptr, cache);
 }
+}  // namespace nsb
 
 extern "C" int nsb_cg(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* rhs, double* sol, int maxsteps, double tol,
                       int initialize, double* history, int* iterations, double* seconds, int* status) {

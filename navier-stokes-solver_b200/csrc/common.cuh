@@ -404,6 +404,59 @@ int drive_batches(Context& c, const int* stop_dev, int maxsteps, int batch_iters
     return rc;
 }
 
+// two timing events that are destroyed on every exit path of a solver
+struct EventPair {
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    EventPair() = default;
+    EventPair(const EventPair&) = delete;
+    EventPair& operator=(const EventPair&) = delete;
+    int create() {
+        NSB_CUDA(cudaEventCreate(&e0));
+        NSB_CUDA(cudaEventCreate(&e1));
+        return NSB_OK;
+    }
+    ~EventPair() {
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+    }
+};
+
+// Capture `n` calls of `one()` on the context's stream into an executable graph.  On any failure nothing is leaked and *exec
+// stays null.  *launches = kernels the captured batch launches (c.launches is left as it was).
+template <class One>
+int capture_batch(Context& c, int n, One one, cudaGraphExec_t* exec, int64_t* launches, const char* who) {
+    *exec = nullptr;
+    const int64_t before = c.launches;
+    cudaGraph_t graph = nullptr;
+    NSB_CUDA(cudaStreamBeginCapture(c.stream, cudaStreamCaptureModeThreadLocal));
+    int rc = NSB_OK;
+    for (int j = 0; j < n && rc == NSB_OK; ++j) rc = one(j);
+    cudaError_t ce = cudaStreamEndCapture(c.stream, &graph);
+    *launches = c.launches - before;
+    c.launches = before;
+    if (rc == NSB_OK && ce != cudaSuccess) {
+        set_error("%s: graph capture failed: %s", who, cudaGetErrorString(ce));
+        rc = NSB_ERR_CUDA;
+    }
+    if (rc == NSB_OK && (ce = cudaGraphInstantiate(exec, graph, 0)) != cudaSuccess) {
+        set_error("%s: graph instantiation failed: %s", who, cudaGetErrorString(ce));
+        *exec = nullptr;
+        rc = NSB_ERR_CUDA;
+    }
+    if (graph) cudaGraphDestroy(graph);
+    return rc;
+}
+
+struct GraphExecHolder {
+    cudaGraphExec_t exec = nullptr;
+    GraphExecHolder() = default;
+    GraphExecHolder(const GraphExecHolder&) = delete;
+    GraphExecHolder& operator=(const GraphExecHolder&) = delete;
+    ~GraphExecHolder() {
+        if (exec) cudaGraphExecDestroy(exec);
+    }
+};
+
 int build_sell(Context& c, nsb_mat_s* m);   // sell.cu
 int build_halo_order(Context& c, nsb_mat_s* m);   // sell.cu: (re)build the interior-first chunk order of every panel for m->halo
 // exchange steps of the fused path (p2p.cu): push only; the consuming SpMV waits inside the kernel

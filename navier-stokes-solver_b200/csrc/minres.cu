@@ -278,10 +278,9 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
     c.launches++;
     NSB_CUDA(cudaGetLastError());
 
-    cudaEvent_t e0, e1;
-    NSB_CUDA(cudaEventCreate(&e0));
-    NSB_CUDA(cudaEventCreate(&e1));
-    NSB_CUDA(cudaEventRecord(e0, c.stream));
+    EventPair ev;
+    NSB_CHECK(ev.create());
+    NSB_CUDA(cudaEventRecord(ev.e0, c.stream));
 
     // ---- iteration; pointer rotation has period 6 (v,w: 3-cycles, z: 2-cycle)  (:131-133)
     auto launch_iteration = [&](int j) -> int {
@@ -314,23 +313,12 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
 
     const int period = 6;
     const int reps = n < 200000 ? 4 : 1;   // iterations in flight between host checks: period * reps
-    cudaGraph_t graph = nullptr;
-    cudaGraphExec_t gexec = nullptr;
+    GraphExecHolder gh;
     int64_t graph_launches = 0;
     int rc = NSB_OK;
-    if (c.use_graphs && maxsteps > 0) {
-        const int64_t before = c.launches;
-        NSB_CUDA(cudaStreamBeginCapture(c.stream, cudaStreamCaptureModeThreadLocal));
-        for (int j = 0; j < period && rc == NSB_OK; ++j) rc = launch_iteration(j);
-        cudaError_t ce = cudaStreamEndCapture(c.stream, &graph);
-        graph_launches = c.launches - before;
-        c.launches = before;
-        if (rc == NSB_OK && ce != cudaSuccess) {
-            set_error("nsb_minres: graph capture failed: %s", cudaGetErrorString(ce));
-            rc = NSB_ERR_CUDA;
-        }
-        if (rc == NSB_OK) NSB_CUDA(cudaGraphInstantiate(&gexec, graph, 0));
-    }
+    if (c.use_graphs && maxsteps > 0)
+        rc = capture_batch(c, period, [&](int j) { return launch_iteration(j); }, &gh.exec, &graph_launches, "nsb_minres");
+    cudaGraphExec_t gexec = gh.exec;
     if (rc == NSB_OK)
         rc = drive_batches(c, &S->stop, maxsteps, period * reps, [&]() -> int {
             for (int r = 0; r < reps; ++r) {
@@ -347,18 +335,14 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
             }
             return NSB_OK;
         });
-    if (gexec) cudaGraphExecDestroy(gexec);
-    if (graph) cudaGraphDestroy(graph);
     NSB_CHECK(rc);
 
-    NSB_CUDA(cudaEventRecord(e1, c.stream));
+    NSB_CUDA(cudaEventRecord(ev.e1, c.stream));
     MinresState hs;
     NSB_CUDA(cudaMemcpyAsync(&hs, S, sizeof(MinresState), cudaMemcpyDeviceToHost, c.stream));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
+    cudaEventElapsedTime(&ms, ev.e0, ev.e1);
     NSB_CHECK(copy_out(c, sol, u.p, n));
     NSB_CHECK(copy_out(c, history, hist.p, hs.nhist));
     NSB_CUDA(cudaStreamSynchronize(c.stream));

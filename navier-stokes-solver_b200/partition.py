@@ -339,7 +339,7 @@ def upload_halo(ctx, plan):
                     plan["recv_counts"])
 
 
-def build_distributed_stokes(cells, lengths, ctx, rank, world, device="cuda", group=None) -> DistributedStokes:
+def build_distributed_stokes(cells, lengths, ctx, rank, world, device="cuda", group=None, keep_local=False) -> DistributedStokes:
     """Assemble the rank's x-slab of the 3D/2D Taylor-Hood channel on its GPU, renumber, upload the blocks
     and attach the halo plans.  Collective over the default process group."""
     import torch.distributed as dist
@@ -363,7 +363,8 @@ def build_distributed_stokes(cells, lengths, ctx, rank, world, device="cuda", gr
     lz = 1.0 + 0.5 * torch.sin(L.owned_u.to(torch.float64) + 1.0)
     out = DistributedStokes(A, B, BT, L.dA, L.dM, L.f, L.g, u_start, lz, L, L.space_u.n_global(), L.space_p.n_global(),
                             int(counts[0]), int(counts[1]), (hu, hp))
-    L.A = L.B = L.BT = None   # the CSR triples now live in the library
+    if not keep_local:
+        L.A = L.B = L.BT = None   # the CSR triples now live in the library (kept only for local_saddle)
     return out
 
 

@@ -257,3 +257,108 @@ int ko_minres(int64_t n_u, int64_t n_p, const int64_t* Ap, const int32_t* Ac, co
     for (size_t i = 0; i < sizeof(all) / sizeof(all[0]); ++i) free(all[i]);
     return ne - 1;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * Thread count.  torch.distributed.run exports OMP_NUM_THREADS=1 into every rank; the CPU baseline of bench.py
+ * states its thread count and sets it here, whatever the launcher exported. */
+void ko_set_threads(int n) {
+    if (n > 0) omp_set_num_threads(n);
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * NGSolve CGSolver as the reference uses it (templates/NavierStokesSIMPLE_iterative.py:93,128): preconditioned CG
+ * from u = 0, err_k = sqrt<C r_k, r_k>, stop when err_k <= tol * err_0 or after maxsteps iterations; diagonal
+ * preconditioner (the reference's bddc / h1amg are NGSolve-internal).  One threaded primitive per
+ * statement of krylov_oracle.pcg.  Returns the number of iterations. */
+static int pcg(const csr_t* A, const double* dinv, const double* rhs, double* u, double tol, int maxsteps, double* d, double* w,
+               double* s, double* q) {
+    const int64_t n = A->rows;
+    memset(u, 0, sizeof(double) * (size_t)n);
+    memcpy(d, rhs, sizeof(double) * (size_t)n);
+    diagmul(w, 1.0, dinv, d, n);
+    memcpy(s, w, sizeof(double) * (size_t)n);
+    double wdn = dot(w, d, n);
+    const double err0 = sqrt(fabs(wdn));
+    if (err0 == 0.0) return 0;
+    int it = 0;
+    for (it = 1; it <= maxsteps; ++it) {
+        spmv(A, s, q);
+        const double wd = wdn;
+        const double alpha = wd / dot(s, q, n);
+        axpy(u, alpha, s, n);
+        axpy(d, -alpha, q, n);
+        diagmul(w, 1.0, dinv, d, n);
+        wdn = dot(w, d, n);
+        lin2(s, wdn / wd, s, 1.0, w, n);
+        if (sqrt(fabs(wdn)) <= tol * err0) break;
+    }
+    return it > maxsteps ? maxsteps : it;
+}
+
+int ko_pcg(const csr_t* A, const double* dinv, const double* rhs, double* u, double tol, int maxsteps) {
+    const int64_t n = A->rows;
+    double *d = vec(n), *w = vec(n), *s = vec(n), *q = vec(n);
+    const int it = pcg(A, dinv, rhs, u, tol, maxsteps, d, w, s, q);
+    free(d); free(w); free(s); free(q);
+    return it;
+}
+
+/* ext @ inv1 @ extT + inner_solve  (:94-98, :129-131) with inv1 = Jacobi-CG; H == NULL: inv1 alone.  y = result. */
+static int extended_inverse(const csr_t* M, const double* dinv, const csr_t* H, const csr_t* HT, const csr_t* inner,
+                            const double* x, double* y, double tol, int maxsteps, double* w[6]) {
+    const int64_t n = M->rows;
+    if (!H) return pcg(M, dinv, x, y, tol, maxsteps, w[0], w[1], w[2], w[3]);
+    double *r = w[4], *t = w[5];
+    spmv(HT, x, r);                                       /* r = (I + HT) x */
+    axpy(r, 1.0, x, n);
+    const int it = pcg(M, dinv, r, y, tol, maxsteps, w[0], w[1], w[2], w[3]);
+    spmv(H, y, t);                                        /* y = (I + H) y */
+    axpy(y, 1.0, t, n);
+    spmv(inner, x, t);                                    /* y += inner_solve x */
+    axpy(y, 1.0, t, n);
+    return it;
+}
+
+/* NavierStokes.DoTimeStep + Project, templates/NavierStokesSIMPLE_iterative.py:427-443, one threaded primitive per
+ * statement; gfu (length n_x) is updated in place, gfup receives tmp_projection[p_begin:p_end].  conv: the vector
+ * conv_operator * gfu.vec (the matrix-free convection stays with the caller), may be NULL; f may be NULL.
+ * ops = {a, mstar, mH, mHT, m_inner, bproj, aproj, pH, pHT, p_inner}; absent ones have rows < 0. */
+int ko_simple_step(const csr_t* ops, const double* dm, const double* dp, const int32_t* mapV, int64_t n_vel, int64_t p_begin,
+                   int64_t p_end, double dt, double prec_m, int max_m, double prec_p, int max_p, double* gfu, const double* f,
+                   const double* conv, double* gfup, int* its, double* seconds) {
+    const csr_t *a = &ops[0], *mstar = &ops[1], *mH = ops[2].rows >= 0 ? &ops[2] : NULL, *mHT = &ops[3], *minner = &ops[4];
+    const csr_t *bproj = &ops[5], *aproj = &ops[6], *pH = ops[7].rows >= 0 ? &ops[7] : NULL, *pHT = &ops[8], *pinner = &ops[9];
+    const int64_t n = a->rows, np_ = aproj->rows, nw = n > np_ ? n : np_;
+    double* w[6];
+    for (int i = 0; i < 6; ++i) w[i] = vec(nw);
+    double *temp = vec(n), *temp2 = vec(n), *rp = vec(np_), *tmp = vec(np_);
+    const double t0 = omp_get_wtime();
+    spmv(a, gfu, temp);                                   /* :432-434  temp = conv + f - a gfu */
+    scal_copy(temp, -1.0, temp, n);
+    if (conv) axpy(temp, 1.0, conv, n);
+    if (f) axpy(temp, 1.0, f, n);
+    its[0] = extended_inverse(mstar, dm, mH, mHT, minner, temp, temp2, prec_m, max_m, w);   /* :436 */
+    spmv(bproj, temp2, rp);                               /* :441 (bproj has n_vel columns: reads temp2[0:n_vel]) */
+    its[1] = extended_inverse(aproj, dp, pH, pHT, pinner, rp, tmp, prec_p, max_p, w);
+    if (gfup) memcpy(gfup, tmp + p_begin, sizeof(double) * (size_t)(p_end - p_begin));   /* :442 */
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n_vel; ++i) temp2[i] -= tmp[mapV[i]];                     /* :443 */
+    axpy(gfu, dt, temp2, n);                              /* :438 */
+    if (seconds) *seconds = omp_get_wtime() - t0;
+    for (int i = 0; i < 6; ++i) free(w[i]);
+    free(temp); free(temp2); free(rp); free(tmp);
+    return 0;
+}
+
+/* orthonormalize(basis, tries), orthonormalization.py:5-16: modified Gram-Schmidt, m vectors of length n (stride n) */
+void ko_orthonormalize(double* Q, int64_t n, int m, int tries) {
+    for (int t = 0; t < tries; ++t)
+        for (int j = 0; j < m; ++j) {
+            double* bj = Q + (int64_t)j * n;
+            for (int i = 0; i < j; ++i) {
+                const double* bi = Q + (int64_t)i * n;
+                axpy(bj, -(dot(bi, bj, n) / dot(bi, bi, n)), bi, n);   /* :11-12 */
+            }
+            scal_copy(bj, 1.0 / sqrt(dot(bj, bj, n)), bj, n);          /* :13 */
+        }
+}

@@ -47,6 +47,18 @@ def num_threads():
     return int(load().ko_num_threads())
 
 
+def set_threads(n=None):
+    """Use ``n`` OpenMP threads (default: every core this process may run on), whatever OMP_NUM_THREADS the launcher
+    exported (torch.distributed.run sets it to 1).  Returns the count now in force."""
+    if n is None:
+        try:
+            n = len(os.sched_getaffinity(0))
+        except AttributeError:
+            n = os.cpu_count() or 1
+    load().ko_set_threads(C.c_int(int(n)))
+    return num_threads()
+
+
 class Blocks:
     """CSR triples of A, B, B^T converted once (the conversion is not part of any timed region)."""
 
@@ -93,3 +105,65 @@ def minres(blocks: Blocks, dC, rhs, sol, tol=1e-7, maxsteps=100, initialize=True
     n = lib.ko_minres(*blocks.args(), _p(dC), _p(rhs), _p(sol), C.c_double(tol), C.c_int(maxsteps), C.c_int(int(initialize)),
                       _p(errors), C.byref(conv), C.byref(secs))
     return errors[:n + 1].copy(), bool(conv.value), secs.value
+
+
+class _CsrT(C.Structure):
+    _fields_ = [("rows", C.c_int64), ("cols", C.c_int64), ("rowptr", C.c_void_p), ("col", C.c_void_p), ("val", C.c_void_p)]
+
+
+def _csr_t(m, keep):
+    if m is None:
+        return _CsrT(-1, -1, None, None, None)
+    t = _csr(m)
+    keep.append(t)
+    return _CsrT(m.shape[0], m.shape[1], t[0].ctypes.data, t[1].ctypes.data, t[2].ctypes.data)
+
+
+def pcg(A, dinv, rhs, tol=1e-8, maxsteps=200):
+    """NGSolve CGSolver from u = 0 with a diagonal preconditioner -> (u, iterations)."""
+    keep = []
+    a = _csr_t(A, keep)
+    u = np.zeros(A.shape[0])
+    dinv, rhs = np.ascontiguousarray(dinv, dtype=np.float64), np.ascontiguousarray(rhs, dtype=np.float64)
+    lib = load()
+    lib.ko_pcg.restype = C.c_int
+    it = lib.ko_pcg(C.byref(a), _p(dinv), _p(rhs), _p(u), C.c_double(tol), C.c_int(maxsteps))
+    return u, it
+
+
+class SimpleOps:
+    """The ten operators of DoTimeStep / Project converted once (a, mstar, mH, mHT, m_inner, bproj, aproj, pH, pHT,
+    p_inner; the condensation parts may be None) plus the two Jacobi diagonals and the V -> Xproj index map."""
+
+    def __init__(self, a, mstar, dm, bproj, aproj, dp, mapV, n_vel, p_range, mcond=None, pcond=None):
+        self.keep = []
+        mc = mcond or {}
+        pc = pcond or {}
+        mats = [a, mstar, mc.get("H"), mc.get("HT"), mc.get("inner_solve"), bproj, aproj, pc.get("H"), pc.get("HT"),
+                pc.get("inner_solve")]
+        self.ops = (_CsrT * 10)(*[_csr_t(m, self.keep) for m in mats])
+        self.dm = np.ascontiguousarray(dm, dtype=np.float64)
+        self.dp = np.ascontiguousarray(dp, dtype=np.float64)
+        self.mapV = np.ascontiguousarray(mapV, dtype=np.int32)
+        self.n_vel, self.p_range = int(n_vel), (int(p_range[0]), int(p_range[1]))
+
+
+def simple_step(S: SimpleOps, gfu, dt, f=None, conv=None, prec_m=1e-4, max_m=200, prec_p=1e-8, max_p=200):
+    """templates/NavierStokesSIMPLE_iterative.py:427-443 -> (gfup, (its_mstar, its_proj), seconds); gfu mutated in place."""
+    lib = load()
+    gfup = np.zeros(S.p_range[1] - S.p_range[0])
+    its = (C.c_int * 2)()
+    secs = C.c_double()
+    f = None if f is None else np.ascontiguousarray(f, dtype=np.float64)
+    conv = None if conv is None else np.ascontiguousarray(conv, dtype=np.float64)
+    lib.ko_simple_step(S.ops, _p(S.dm), _p(S.dp), _p(S.mapV), C.c_int64(S.n_vel), C.c_int64(S.p_range[0]), C.c_int64(S.p_range[1]),
+                       C.c_double(dt), C.c_double(prec_m), C.c_int(max_m), C.c_double(prec_p), C.c_int(max_p), _p(gfu),
+                       _p(f) if f is not None else None, _p(conv) if conv is not None else None, _p(gfup), its, C.byref(secs))
+    return gfup, (its[0], its[1]), secs.value
+
+
+def orthonormalize(Q, tries=3):
+    """orthonormalization.py:5-16 on an (m, n) C-contiguous array, in place."""
+    m, n = Q.shape
+    load().ko_orthonormalize(_p(Q), C.c_int64(n), C.c_int(m), C.c_int(tries))
+    return Q
