@@ -250,4 +250,89 @@ def parity_vs_single(env, dofs=0.8e6):
 
 # ------------------------------------------------------------------------------------------------
 def simple_step_leg(env, peak, spmv_bytes, cg_vec_passes):
-    raise NotImplementedError("simple_step leg: see benchlegs_simple")
+    """NavierStokes.DoTimeStep + Project (templates/NavierStokesSIMPLE_iterative.py:427-443) on the bench's mesh: X = the P2 velocity
+    space (19.6M dofs), Xproj = [V2 | Q]; operators from simple_synth (same shapes and roles as the reference's forms, Jacobi in place
+    of its bddc / h1amg).  One step = nsb_simple_step: 1 SpMV(a) with the right-hand side fused, CGSolver(mstar, 1e-4), Project with
+    CGSolver(aproj, NGSolve's default precision 1e-8, step cap --simple-proj-maxsteps), gather + update.  Row-partitioned at N > 1."""
+    import torch
+    from navier_stokes_solver_b200 import simple_synth
+    args = env.args
+    dt_step = 1e-3                                   # NavierStokesSIMPLE_test.py:20 timestep
+    want_cpu = env.world == 1 and env.rank == 0 and not args.no_cpu_baseline
+    t0 = time.perf_counter()
+    D = simple_synth.build_device_simple(env.cells, env.lengths, dt_step, env.ctx, env.rank, env.world, device="cuda:%d" % env.local,
+                                         proj_maxsteps=args.simple_proj_maxsteps, keep_host=want_cpu)
+    torch.cuda.synchronize()
+    setup_s = time.perf_counter() - t0
+    st = D.stepper
+    n_x, n_proj, nnz = D.n_x_global, D.n_proj_global, D.nnz
+    its_log = []
+
+    def one():
+        st.DoTimeStep()
+        its_log.append(st.cg_iterations)
+        return st.seconds
+
+    one()                                            # warm-up: first-use set-up (graph capture of the two CG batches)
+    gfu_after_1 = st.gfu.clone()
+    its_first = its_log[0]
+    its_log.clear()
+    l0 = env.ctx.launch_count()
+    dt, loop = env.timed(args.simple_steps, one)
+    launches = (env.ctx.launch_count() - l0) // max(args.simple_steps, 1)
+    its_m = float(np.mean([i[0] for i in its_log]))
+    its_p = float(np.mean([i[1] for i in its_log]))
+    # algorithmic bytes of one step: every SpMV at 12 B/nnz + its vectors, the CG iterations at SpMV + 12 vector passes, the CG
+    # set-up (w = C d, s = w, <w,d>: 7 passes), the gather/update kernel (r gfu, temp2, tmp, 4 B index; w gfu)
+    def sp(name, r, c):
+        return spmv_bytes(r, c, nnz[name])
+    step_bytes = (sp("a", n_x, n_x) + 16 * n_x
+                  + its_m * (sp("mstar", n_x, n_x) + 8 * cg_vec_passes * n_x) + 8 * 7 * n_x
+                  + sp("bproj", n_proj, n_x) + sp("HT", n_proj, n_proj) + sp("H", n_proj, n_proj) + sp("inner", n_proj, n_proj) + 4 * 8 * n_proj
+                  + its_p * (sp("aproj", n_proj, n_proj) + 8 * cg_vec_passes * n_proj) + 8 * 7 * n_proj
+                  + 36 * n_x)
+    ms = 1e3 * dt / args.simple_steps
+    gbs = step_bytes / (ms * 1e-3) / 1e9 / env.world
+    nrm = torch.stack([(st.gfu * st.gfu).sum(), (st.gfup * st.gfup).sum()])
+    _allreduce(env, nrm)
+    out = {"workload": "DoTimeStep + Project, X.ndof = %d, Xproj.ndof = %d, timestep %g, CGSolver(mstar, Jacobi, 1e-4), CGSolver(aproj, Jacobi, "
+                       "1e-8, maxsteps %d)" % (n_x, n_proj, dt_step, args.simple_proj_maxsteps),
+           "ms_per_step": ms, "steps": args.simple_steps, "cg_iterations_mstar": its_m, "cg_iterations_projection": its_p,
+           "gpu_launches_per_step": int(launches), "algorithmic_bytes_per_step": step_bytes, "achieved_gbs_per_gpu": gbs,
+           "frac_of_measured_peak": gbs / peak, "frac_of_nominal_8TBs": gbs / 8000.0, "nnz": nnz, "setup_s": setup_s,
+           "state_after_%d_steps" % (args.simple_steps + 1): {"norm_gfu": float(torch.sqrt(nrm[0])), "norm_gfup": float(torch.sqrt(nrm[1]))},
+           "formats": {k: D.ops[k].format() for k in ("a", "aproj", "bproj", "HT")}}
+    if want_cpu:
+        from oracle import cbuild
+        H = D.host
+        nt = cbuild.set_threads()
+        ops = cbuild.SimpleOps(H["a"], H["mstar"], H["dm"], H["bproj"], H["aproj"], H["dp"], H["map"], n_x, (n_x, n_proj), None,
+                               dict(H=H["H"], HT=H["HT"], inner_solve=H["inner"]))
+        g = H["u0"].copy()
+        _, its_c, secs_c = cbuild.simple_step(ops, g, dt_step, f=H["f"], prec_m=1e-4, max_m=200, prec_p=1e-8, max_p=args.simple_proj_maxsteps)
+        ref = torch.as_tensor(g, device=gfu_after_1.device)
+        u0 = torch.as_tensor(H["u0"], device=gfu_after_1.device)
+        out["cpu_baseline"] = {"value": 1e3 * secs_c, "unit": "ms_per_step", "cores": nt, "kind": "port",
+                               "sample": "one step of the C+OpenMP port (oracle/c/krylov_omp.c: ko_simple_step, one threaded primitive per "
+                                         "reference statement) on the SAME operators", "cg_iterations": list(its_c)}
+        # Parity at full size.  CG recurrences decorrelate under rounding after ~100 iterations on systems this ill-conditioned (Jacobi
+        # in place of the reference's bddc / h1amg: the projection solve is cut off by the step cap, not converged), so the contract
+        # check runs both solves capped at 40 iterations; the uncapped step is reported beside it.
+        cap = 40
+        st40 = D.make_stepper(u0.clone(), 1e-4, cap, 1e-8, cap)
+        st40.DoTimeStep()
+        g40 = H["u0"].copy()
+        _, its40, _ = cbuild.simple_step(ops, g40, dt_step, f=H["f"], prec_m=1e-4, max_m=cap, prec_p=1e-8, max_p=cap)
+        r40 = torch.as_tensor(g40, device=u0.device)
+        out["parity_full_size"] = {"oracle": "oracle/c/krylov_omp.c ko_simple_step", "after_steps": 1,
+                                   "capped_at_%d_iterations" % cap: {"gfu_rel": float((st40.gfu - r40).norm() / r40.norm()),
+                                                                     "increment_rel": float((st40.gfu - r40).norm() / (r40 - u0).norm()),
+                                                                     "cg_iterations_dev": list(st40.cg_iterations), "cg_iterations_oracle": list(its40)},
+                                   "bench_configuration": {"gfu_rel": float((gfu_after_1 - ref).norm() / ref.norm()),
+                                                           "increment_rel": float((gfu_after_1 - ref).norm() / (ref - u0).norm()),
+                                                           "cg_iterations_dev": list(its_first), "cg_iterations_oracle": list(its_c)}}
+        out["parity_full_size"]["within_contract"] = bool(out["parity_full_size"]["capped_at_%d_iterations" % cap]["gfu_rel"] < 1e-8)
+        del st40
+    del D, st
+    torch.cuda.empty_cache()
+    return out

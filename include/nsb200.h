@@ -54,6 +54,7 @@ typedef struct nsb_mat_s* nsb_mat;
 typedef struct nsb_pre_s* nsb_pre;
 typedef struct nsb_halo_s* nsb_halo;
 typedef struct nsb_cond_s* nsb_cond;
+typedef struct nsb_simple_s* nsb_simple;
 
 /* ---- library / context ------------------------------------------------------------------- */
 NSB_API int nsb_version(void);
@@ -127,7 +128,9 @@ NSB_API int nsb_mat_set_halo(nsb_mat m, nsb_halo h);
 NSB_API int nsb_pre_create_diag(nsb_ctx ctx, int64_t n, const double* d, nsb_pre* out);
 /* Jacobi from the operator's diagonal; free_mask (n bytes, 1 = free) may be NULL */
 NSB_API int nsb_pre_create_jacobi(nsb_ctx ctx, nsb_mat m, const uint8_t* free_mask, nsb_pre* out);
-/* block-diagonal of two diagonal preconditioners: BlockMatrix([[preA, None], [None, preS]]) (run.py:46) */
+/* BlockMatrix([[preA, None], [None, preS]]) (run.py:46).  Two diagonal preconditioners are merged into one diagonal; with a
+ * block smoother / auxiliary-space composite in either block the result applies them block by block and borrows the two handles
+ * (they must outlive it; single-GPU contexts). */
 NSB_API int nsb_pre_create_blockdiag2(nsb_ctx ctx, nsb_pre a, nsb_pre b, nsb_pre* out);
 /* Block smoother: a.mat.CreateBlockSmoother(blocks) with the facet blocks of NavierStokesSIMPLE_iterative.py:360-373.
  * Disjoint dof blocks (at most 64 dofs each) in CSR-like form, listed colour by colour: blocks [color_ptr[c], color_ptr[c+1])
@@ -210,6 +213,33 @@ NSB_API int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int
  *   nsb_vec_gather_axpy:  y[i] += a x[idx[i]]    (vel.data -= mapV * tmp_projection with mapV = PermutationMatrix, :138-144,:442) */
 NSB_API int nsb_vec_axpby(nsb_ctx ctx, double* y, double a, const double* x, double b, int64_t n);
 NSB_API int nsb_vec_gather_axpy(nsb_ctx ctx, double* y, double a, const double* x, const int32_t* idx, int64_t n);
+
+/* One time step of the SIMPLE-type splitting, NavierStokes.DoTimeStep + NavierStokes.Project
+ * (templates/NavierStokesSIMPLE_iterative.py:427-443), as ONE call on a handle that owns its work vectors:
+ *     temp = conv + f - a gfu ; temp2 = invmstar temp ; Project(temp2[0:n_vel]) ; gfu += timestep temp2
+ *     Project(vel): tmp = invproj (bproj vel) ; gfup = tmp[p_begin:p_end] ; vel[i] -= tmp[map_ind[i]]
+ * with the operator compositions of :93-98 and :128-131
+ *     invmstar = (I + mstar_H) CGSolver(mstar, pre_mstar, mstar_precision) (I + mstar_HT) + mstar_inner_solve
+ *     invproj  = (I + aproj_H) CGSolver(aproj, pre_aproj, proj_precision)  (I + aproj_HT) + aproj_inner_solve
+ * (the three condensation operators of a form may all be NULL: the CG solve alone).  a, mstar: X.ndof x X.ndof; bproj:
+ * Xproj.ndof x n_vel; aproj and its condensation operators: Xproj.ndof x Xproj.ndof; map_ind (n_vel entries, host or device):
+ * the index list of PermutationMatrix(Xproj.ndof, ind) (:138-144).  CGSolver semantics as nsb_cg (start from zero, stop at
+ * sqrt<Cr,r> <= precision * initial or after maxsteps iterations; NGSolve's defaults are 1e-8 and 200).  Row-partitioned contexts:
+ * every operator carries its own halo plan, vectors hold owned rows, map_ind indexes [owned | halo of aproj].  The handle borrows
+ * all operators and preconditioners (they must outlive it). */
+NSB_API int nsb_simple_create(nsb_ctx ctx, nsb_mat a, nsb_mat mstar, nsb_pre pre_mstar, nsb_mat mstar_H, nsb_mat mstar_HT,
+                              nsb_mat mstar_inner_solve, nsb_mat bproj, nsb_mat aproj, nsb_pre pre_aproj, nsb_mat aproj_H,
+                              nsb_mat aproj_HT, nsb_mat aproj_inner_solve, const int32_t* map_ind, int64_t n_vel, int64_t p_begin,
+                              int64_t p_end, double timestep, double mstar_precision, int mstar_maxsteps, double proj_precision,
+                              int proj_maxsteps, nsb_simple* out);
+NSB_API int nsb_simple_destroy(nsb_simple s);
+/* DoTimeStep (:427-438).  gfu (X.ndof; host or device) is updated in place; f (f.vec) and conv (the vector conv_operator * gfu.vec,
+ * evaluated by the caller: the matrix-free convection form stays in NGSolve) may be NULL; gfup (p_end - p_begin entries) may be NULL.
+ * cg_iterations[0..1]: iterations of the mstar and of the projection solve; seconds: the whole step by CUDA events. */
+NSB_API int nsb_simple_step(nsb_ctx ctx, nsb_simple s, double* gfu, const double* f, const double* conv, double* gfup,
+                            int* cg_iterations, double* seconds);
+/* Project(vel) alone (:440-443; SolveInitial calls it on gfu.vec[0:V.ndof], :415,:426): vel (n_vel entries) corrected in place. */
+NSB_API int nsb_simple_project(nsb_ctx ctx, nsb_simple s, double* vel, double* gfup, int* cg_iterations);
 
 /* One pass of the time-loop body of heat.py:81-146 ("exponential integrator" in an m-dimensional subspace):
  * basis u, then m-1 implicit Euler sub-steps u -= dt H^-1 K u with dt = time_step/m (heat.py:95-98; H, the caller's

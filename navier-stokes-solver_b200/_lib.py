@@ -69,6 +69,11 @@ SIGNATURES = {
                                              P(C.c_double), P(C.c_int)]),
     "nsb_vec_axpby": (C.c_int, [c_ctx, C.c_void_p, C.c_double, C.c_void_p, C.c_double, C.c_int64]),
     "nsb_vec_gather_axpy": (C.c_int, [c_ctx, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int64]),
+    "nsb_simple_create": (C.c_int, [c_ctx, c_mat, c_mat, c_pre, c_mat, c_mat, c_mat, c_mat, c_mat, c_pre, c_mat, c_mat, c_mat, C.c_void_p,
+                                    C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int, C.c_double, C.c_int, P(C.c_void_p)]),
+    "nsb_simple_destroy": (C.c_int, [C.c_void_p]),
+    "nsb_simple_step": (C.c_int, [c_ctx, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, P(C.c_int), P(C.c_double)]),
+    "nsb_simple_project": (C.c_int, [c_ctx, C.c_void_p, C.c_void_p, C.c_void_p, P(C.c_int)]),
     "nsb_heat_step": (C.c_int, [c_ctx, c_mat, c_mat, c_mat, c_pre, C.c_void_p, C.c_double, C.c_int, C.c_int, C.c_void_p,
                                 C.c_void_p, C.c_double, C.c_int, P(C.c_int), C.c_void_p, C.c_void_p]),
 }

@@ -138,6 +138,10 @@ static int auxspace_apply(Context& c, nsb_pre_s* p, const double* x, double* y) 
 int pre_apply_device(Context& c, nsb_pre_s* p, const double* x, double* y) {
     if (p->kind == 0) return vec_diagmul(c, y, 1.0, p->d.p, x, p->n);
     if (p->kind == 2) return auxspace_apply(c, p, x, y);
+    if (p->kind == 3) {
+        NSB_CHECK(pre_apply_device(c, p->blk0, x, y));
+        return pre_apply_device(c, p->blk1, x + p->blk0->n, y + p->blk0->n);
+    }
     if (!p->gs) return block_jacobi(c, p, x, y);
     // MypreA.Mult with GS = True and no auxiliary-space term (:375-381): y = 0; Smooth(y, x); SmoothBack(y, x)
     NSB_CHECK(vec_set(c, y, 0.0, p->n));

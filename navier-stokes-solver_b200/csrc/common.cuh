@@ -215,7 +215,7 @@ struct nsb_mat_s {
 struct nsb_pre_s {
     nsb::Context* ctx = nullptr;
     int64_t n = 0;
-    int kind = 0;           // 0: diagonal (y = d .* x)   1: block smoother   2: auxiliary-space composite (blockpre.cu)
+    int kind = 0;           // 0: diagonal (y = d .* x)   1: block smoother   2: auxiliary-space composite   3: block-diagonal of two (blockpre.cu)
     nsb::DevBuf<double> d;  // diagonal preconditioner: y = d .* x
     // block smoother, a.mat.CreateBlockSmoother(blocks) (templates/NavierStokesSIMPLE_iterative.py:360-373): disjoint dof
     // blocks listed colour by colour (blocks of one colour are not coupled by the matrix), dense inverse per block
@@ -233,6 +233,8 @@ struct nsb_pre_s {
     nsb_pre_s* coarse = nullptr;           // any kind, size = transform columns
     nsb_mat_s *transform = nullptr, *transform_t = nullptr;
     nsb::DevBuf<double> aux_t, aux_c, aux_z;   // scratch: n, n_coarse, n_coarse
+    // kind 3: BlockMatrix([[blk0, None], [None, blk1]]) of two preconditioners of any kind (run.py:46), not owned
+    nsb_pre_s *blk0 = nullptr, *blk1 = nullptr;
 };
 
 namespace nsb {

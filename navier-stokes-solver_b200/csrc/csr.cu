@@ -456,12 +456,18 @@ int nsb_pre_create_jacobi(nsb_ctx ctx, nsb_mat m, const uint8_t* free_mask, nsb_
 
 int nsb_pre_create_blockdiag2(nsb_ctx ctx, nsb_pre a, nsb_pre b, nsb_pre* out) {
     NSB_REQUIRE(ctx && a && b && out, "nsb_pre_create_blockdiag2: NULL argument");
-    NSB_REQUIRE(a->kind == 0 && b->kind == 0, "nsb_pre_create_blockdiag2: diagonal preconditioners only");
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
     nsb_pre_s* p = new nsb_pre_s();
     p->ctx = &c;
     p->n = a->n + b->n;
+    if (a->kind != 0 || b->kind != 0) {   // a block smoother / composite in one of the blocks: applied block by block (borrowed handles)
+        p->kind = 3;
+        p->blk0 = a;
+        p->blk1 = b;
+        *out = p;
+        return NSB_OK;
+    }
     int r = p->d.alloc(p->n > 0 ? p->n : 1);
     if (r == NSB_OK) r = copy_in(c, p->d.p, a->d.p, a->n);
     if (r == NSB_OK) r = copy_in(c, p->d.p + a->n, b->d.p, b->n);

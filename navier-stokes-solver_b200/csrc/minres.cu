@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(kBlock) k_minres_k2(MinresState* S, const doub
                                                       const double* __restrict__ vh, const double* __restrict__ vh_old,
                                                       const double* __restrict__ dinv, double* __restrict__ vh_new,
                                                       double* __restrict__ zh_new, int64_t n, double* hist,
-                                                      double* partials, unsigned int* ticket, bool fused_scalar) {
+                                                      double* partials, unsigned int* ticket, bool fused_scalar, bool defer_pre) {
     pdl_enter();
     if (S->stop) return;
     const double ig = S->ig;
@@ -139,11 +139,13 @@ __global__ void __launch_bounds__(kBlock) k_minres_k2(MinresState* S, const doub
     double acc[1] = {0.0};
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         const double vn = ig * t[i] - c1 * vh[i] - c2 * vh_old[i];
-        const double zn = dinv ? dinv[i] * vn : vn;
         vh_new[i] = vn;
+        if (defer_pre) continue;                // a general preconditioner is applied by its own kernels behind this one
+        const double zn = dinv ? dinv[i] * vn : vn;
         zh_new[i] = zn;
         acc[0] = fma(zn, vn, acc[0]);
     }
+    if (defer_pre) return;
     if (grid_sum<1>(acc, partials, ticket)) {
         if (threadIdx.x == 0) {
             if (fused_scalar) minres_after_gamma(S, acc[0], hist);
@@ -242,8 +244,11 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
     if (pre) NSB_REQUIRE(pre->n == n, "nsb_minres: preconditioner size %lld != %lld", (long long)pre->n, (long long)n);
     const bool dist = c.nranks > 1;
     const bool fused = !dist;
-    if (pre) NSB_REQUIRE(pre->kind == 0, "nsb_minres: diagonal / block-diagonal-of-diagonal preconditioners only");
-    const double* dinv = pre ? pre->d.p : nullptr;
+    // pre: diagonal (fused into K2) or any other device preconditioner -- block smoother, auxiliary-space composite (run.py:61-62
+    // and stokes_hcurldiv.py:48 configure non-Jacobi ones) -- applied by its own kernels between K2 and the gamma reduction
+    const bool general_pre = pre != nullptr && pre->kind != 0;
+    if (general_pre) NSB_REQUIRE(!dist, "nsb_minres: block smoothers / composite preconditioners are single-GPU");
+    const double* dinv = (pre && !general_pre) ? pre->d.p : nullptr;
 
     DevBuf<double> u, t, v[3], w[3], z[2], hist, drhs;
     DevBuf<MinresState> st;
@@ -271,9 +276,14 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
     NSB_CHECK(vec_set(c, v[0].p, 0.0, n));   // v_old
     NSB_CHECK(vec_set(c, w[0].p, 0.0, n));   // w_old
     NSB_CHECK(vec_set(c, w[1].p, 0.0, n));   // w
-    k_minres_init<<<vg, kBlock, 0, c.stream>>>(S, v[1].p, dinv, z[0].p, n, c.partials, c.ticket);
-    c.launches++;
-    NSB_CHECK(allreduce_sum(c, S->red, 1));
+    if (general_pre) {
+        NSB_CHECK(pre_apply_device(c, pre, v[1].p, z[0].p));                 // z = C v (:68)
+        NSB_CHECK(vec_dot(c, z[0].p, v[1].p, n, &S->red[0]));
+    } else {
+        k_minres_init<<<vg, kBlock, 0, c.stream>>>(S, v[1].p, dinv, z[0].p, n, c.partials, c.ticket);
+        c.launches++;
+        NSB_CHECK(allreduce_sum(c, S->red, 1));
+    }
     k_minres_init_scalar<<<1, 1, 0, c.stream>>>(S, maxsteps, tol, hist.p);
     c.launches++;
     NSB_CUDA(cudaGetLastError());
@@ -298,9 +308,15 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
             c.launches++;
         }
-        NSB_CUDA(launch_k(c, 2, k_minres_k2, vg, kBlock, 0, S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, fused));
+        NSB_CUDA(launch_k(c, 2, k_minres_k2, vg, kBlock, 0, S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, fused,
+                          general_pre));
         c.launches++;
-        if (!fused && !p2p_allreduce_then(c, &S->red[1], 1, MinresPost{S, 1, hist.p})) {
+        if (general_pre) {   // z_new = C v_new (:101), gamma_new^2 = <z_new, v_new> (:103); ignored once the stop flag is up
+            NSB_CHECK(pre_apply_device(c, pre, v_new, z_new));
+            NSB_CHECK(vec_dot(c, z_new, v_new, n, &S->red[1]));
+            k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
+            c.launches++;
+        } else if (!fused && !p2p_allreduce_then(c, &S->red[1], 1, MinresPost{S, 1, hist.p})) {
             NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;

@@ -197,6 +197,44 @@ static int pick_lanes_per_row(double mean) {
     return 32;
 }
 
+__global__ void k_sell_identity_perm(unsigned short* __restrict__ perm, int64_t nvr, int mask) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvr; i += (int64_t)gridDim.x * blockDim.x)
+        perm[i] = (unsigned short)(i & mask);
+}
+
+// A row panel without a single nonzero (the condensed-out rows of a projection operator, the V2 rows of bproj): the SELL kernel
+// still has to run its row epilogue over these rows (y = 0, or xin + 0 for the fused adds), so the panel gets the smallest legal
+// shape with empty slices -- per chunk the kernel reads 2 B per row of perm plus the slice offsets and stages nothing.
+static int build_empty_panel(Context& c, SellData* ms, int64_t rows) {
+    const int log2R = 8, T = 1;
+    const int64_t R = 1LL << log2R;
+    const int nchunks = (int)((rows + R - 1) / R);
+    const int64_t nvr = (int64_t)nchunks * R, nslices = nvr / (32 / T);
+    NSB_CHECK(ms->sell_perm.alloc(nvr));
+    NSB_CHECK(ms->sell_off.alloc(nslices + 1));
+    NSB_CHECK(ms->sell_uptr.alloc(nchunks + 1));
+    NSB_CHECK(ms->sell_ucol.alloc(1));
+    NSB_CHECK(ms->sell_vals.alloc(64));
+    NSB_CHECK(ms->sell_lcol.alloc(64));
+    k_sell_identity_perm<<<vec_grid(nvr, c.num_sms), kBlock, 0, c.stream>>>(ms->sell_perm.p, nvr, (int)R - 1);
+    NSB_CUDA(cudaMemsetAsync(ms->sell_off.p, 0, sizeof(unsigned int) * (size_t)(nslices + 1), c.stream));
+    NSB_CUDA(cudaMemsetAsync(ms->sell_uptr.p, 0, sizeof(int) * (size_t)(nchunks + 1), c.stream));
+    NSB_CUDA(cudaMemsetAsync(ms->sell_ucol.p, 0, sizeof(int), c.stream));
+    NSB_CUDA(cudaMemsetAsync(ms->sell_vals.p, 0, sizeof(double) * 64, c.stream));
+    NSB_CUDA(cudaMemsetAsync(ms->sell_lcol.p, 0, sizeof(unsigned short) * 64, c.stream));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    ms->sell_R = (int)R;
+    ms->sell_log2R = log2R;
+    ms->sell_T = T;
+    ms->sell_nchunks = nchunks;
+    ms->sell_max_uniq = 0;
+    ms->sell_cap = 32;
+    ms->sell_total_uniq = 0;
+    ms->sell_stored = 0;
+    ms->sell_nruns = 0;
+    return NSB_OK;
+}
+
 // Try to build the SELL-LX storage of the row panel [row0, row0 + rows) of m into S.  Leaves S.sell_R == 0 when the
 // panel does not qualify.
 static int build_sell_panel(Context& c, nsb_mat_s* m, int64_t row0, int64_t rows, SellData& S_) {
@@ -211,7 +249,7 @@ static int build_sell_panel(Context& c, nsb_mat_s* m, int64_t row0, int64_t rows
     NSB_CUDA(cudaMemcpy(&pends[1], m->rowptr.p + row0 + rows, sizeof(int), cudaMemcpyDeviceToHost));
     const int pbase = pends[0];
     const int64_t nnz = (int64_t)pends[1] - pends[0];
-    if (nnz < 1) return NSB_OK;
+    if (nnz < 1) return build_empty_panel(c, ms, rows);
     const double mean = (double)nnz / (double)rows;
     const int T = pick_lanes_per_row(mean);
     const int rps = 32 / T;

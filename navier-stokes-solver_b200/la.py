@@ -731,17 +731,20 @@ class BlockMatrix(BaseMatrix):
             self._K = SparseMatrix._wrap(h, ctx)
         return self._K
 
-    def blockdiag_preconditioner(self) -> DiagonalPreconditioner:
+    def blockdiag_preconditioner(self):
+        """[[pre0, None], [None, pre1]] (run.py:46) of device preconditioners: two Jacobi blocks merge into one diagonal, a block
+        smoother / auxiliary-space composite in either block gives a block-by-block composite."""
         if self._P is None:
             (p0, z01), (z10, p1) = self.rows
-            if z01 is not None or z10 is not None or not isinstance(p0, DiagonalPreconditioner) \
-                    or not isinstance(p1, DiagonalPreconditioner):
-                raise TypeError("block preconditioner must be [[pre0, None], [None, pre1]] of diagonal device "
-                                "preconditioners (no CPU fallback for general operators)")
+            kinds = (DiagonalPreconditioner, BlockSmoother, AuxiliarySpacePreconditioner)
+            if z01 is not None or z10 is not None or not isinstance(p0, kinds) or not isinstance(p1, kinds):
+                raise TypeError("block preconditioner must be [[pre0, None], [None, pre1]] of device preconditioners (Jacobi, block "
+                                "smoother, auxiliary-space composite); there is no CPU fallback for general operators")
             ctx = p0.ctx
             h = _lib.c_pre()
             _lib.check(ctx._lib.nsb_pre_create_blockdiag2(ctx.h, p0.h, p1.h, C.byref(h)), "nsb_pre_create_blockdiag2")
             self._P = DiagonalPreconditioner(h, p0.n + p1.n, ctx)
+            self._P._blocks = (p0, p1)      # borrowed by the composite handle
         return self._P
 
     def __mul__(self, v):

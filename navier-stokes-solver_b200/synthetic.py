@@ -241,7 +241,7 @@ def _lattice_index(idx, dims):
 
 
 def assemble_stokes(cells, lengths=None, nu=1.0, device="cpu", slab=None, nslabs=1,
-                    outlet=True, with_mass2=False) -> StokesSystem:
+                    outlet=True, with_mass2=False, vrange=None, parts=("A", "B", "BT", "Mp")) -> StokesSystem:
     """Taylor-Hood P2/P1 Stokes blocks on a box ``[0,L_0] x ...`` split into ``cells`` cubes, each
     cut into d! Kuhn simplices.
 
@@ -250,7 +250,9 @@ def assemble_stokes(cells, lengths=None, nu=1.0, device="cpu", slab=None, nslabs
     parabolic profile of the reference scripts.
 
     ``slab``/``nslabs``: assemble only the rows owned by x-slab ``slab`` of ``nslabs`` (row partition
-    of SURVEY.md 8(e)); columns stay global.
+    of SURVEY.md 8(e)); columns stay global.  ``vrange = (v0, v1)``: the rows of the vertex planes [v0, v1) instead
+    (an arbitrary slab, e.g. a rank's rows plus the neighbouring planes).  ``parts``: which blocks to build (the others
+    are None).
     """
     d = len(cells)
     cells = tuple(int(c) for c in cells)
@@ -269,7 +271,11 @@ def assemble_stokes(cells, lengths=None, nu=1.0, device="cpu", slab=None, nslabs
     def vertex_cut(s):
         return (cells[0] + 1) * s // nslabs  # first owned vertex plane of slab s
 
-    if slab is None:
+    if vrange is not None:
+        vx0, vx1 = max(int(vrange[0]), 0), min(int(vrange[1]), cells[0] + 1)
+        cx0, cx1 = max(vx0 - 1, 0), min(vx1, cells[0])
+        slab = -1   # "not the whole mesh"
+    elif slab is None:
         vx0, vx1 = 0, cells[0] + 1
         cx0, cx1 = 0, cells[0]
     else:
@@ -306,24 +312,29 @@ def assemble_stokes(cells, lengths=None, nu=1.0, device="cpu", slab=None, nslabs
         dof1 = _lattice_index(vtx, dims1)                             # ne x (d+1)
         nP2 = dof2.shape[1]
         K2 = torch.as_tensor(loc["K2"] * nu, device=dev)
-        r = dof2[:, :, None].expand(ne, nP2, nP2).reshape(-1)
-        c = dof2[:, None, :].expand(ne, nP2, nP2).reshape(-1)
-        coo["A1"][0].append(r); coo["A1"][1].append(c)
-        coo["A1"][2].append(K2[None].expand(ne, nP2, nP2).reshape(-1))
+        if "A" in parts or with_mass2:
+            r = dof2[:, :, None].expand(ne, nP2, nP2).reshape(-1)
+            c = dof2[:, None, :].expand(ne, nP2, nP2).reshape(-1)
+        if "A" in parts:
+            coo["A1"][0].append(r); coo["A1"][1].append(c)
+            coo["A1"][2].append(K2[None].expand(ne, nP2, nP2).reshape(-1))
         if with_mass2:
             coo["M2"][0].append(r); coo["M2"][1].append(c)
             coo["M2"][2].append(torch.as_tensor(loc["M2"], device=dev)[None].expand(ne, nP2, nP2).reshape(-1))
-        for comp in range(d):
+        for comp in range(d if ("B" in parts or "BT" in parts) else 0):
             Bl = torch.as_tensor(loc["Bc"][comp], device=dev)        # (d+1) x nP2
             r1 = dof1[:, :, None].expand(ne, d + 1, nP2).reshape(-1)
             c1 = (dof2 + comp * n2)[:, None, :].expand(ne, d + 1, nP2).reshape(-1)
             v1 = Bl[None].expand(ne, d + 1, nP2).reshape(-1)
-            coo["B"][0].append(r1); coo["B"][1].append(c1); coo["B"][2].append(v1)
-            coo["BT"][0].append(c1); coo["BT"][1].append(r1); coo["BT"][2].append(v1)
-        M1 = torch.as_tensor(loc["M1"], device=dev)
-        coo["Mp"][0].append(dof1[:, :, None].expand(ne, d + 1, d + 1).reshape(-1))
-        coo["Mp"][1].append(dof1[:, None, :].expand(ne, d + 1, d + 1).reshape(-1))
-        coo["Mp"][2].append(M1[None].expand(ne, d + 1, d + 1).reshape(-1))
+            if "B" in parts:
+                coo["B"][0].append(r1); coo["B"][1].append(c1); coo["B"][2].append(v1)
+            if "BT" in parts:
+                coo["BT"][0].append(c1); coo["BT"][1].append(r1); coo["BT"][2].append(v1)
+        if "Mp" in parts:
+            M1 = torch.as_tensor(loc["M1"], device=dev)
+            coo["Mp"][0].append(dof1[:, :, None].expand(ne, d + 1, d + 1).reshape(-1))
+            coo["Mp"][1].append(dof1[:, None, :].expand(ne, d + 1, d + 1).reshape(-1))
+            coo["Mp"][2].append(M1[None].expand(ne, d + 1, d + 1).reshape(-1))
         # f = int (x - 0.5) v_1 : x = sum_k x_k lambda_k   (component 1, run.py:92-94)
         T = torch.as_tensor(loc["T"], device=dev)                     # (d+1) x nP2
         xk = vtx[:, :, 0].to(torch.float64) * h[0] - 0.5              # ne x (d+1)
@@ -336,22 +347,25 @@ def assemble_stokes(cells, lengths=None, nu=1.0, device="cpu", slab=None, nslabs
         return _coo_to_csr(r, c, v, shape, rows_sel)
 
     whole = slab is None
-    A1 = build("A1", (n2, n2), None if whole else own_nodes2)
-    # vector Laplacian: d copies of the scalar block on the diagonal (component-major)
-    nr1 = A1.shape[0]
-    counts = A1.rowptr[1:] - A1.rowptr[:-1]
-    rowptr = torch.zeros(d * nr1 + 1, dtype=torch.int64, device=dev)
-    rowptr[1:] = torch.cumsum(counts.repeat(d), 0)
-    colidx = torch.cat([(A1.colidx.to(torch.int64) + comp * n2).to(torch.int32) for comp in range(d)])
-    A = CSR((d * nr1, n_u), rowptr, colidx, A1.values.repeat(d))
     extras = {}
+    A = None
+    if "A" in parts:
+        A1 = build("A1", (n2, n2), None if whole else own_nodes2)
+        # vector Laplacian: d copies of the scalar block on the diagonal (component-major)
+        nr1 = A1.shape[0]
+        counts = A1.rowptr[1:] - A1.rowptr[:-1]
+        rowptr = torch.zeros(d * nr1 + 1, dtype=torch.int64, device=dev)
+        rowptr[1:] = torch.cumsum(counts.repeat(d), 0)
+        colidx = torch.cat([(A1.colidx.to(torch.int64) + comp * n2).to(torch.int32) for comp in range(d)])
+        A = CSR((d * nr1, n_u), rowptr, colidx, A1.values.repeat(d))
+        if with_mass2:
+            extras["K2"] = A1
+        del A1
     if with_mass2:
         extras["M2"] = build("M2", (n2, n2), None if whole else own_nodes2)
-        extras["K2"] = A1
-    del A1
-    B = build("B", (n1, n_u), None if whole else owned_p)
-    BT = build("BT", (n_u, n1), None if whole else owned_u)
-    Mp = build("Mp", (n1, n1), None if whole else owned_p)
+    B = build("B", (n1, n_u), None if whole else owned_p) if "B" in parts else None
+    BT = build("BT", (n_u, n1), None if whole else owned_u) if "BT" in parts else None
+    Mp = build("Mp", (n1, n1), None if whole else owned_p) if "Mp" in parts else None
 
     # load vector, deterministic accumulation: sort by row then segmented sum via the CSR helper
     fr = torch.cat(f_rows); fv = torch.cat(f_vals)

@@ -127,7 +127,7 @@ def heat_case(cells=(10, 10)):
     return K, M, free, (x, y), u0
 
 
-def simple_case(mesh_cells=(12, 4), lengths=(2.0, 0.41), dt=1e-3, seed=5):
+def simple_case(mesh_cells=(12, 4), lengths=(2.0, 0.41), dt=1e-3, seed=5, perm="random"):
     """Synthetic operators with the shapes of NavierStokesSIMPLE_iterative.py:79-144: a, mstar = M + dt a, the mixed
     projection system [[-Ml, B^T], [B, 0]] condensed onto the pressure (diagonal mass Ml), bproj = [0; B], mapV a
     permutation between the continuous (V) and the 'broken' (V2) velocity numbering."""
@@ -141,8 +141,12 @@ def simple_case(mesh_cells=(12, 4), lengths=(2.0, 0.41), dt=1e-3, seed=5):
     M = sp.kron(sp.identity(d), S.extras["M2"].to_scipy()).tocsr()
     mstar = (M + dt * A).tocsr()
     n_u, n_p = S.n_u, S.n_p
-    rng = np.random.default_rng(seed)
-    perm = rng.permutation(n_u)                         # V dof i lives at V2 dof perm[i]
+    if isinstance(perm, str) and perm == "rotate":      # V dof (c, node) lives at V2 dof ((c + 1) % d, node): node-local
+        n2 = n_u // d
+        perm = (np.arange(n_u) + n2) % n_u
+    else:
+        rng = np.random.default_rng(seed)
+        perm = rng.permutation(n_u)                     # V dof i lives at V2 dof perm[i]
     Ml = M.diagonal()                                   # (row sums vanish at P2 vertices; the diagonal is positive)
     Bf = (B @ sp.diags(free.astype(float))).tocsr()
     P = sp.csr_matrix((np.ones(n_u), (perm, np.arange(n_u))), shape=(n_u, n_u))   # V -> V2

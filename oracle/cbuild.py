@@ -114,6 +114,11 @@ class _CsrT(C.Structure):
 def _csr_t(m, keep):
     if m is None:
         return _CsrT(-1, -1, None, None, None)
+    if isinstance(m, tuple):      # (shape, rowptr int64, col int32, val float64) already in the C layout
+        shape, rp, ci, va = m
+        t = (np.ascontiguousarray(rp, dtype=np.int64), np.ascontiguousarray(ci, dtype=np.int32), np.ascontiguousarray(va, dtype=np.float64))
+        keep.append(t)
+        return _CsrT(shape[0], shape[1], t[0].ctypes.data, t[1].ctypes.data, t[2].ctypes.data)
     t = _csr(m)
     keep.append(t)
     return _CsrT(m.shape[0], m.shape[1], t[0].ctypes.data, t[1].ctypes.data, t[2].ctypes.data)

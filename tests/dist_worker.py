@@ -81,6 +81,20 @@ def main():
     res.update(minres_it=len(merr) - 1, minres_it1=len(merr1) - 1,
                minres_hist_rel=float(np.max(np.abs(np.array(merr[:mm]) - np.array(merr1[:mm])) / np.abs(np.array(merr1[:mm])))),
                minres_sol_rel=float((msol - mref).norm() / mref.norm()))
+    # SIMPLE time step (nsb_simple_step) row-partitioned vs the same steps on one GPU
+    import navier_stokes_solver_b200.simple_synth as ss
+    kw = dict(proj_precision=1e-10, proj_maxsteps=3000, mstar_precision=1e-10, mstar_maxsteps=500)
+    D1 = ss.build_device_simple(CELLS, LENGTHS, 1e-3, ctx1, device=dev, **kw)
+    DN = ss.build_device_simple(CELLS, LENGTHS, 1e-3, ctx, rank, world, device=dev, **kw)
+    for _ in range(2):
+        D1.stepper.DoTimeStep()
+        DN.stepper.DoTimeStep()
+    own = DN.sys.owned_u
+    g1 = D1.stepper.gfu[own]
+    p1 = D1.stepper.gfup[DN.sys.owned_p]
+    res.update(simple_gfu_rel=float((DN.stepper.gfu - g1).norm() / g1.norm()),
+               simple_gfup_rel=float((DN.stepper.gfup - p1).norm() / max(float(p1.norm()), 1e-300)),
+               simple_its=list(DN.stepper.cg_iterations), simple_its1=list(D1.stepper.cg_iterations))
     print("DISTRESULT " + json.dumps(res), flush=True)
     dist.barrier()
     dist.destroy_process_group()

@@ -43,3 +43,5 @@ def test_two_rank_bpcg_and_minres_match_single_gpu(sell, fused_halo):
         assert abs(r["minres_it"] - r["minres_it1"]) <= 1, r
         assert r["minres_hist_rel"] < 1e-10, r
         assert r["minres_sol_rel"] < 1e-8, r
+        assert r["simple_gfu_rel"] < 1e-8 and r["simple_gfup_rel"] < 1e-6, r
+        assert all(abs(a - b) <= 1 for a, b in zip(r["simple_its"], r["simple_its1"])), r

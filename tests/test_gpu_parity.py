@@ -784,3 +784,94 @@ def test_auxiliary_space_preconditioner_matches_oracle(nsb, cases, GS):
                                          nsb.DiagonalPreconditioner.from_diagonal(dc))
     with pytest.raises(nsb._lib.NsbError):
         nsb.AuxiliarySpacePreconditioner(sm, nsb.SparseMatrix.from_scipy(T), nsb.DiagonalPreconditioner.from_diagonal(c.dA))
+
+
+# ------------------------------------------------------------------------------------------ nsb_simple_step
+@pytest.mark.parametrize("sell", ["0", "200000"])
+def test_empty_row_panels_run_the_row_epilogue(nsb, monkeypatch, sell):
+    """Operators whose row panels are partly EMPTY (bproj = [0; B], aproj = [[0,0],[0,S]]): y = M x and the fused adds still
+    cover the empty rows (SELL-LX: degenerate panel shape; CSR-vector otherwise)."""
+    import scipy.sparse as sp
+    monkeypatch.setenv("NSB_SELL_MIN_NNZ", sell)
+    rng = np.random.default_rng(11)
+    n_top, n_bot, n_c = 700, 300, 450
+    Bm = sp.random(n_bot, n_c, density=0.15, random_state=5, format="csr")
+    for M in (sp.vstack([sp.csr_matrix((n_top, n_c)), Bm]).tocsr(), sp.vstack([Bm, sp.csr_matrix((n_top, n_c))]).tocsr()):
+        A = nsb.SparseMatrix.from_scipy(M)
+        A.set_row_panels([0, n_top, n_top + n_bot] if M[:n_top].nnz == 0 else [0, n_bot, n_top + n_bot])
+        x = rng.uniform(-1, 1, n_c)
+        np.testing.assert_allclose((A * x).NumPy(), M @ x, rtol=0, atol=1e-13)
+        if sell == "0":
+            assert A.format()["rows_per_chunk"] > 0
+
+
+@pytest.mark.parametrize("sell", ["0", "200000"])
+def test_simple_stepper_on_the_synthetic_channel_matches_c_oracle(nsb, monkeypatch, sell):
+    """The bench's SIMPLE operators (simple_synth, 3D channel, V2 = rotated components) through nsb_simple_step against the C
+    oracle's ko_simple_step on the same operators: CG iteration counts, velocity after each of 3 steps, projection pressure."""
+    import torch
+    import navier_stokes_solver_b200.simple_synth as ss
+    from oracle import cbuild
+    monkeypatch.setenv("NSB_SELL_MIN_NNZ", sell)
+    cells, lengths, dt = (10, 4, 3), (2.5, 0.41, 0.41), 1e-3
+    D = ss.build_device_simple(cells, lengths, dt, nsb.default_context(), proj_precision=1e-10, proj_maxsteps=3000, mstar_precision=1e-10,
+                               mstar_maxsteps=500, keep_host=True)
+    H = D.host
+    n_x, n_proj = D.n_x_global, D.n_proj_global
+    ops = cbuild.SimpleOps(H["a"], H["mstar"], H["dm"], H["bproj"], H["aproj"], H["dp"], H["map"], n_x, (n_x, n_proj), None,
+                           dict(H=H["H"], HT=H["HT"], inner_solve=H["inner"]))
+    g = H["u0"].copy()
+    st = D.stepper
+    for step in range(3):
+        gp, its, _ = cbuild.simple_step(ops, g, dt, f=H["f"], prec_m=1e-10, max_m=500, prec_p=1e-10, max_p=3000)
+        st.DoTimeStep()
+        assert abs(st.cg_iterations[0] - its[0]) <= 1 and abs(st.cg_iterations[1] - its[1]) <= 1, (st.cg_iterations, its)
+        assert relerr(st.gfu.cpu().numpy(), g) < SOL_RTOL
+        assert relerr(st.gfup.cpu().numpy(), gp) < 1e-6
+    # the projected increment is discretely divergence-free on the free dofs
+    Bf = D.sys.Bf.to_scipy()
+    div = Bf @ (st.gfu.cpu().numpy() - H["u0"])
+    assert np.abs(div).max() < 1e-7 * np.abs(Bf).sum(axis=1).max() * np.abs(st.gfu.cpu().numpy() - H["u0"]).max()
+    # Project alone on a host vector (SolveInitial's use, :415)
+    vel = np.random.default_rng(2).uniform(-1, 1, n_x) * D.sys.free_u.cpu().numpy()
+    ref = vel.copy()
+    st.Project(vel)
+    assert np.abs(Bf @ vel).max() < 1e-6 * np.abs(Bf @ ref).max()
+
+
+def test_simple_stepper_rejects_host_inverses(nsb):
+    import scipy.sparse as sp
+    import torch
+    A = nsb.SparseMatrix.from_scipy(sp.identity(4, format="csr"))
+    with pytest.raises(TypeError):
+        nsb.SimpleStepper(A, object(), A, object(), nsb.PermutationMatrix(4, [0, 1, 2, 3]), torch.zeros(4, dtype=torch.float64, device="cuda"),
+                          4, (0, 4), 1e-3)
+
+
+@pytest.mark.parametrize("gauss_seidel", [False, True])
+def test_minres_with_block_smoother_preconditioner(nsb, cases, gauss_seidel):
+    """MinRes takes any `pre` (minres.py:68,101); run.py:61-62 pairs a non-Jacobi velocity preconditioner with 'local' on the
+    pressure mass: C = BlockMatrix([[preA, None], [None, preS]]) with MypreA's block smoother as preA, against the oracle."""
+    from oracle import krylov_oracle as ko
+    c = cases("chan2d")
+    A, B = nsb.SparseMatrix.from_scipy(c.A), nsb.SparseMatrix.from_scipy(c.B)
+    preA = A.CreateBlockSmoother(_blocks_of(c, 4), pattern=c.A, gauss_seidel=gauss_seidel)
+    ref = ko.BlockSmoother(c.A, preA.blocks)
+    pa = ref.symmetric_gs if gauss_seidel else ref.jacobi
+    K = nsb.BlockMatrix([[A, B.T], [B, None]])
+    C = nsb.BlockMatrix([[preA, None], [None, nsb.DiagonalPreconditioner.from_diagonal(c.dM)]])
+    sol = c.start()
+    (u, errors), _ = quiet(nsb.MinRes, mat=K, pre=C, rhs=c.rhs(), sol=sol, initialize=False, tol=1e-8, maxsteps=5000)
+    sol_ref = c.start()
+    pre_ref = lambda v: np.concatenate([pa(v[:c.n_u]), c.dM * v[c.n_u:]])
+    _, eref, _ = ko.minres(ko.SaddleOperator(c.A, c.B, c.BT), c.rhs(), pre=pre_ref, sol=sol_ref, maxsteps=5000, initialize=False, tol=1e-8)
+    assert abs(len(errors) - len(eref)) <= 1
+    m = min(50, len(errors), len(eref))
+    np.testing.assert_allclose(errors[:m], eref[:m], rtol=HIST_RTOL)
+    assert relerr(sol, sol_ref) < 1e-7
+    assert len(errors) < 0.8 * len(load_minres_len("minres_chan2d"))   # the smoother beats Jacobi
+
+
+def load_minres_len(name):
+    from oracle.cases import load_golden
+    return load_golden(name)["errors"]
