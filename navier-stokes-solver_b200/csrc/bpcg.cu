@@ -84,6 +84,8 @@ struct BpcgB1Op {
     double* __restrict__ tmp0;
     double* __restrict__ tmp1;
     double* __restrict__ tmp4;
+    PushOut push;   // row-partitioned: the interface rows of tmp1 / tmp4 go straight into the neighbours' landing buffers (areas 0 / 1)
+    __device__ const PushOut& push_out() const { return push; }
     __device__ bool skip() const { return S->stop != 0; }
     struct Pre {
         double as0, z, d, s, w;
@@ -101,6 +103,10 @@ struct BpcgB1Op {
         tmp4[i] = t1 - sn;
     }
     __device__ void row(int64_t i, double ax, double (&acc)[1]) const { apply(i, ax, load(i), acc); }
+    __device__ void row_pushing(int64_t i, double ax, double (&acc)[1]) const {   // rows of a chunk that holds interface rows
+        apply(i, ax, load(i), acc);
+        push_store<true>(push, i, tmp1[i], tmp4[i]);
+    }
     __device__ void finish(const double (&)[1]) const {}
 };
 
@@ -127,7 +133,7 @@ struct BpcgB2Op {
     double* __restrict__ tmp2;
     const double* __restrict__ tmp0;
     const double* __restrict__ s0;
-    bool fused;
+    int red_kind;   // kRedLocal: the total is kept for B3's scalar step; else: it goes to the all-reduce landing zone
     __device__ bool skip() const { return S->stop != 0; }
     struct Pre {
         double s, t0;
@@ -139,7 +145,7 @@ struct BpcgB2Op {
     }
     __device__ void row(int64_t i, double ax, double (&acc)[1]) const { apply(i, ax, load(i), acc); }
     __device__ void finish(const double (&tot)[1]) const {
-        if (fused) S->as_part = tot[0];
+        if (red_kind == kRedLocal) S->as_part = tot[0];
         else S->red[0] = tot[0];
     }
 };
@@ -148,7 +154,7 @@ struct BpcgB3Op {
     BpcgState* S;
     double* __restrict__ tmp3;
     const double* __restrict__ s1;
-    bool fused;
+    RedMode red;
     __device__ bool skip() const { return S->stop != 0; }
     struct Pre {
         double s;
@@ -159,10 +165,18 @@ struct BpcgB3Op {
         acc[0] = fma(p.s, ax, acc[0]);
     }
     __device__ void row(int64_t j, double ax, double (&acc)[1]) const { apply(j, ax, load(j), acc); }
-    __device__ void finish(const double (&tot)[1]) const {
-        if (fused) bpcg_after_as(S, S->as_part, tot[0]);
-        else S->red[1] = tot[0];
+    // last block, all threads: <s,v> = red[0] (A SpMV, earlier kernel) + red[1] summed over the ranks, then alpha (:222-226)
+    using BlockFinish = void;
+    __device__ void finish_block(const double (&tot)[1]) const {
+        if (red.kind == kRedLocal) {
+            if (threadIdx.x == 0) bpcg_after_as(S, S->as_part, tot[0]);
+            return;
+        }
+        if (threadIdx.x == 0) S->red[1] = tot[0];
+        BpcgState* St = S;
+        reduce_finish(red, &S->red[0], 2, [St]() { bpcg_after_as(St, St->red[0], St->red[1]); });
     }
+    __device__ void finish(const double (&tot)[1]) const { S->red[1] = tot[0]; }
 };
 
 struct BpcgVecs {
@@ -172,7 +186,7 @@ struct BpcgVecs {
 };
 
 __global__ void __launch_bounds__(kBlock) k_bpcg_b4(BpcgState* S, BpcgVecs V, double* hist, double* partials,
-                                                    unsigned int* ticket, bool fused) {
+                                                    unsigned int* ticket, RedMode red) {
     pdl_enter();
     if (S->stop) return;
     const double a = S->alpha;
@@ -199,21 +213,30 @@ __global__ void __launch_bounds__(kBlock) k_bpcg_b4(BpcgState* S, BpcgVecs V, do
             acc[0] = fma(w, d, acc[0]);
         }
     }
-    if (grid_sum<1>(acc, partials, ticket)) {
-        if (threadIdx.x == 0) {
-            if (fused) bpcg_after_wd(S, acc[0], hist);
-            else S->red[2] = acc[0];
-        }
+    if (grid_sum<1>(acc, partials, ticket)) {   // last block: <w,d> over the ranks, then beta, err, exit test (:235-247)
+        if (threadIdx.x == 0) S->red[2] = acc[0];
+        reduce_finish(red, &S->red[2], 1, [S, hist]() { bpcg_after_wd(S, S->red[2], hist); });
     }
 }
 
 // s1 = beta s1 + w1 (:240-241, pressure part; the velocity part rides in B1's epilogue of the next pass)
-__global__ void __launch_bounds__(kBlock) k_bpcg_b5(const BpcgState* S, BpcgVecs V) {
+// Row-partitioned: the interface rows of the new s1 go straight into the neighbours' landing buffers (the B^T SpMV of the next
+// pass takes them from there).
+__global__ void __launch_bounds__(kBlock) k_bpcg_b5(const BpcgState* S, BpcgVecs V, PushOut P) {
     pdl_enter();
     if (S->stop) return;
     const double b = S->beta;
-    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < V.n_p; j += (int64_t)gridDim.x * blockDim.x)
-        V.s1[j] = b * V.s1[j] + V.w1[j];
+    u64 e = 0;
+    if (P.nruns > 0) {
+        e = push_begin(P);
+        push_wait_consumed(P, e);
+    }
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < V.n_p; j += (int64_t)gridDim.x * blockDim.x) {
+        const double v = b * V.s1[j] + V.w1[j];
+        V.s1[j] = v;
+        if (P.nruns > 0 && push_tile(P, j)) push_store<false>(P, j, v, 0.0);
+    }
+    if (P.nruns > 0) push_end(P, e);
 }
 
 __global__ void k_bpcg_init_scalar(BpcgState* S, double k, double wdn_u, const double* wdn_dev, int maxsteps, double tol,
@@ -266,7 +289,6 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     NSB_REQUIRE(preA->n == n_u, "nsb_bpcg: preA size mismatch");
     if (preM) NSB_REQUIRE(preM->n == n_p, "nsb_bpcg: preM size mismatch");
     NSB_REQUIRE(maxsteps >= 0, "nsb_bpcg: maxsteps < 0");
-    const bool fused = c.nranks == 1;
     // preA: diagonal (fused into the SpMV epilogues) or a block smoother (MypreA's Jacobi / Gauss-Seidel part,
     // NavierStokesSIMPLE_iterative.py:364-383), applied as its own kernels between B1 and B2
     const bool general_pre = preA->kind != 0;
@@ -351,43 +373,55 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     // row-partitioned with the peer-memory path: tmp1 and tmp4 are pushed together and the A and B SpMVs each wait
     // for their landing area inside the kernel (interior chunks first), no wait/copy kernels in between
     const bool fused_AB = A->halo && A->halo == B->halo && halo_fused_ok(c, A) && halo_fused_ok(c, B) && !(K || general_pre);
+    // ... and the vectors are pushed by the kernels that PRODUCE them: tmp1 / tmp4 from the row epilogue of the B^T SpMV, the new
+    // s1 from the pressure-direction kernel; both reductions end in the last block of the kernel that formed the partial sums
+    // (peer all-reduce + scalar step).  A row-partitioned iteration is then the same five launches as on one GPU.
+    const RedMode red = red_mode(c);
+    const int rk = red.kind;
+    PushOut push_u, push_p;
+    memset(&push_u, 0, sizeof(push_u));
+    memset(&push_p, 0, sizeof(push_p));
+    if (fused_AB && push_fused_ok(c, A) && push_fused_ok(c, B) && BT->panels.size() == 1) push_u = p2p_push_out(A->halo);
+    if (!(K || general_pre) && BT->halo && push_fused_ok(c, BT)) push_p = p2p_push_out(BT->halo);
+    if (push_p.nruns > 0) NSB_CHECK(p2p_halo_push(c, BT->halo, s1.p));   // the first pass finds s1's interface entries pushed
+    auto reduce_unfused = [&](double* vals, int count, int which) -> int {   // NCCL fallback: all-reduce + scalar kernel
+        if (rk != kRedStore) return NSB_OK;
+        NSB_CHECK(allreduce_sum(c, vals, count));
+        k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, which, hist.p);
+        c.launches++;
+        return NSB_OK;
+    };
     auto launch_iteration = [&]() -> int {
         if (K || general_pre) {
             NSB_CHECK(halo_exchange(c, BT->halo, s1.p));
             NSB_CHECK(spmv_launch<0>(c, BT, s1.p, BpcgB1cOp{S, As0.p, z0.p, s0.p, w0.p, tmp0.p}));
             NSB_CHECK(applyPre(tmp0.p, tmp1.p));                                                   // :209
             NSB_CHECK(vec_lincomb(c, tmp4.p, 1.0, tmp1.p, -1.0, s0.p, 0, nullptr, n_u));           // :212
-            if (K) NSB_CHECK((cond_apply_A<1>(c, K, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused})));   // :210,:218,:222
-            else NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
+            if (K) NSB_CHECK((cond_apply_A<1>(c, K, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, rk})));   // :210,:218,:222
+            else NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, rk}));
         } else {
-            NSB_CHECK(spmv_exchange_launch<0>(c, BT, s1.p, BpcgB1Op{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p}));
+            const BpcgB1Op b1{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p, push_u};
+            if (push_p.nruns > 0) NSB_CHECK(spmv_launch_halo_in<0>(c, BT, s1.p, b1, 0));      // s1 was pushed by b5 (or before the loop)
+            else NSB_CHECK(spmv_exchange_launch<0>(c, BT, s1.p, b1));
             // tmp1 and tmp4 travel in the velocity halo, in one exchange when A and B share the halo plan
             if (fused_AB) {
-                NSB_CHECK(p2p_halo_push(c, A->halo, tmp1.p, tmp4.p));
-                NSB_CHECK(spmv_launch_halo_in<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}, 0));
+                if (push_u.nruns == 0) NSB_CHECK(p2p_halo_push(c, A->halo, tmp1.p, tmp4.p));
+                NSB_CHECK(spmv_launch_halo_in<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, rk}, 0));
             } else {
                 if (A->halo == B->halo) NSB_CHECK(halo_exchange2(c, A->halo, tmp1.p, tmp4.p));
                 else NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));
-                NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, fused}));
+                NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, rk}));
                 if (A->halo != B->halo) NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
             }
         }
         if (K || general_pre) NSB_CHECK(halo_exchange(c, B->halo, tmp4.p));
-        if (fused_AB) NSB_CHECK(spmv_launch_halo_in<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, fused}, 1));
-        else NSB_CHECK(spmv_launch<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, fused}));
-        if (!fused && !p2p_allreduce_then(c, &S->red[0], 2, BpcgPost{S, 0, hist.p})) {
-            NSB_CHECK(allreduce_sum(c, &S->red[0], 2));
-            k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
-            c.launches++;
-        }
-        NSB_CUDA(launch_k(c, 2, k_bpcg_b4, vg, kBlock, 0, S, V, hist.p, c.partials, c.ticket, fused));
+        if (fused_AB) NSB_CHECK(spmv_launch_halo_in<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, red}, 1));
+        else NSB_CHECK(spmv_launch<1>(c, B, tmp4.p, BpcgB3Op{S, tmp3.p, s1.p, red}));
+        NSB_CHECK(reduce_unfused(&S->red[0], 2, 0));
+        NSB_CUDA(launch_k(c, 2, k_bpcg_b4, vg, kBlock, 0, S, V, hist.p, c.partials, c.ticket, red));
         c.launches++;
-        if (!fused && !p2p_allreduce_then(c, &S->red[2], 1, BpcgPost{S, 1, hist.p})) {
-            NSB_CHECK(allreduce_sum(c, &S->red[2], 1));
-            k_bpcg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
-            c.launches++;
-        }
-        NSB_CUDA(launch_k(c, 2, k_bpcg_b5, vec_grid(n_p > 0 ? n_p : 1, c.num_sms), kBlock, 0, S, V));
+        NSB_CHECK(reduce_unfused(&S->red[2], 1, 1));
+        NSB_CUDA(launch_k(c, 2, k_bpcg_b5, vec_grid(n_p > 0 ? n_p : 1, c.num_sms), kBlock, 0, S, V, push_p));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;
@@ -415,6 +449,7 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
             return NSB_OK;
         });
     NSB_CHECK(rc);
+    NSB_CHECK(check_fault(c, "nsb_bpcg"));
 
     NSB_CUDA(cudaEventRecord(ev.e1, c.stream));
     BpcgState hs;

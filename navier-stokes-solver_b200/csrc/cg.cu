@@ -57,7 +57,7 @@ struct CgC1Op {
     double* __restrict__ q;
     const double* __restrict__ s;
     double* alphas;
-    bool fused;
+    RedMode red;
     __device__ bool skip() const { return S->stop != 0; }
     struct Pre {
         double s;
@@ -68,17 +68,21 @@ struct CgC1Op {
         acc[0] = fma(p.s, ax, acc[0]);
     }
     __device__ void row(int64_t i, double ax, double (&acc)[1]) const { apply(i, ax, load(i), acc); }
-    __device__ void finish(const double (&tot)[1]) const {
-        if (fused) cg_after_as(S, tot[0], alphas);
-        else S->red[0] = tot[0];
+    using BlockFinish = void;   // last block, all threads: <s, A s> over the ranks, then alpha
+    __device__ void finish_block(const double (&tot)[1]) const {
+        if (threadIdx.x == 0) S->red[0] = tot[0];
+        CgState* St = S;
+        double* al = alphas;
+        reduce_finish(red, &S->red[0], 1, [St, al]() { cg_after_as(St, St->red[0], al); });
     }
+    __device__ void finish(const double (&tot)[1]) const { S->red[0] = tot[0]; }
 };
 
 __global__ void __launch_bounds__(kBlock) k_cg_c2(CgState* S, double* __restrict__ u, const double* __restrict__ s,
                                                   double* __restrict__ d, const double* __restrict__ q,
                                                   const double* __restrict__ dinv, double* __restrict__ w, int64_t n,
                                                   double* hist, double* betas, double* partials, unsigned int* ticket,
-                                                  bool fused) {
+                                                  RedMode red, bool defer_pre) {
     pdl_enter();
     if (S->stop) return;
     const double a = S->alpha;
@@ -86,26 +90,36 @@ __global__ void __launch_bounds__(kBlock) k_cg_c2(CgState* S, double* __restrict
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         if (u) u[i] += a * s[i];
         const double di = d[i] + (-a) * q[i];
-        const double wi = dinv ? dinv[i] * di : di;
         d[i] = di;
+        if (defer_pre) continue;   // a general preconditioner forms w = C d and <w,d> with its own kernels behind this one
+        const double wi = dinv ? dinv[i] * di : di;
         w[i] = wi;
         acc[0] = fma(wi, di, acc[0]);
     }
-    if (grid_sum<1>(acc, partials, ticket)) {
-        if (threadIdx.x == 0) {
-            if (fused) cg_after_wd(S, acc[0], hist, betas);
-            else S->red[1] = acc[0];
-        }
+    if (defer_pre) return;
+    if (grid_sum<1>(acc, partials, ticket)) {   // last block: <w,d> over the ranks, then beta, err and the stop test
+        if (threadIdx.x == 0) S->red[1] = acc[0];
+        reduce_finish(red, &S->red[1], 1, [S, hist, betas]() { cg_after_wd(S, S->red[1], hist, betas); });
     }
 }
 
+// Row-partitioned: the interface rows of the new s go straight into the neighbours' landing buffers (next pass's A s).
 __global__ void __launch_bounds__(kBlock) k_cg_c3(const CgState* S, double* __restrict__ s, const double* __restrict__ w,
-                                                  int64_t n) {
+                                                  int64_t n, PushOut P) {
     pdl_enter();
     if (S->stop) return;
     const double b = S->beta;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        s[i] = b * s[i] + w[i];
+    u64 e = 0;
+    if (P.nruns > 0) {
+        e = push_begin(P);
+        push_wait_consumed(P, e);
+    }
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double v = b * s[i] + w[i];
+        s[i] = v;
+        if (P.nruns > 0 && push_tile(P, i)) push_store<false>(P, i, v, 0.0);
+    }
+    if (P.nruns > 0) push_end(P, e);
 }
 
 __global__ void k_cg_init_scalar(CgState* S, int maxsteps, double tol, double* hist, int lanczos) {
@@ -145,7 +159,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
     // a block smoother as preconditioner is applied between the update kernel and the <w,d> reduction (unfused)
     const bool general_pre = pre != nullptr && pre->kind != 0;
     const double* dinv = (pre && !general_pre) ? pre->d.p : nullptr;
-    const bool fused = c.nranks == 1 && !general_pre;
+    const RedMode red = red_mode(c);
     CgState* S = b.st.p;
     const int vg = vec_grid(n, c.num_sms);
     double* u = want_u ? b.u.p : nullptr;
@@ -162,27 +176,35 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
     EventPair ev;
     NSB_CHECK(ev.create());
     NSB_CUDA(cudaEventRecord(ev.e0, c.stream));
+    // Row-partitioned over peer memory: both reductions end in the last block of the kernel that formed the partial sums and C3
+    // ships the interface rows of the s it writes -- three launches per iteration, as on one GPU.
+    PushOut push_s;
+    memset(&push_s, 0, sizeof(push_s));
+    if (!K && A->halo && push_fused_ok(c, A)) push_s = p2p_push_out(A->halo);
+    if (push_s.nruns > 0) NSB_CHECK(p2p_halo_push(c, A->halo, b.s.p));   // the first pass finds s's interface entries pushed
+    auto reduce_unfused = [&](double* vals, int which) -> int {   // NCCL fallback: all-reduce + scalar kernel
+        if (red.kind != kRedStore) return NSB_OK;
+        NSB_CHECK(allreduce_sum(c, vals, 1));
+        k_cg_scalar<<<1, 1, 0, c.stream>>>(S, which, hist, alphas, betas);
+        c.launches++;
+        return NSB_OK;
+    };
     auto launch_iteration = [&]() -> int {
-        if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused})));   // condensed: single-GPU
-        else NSB_CHECK(spmv_exchange_launch<1>(c, A, b.s.p, CgC1Op{S, b.q.p, b.s.p, alphas, fused}));
-        if (!fused && !p2p_allreduce_then(c, &S->red[0], 1, CgPost{S, 0, hist, alphas, betas})) {
-            NSB_CHECK(allreduce_sum(c, &S->red[0], 1));
-            k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist, alphas, betas);
-            c.launches++;
-        }
-        NSB_CUDA(launch_k(c, 2, k_cg_c2, vg, kBlock, 0, S, u, b.s.p, b.d.p, b.q.p, dinv, b.w.p, n, hist, betas, c.partials, c.ticket, fused));
+        const CgC1Op c1{S, b.q.p, b.s.p, alphas, red};
+        if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, c1)));   // condensed: single-GPU
+        else if (push_s.nruns > 0) NSB_CHECK(spmv_launch_halo_in<1>(c, A, b.s.p, c1, 0));
+        else NSB_CHECK(spmv_exchange_launch<1>(c, A, b.s.p, c1));
+        NSB_CHECK(reduce_unfused(&S->red[0], 0));
+        NSB_CUDA(launch_k(c, 2, k_cg_c2, vg, kBlock, 0, S, u, b.s.p, b.d.p, b.q.p, dinv, b.w.p, n, hist, betas, c.partials, c.ticket, red,
+                          general_pre));
         c.launches++;
         if (general_pre) {   // w = P d, then <w,d>
             NSB_CHECK(pre_apply_device(c, pre, b.d.p, b.w.p));
             NSB_CHECK(vec_dot(c, b.w.p, b.d.p, n, &S->red[1]));
             k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
             c.launches++;
-        } else if (!fused && !p2p_allreduce_then(c, &S->red[1], 1, CgPost{S, 1, hist, alphas, betas})) {
-            NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
-            k_cg_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist, alphas, betas);
-            c.launches++;
-        }
-        NSB_CUDA(launch_k(c, 2, k_cg_c3, vg, kBlock, 0, S, b.s.p, b.w.p, n));
+        } else NSB_CHECK(reduce_unfused(&S->red[1], 1));
+        NSB_CUDA(launch_k(c, 2, k_cg_c3, vg, kBlock, 0, S, b.s.p, b.w.p, n, push_s));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
         return NSB_OK;
@@ -245,6 +267,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
         if (host_check && host_check(check_arg, hs)) break;
     }
     NSB_CHECK(rc);
+    NSB_CHECK(check_fault(c, "cg"));
     NSB_CUDA(cudaEventRecord(ev.e1, c.stream));
     NSB_CUDA(cudaMemcpyAsync(&hs, S, sizeof(CgState), cudaMemcpyDeviceToHost, c.stream));
     NSB_CUDA(cudaStreamSynchronize(c.stream));
@@ -357,6 +380,104 @@ __global__ void __launch_bounds__(kBlock) k_gs_scale(double* __restrict__ bj, co
         bj[i] = sc * bj[i];
 }
 
+// ---- column-batched modified Gram-Schmidt --------------------------------------------------------
+// The reference orthogonalises column j against b_0 .. b_{j-1} one pair at a time (2 dots + 1 axpy per pair: 5 vector passes).
+// Here a column costs three passes whatever j is:
+//   dots    d_i = <b_i, b_j> for all i < j from ONE read of the j + 1 vectors; the MODIFIED Gram-Schmidt coefficients follow from
+//           them by the recurrence  c_i = d_i - sum_{k<i} c_k G_ki  (G_ki = <b_k, b_i> of the already normalised columns, kept from
+//           their own update pass) -- the same numbers the pairwise sweep produces, without re-reading b_j between pairs;
+//   update  b_j -= c_0 b_0, -= c_1 b_1, ... in the reference's order, with |b_j|^2 and the cross products <b_i, b_j> of the NEW
+//           column accumulated in the same pass;
+//   scale   b_j *= 1 / |b_j|.
+// Row-partitioned: each reduction is finished by the last block of its kernel (peer all-reduce, p2p.cuh), one per pass instead of
+// one per pair.
+constexpr int kGsMax = 8;
+struct GsPtrs {
+    const double* q[kGsMax];
+};
+struct GsState {
+    double G[kGsMax][kGsMax];   // G[k][i], k < i: <b_k, b_i> of this sweep's normalised columns
+    double coef[kGsMax];
+    double red[kGsMax];
+    double sigma;
+};
+
+template <int J>
+__global__ void __launch_bounds__(kBlock) k_gs_dots(GsPtrs B, const double* __restrict__ bj, int64_t n, GsState* S, double* partials,
+                                                    unsigned int* ticket, RedMode red) {
+    double acc[J];
+#pragma unroll
+    for (int k = 0; k < J; ++k) acc[k] = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double x = bj[i];
+#pragma unroll
+        for (int k = 0; k < J; ++k) acc[k] = fma(B.q[k][i], x, acc[k]);
+    }
+    if (grid_sum<J>(acc, partials, ticket)) {
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int k = 0; k < J; ++k) S->red[k] = acc[k];
+        }
+        reduce_finish(red, S->red, J, [S]() {
+            for (int i = 0; i < J; ++i) {                      // <b_i, b_j after the projections on b_0 .. b_{i-1}>  /  <b_i, b_i> (= 1)
+                double ci = S->red[i];
+                for (int k = 0; k < i; ++k) ci -= S->coef[k] * S->G[k][i];
+                S->coef[i] = ci;                               // orthonormalization.py:11
+            }
+        });
+    }
+}
+
+template <int J>
+__global__ void __launch_bounds__(kBlock) k_gs_update(GsPtrs B, double* __restrict__ bj, int64_t n, GsState* S, int j, double* partials,
+                                                      unsigned int* ticket, RedMode red) {
+    double cf[J > 0 ? J : 1], acc[J + 1];
+#pragma unroll
+    for (int k = 0; k < J; ++k) cf[k] = S->coef[k];
+#pragma unroll
+    for (int k = 0; k <= J; ++k) acc[k] = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        double x = bj[i];
+        double b[J > 0 ? J : 1];
+#pragma unroll
+        for (int k = 0; k < J; ++k) b[k] = B.q[k][i];
+#pragma unroll
+        for (int k = 0; k < J; ++k) x -= cf[k] * b[k];         // orthonormalization.py:12, pair after pair
+        if (J > 0) bj[i] = x;
+        acc[0] = fma(x, x, acc[0]);
+#pragma unroll
+        for (int k = 0; k < J; ++k) acc[1 + k] = fma(b[k], x, acc[1 + k]);
+    }
+    if (grid_sum<J + 1>(acc, partials, ticket)) {
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int k = 0; k <= J; ++k) S->red[k] = acc[k];
+        }
+        reduce_finish(red, S->red, J + 1, [S, j]() {
+            const double sigma = 1.0 / sqrt(S->red[0]);        // orthonormalization.py:13
+            S->sigma = sigma;
+            for (int k = 0; k < J; ++k) S->G[k][j] = S->red[1 + k] * sigma;
+        });
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_gs_scale_by(double* __restrict__ bj, const GsState* S, int64_t n) {
+    const double sc = S->sigma;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) bj[i] = sc * bj[i];
+}
+
+template <int J>
+static int gs_column(Context& c, const GsPtrs& B, double* bj, int64_t n, GsState* S, int j, int vg, const RedMode& red) {
+    if (J > 0) {
+        k_gs_dots<(J > 0 ? J : 1)><<<vg, kBlock, 0, c.stream>>>(B, bj, n, S, c.partials, c.ticket, red);
+        c.launches++;
+    }
+    k_gs_update<J><<<vg, kBlock, 0, c.stream>>>(B, bj, n, S, j, c.partials, c.ticket, red);
+    k_gs_scale_by<<<vg, kBlock, 0, c.stream>>>(bj, S, n);
+    c.launches += 2;
+    return NSB_OK;
+}
+
 }  // namespace nsb
 
 using namespace nsb;
@@ -448,8 +569,9 @@ static int lanczos_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_pre pre, cons
     return NSB_OK;
 }
 
-// modified Gram-Schmidt on m device-resident vectors of length n (stride n), orthonormalization.py:8-13
-static int gs_device(Context& c, double* Q, int64_t n, int m, int tries) {
+// modified Gram-Schmidt on m device-resident vectors of length n (stride n), orthonormalization.py:8-13, pair by pair: the
+// reference's pass structure (2 dots + 1 axpy per pair).  Kept for m > 8 and for the NCCL fallback.
+static int gs_pairwise(Context& c, double* Q, int64_t n, int m, int tries) {
     DevBuf<double> sc;
     NSB_CHECK(sc.allocs(c, 2));
     const int vg = vec_grid(n, c.num_sms);
@@ -470,6 +592,41 @@ static int gs_device(Context& c, double* Q, int64_t n, int m, int tries) {
         }
     }
     return NSB_OK;
+}
+
+// orthonormalize(basis, tries): column-batched (three passes per column, see k_gs_dots) for m <= 8
+static int gs_device(Context& c, double* Q, int64_t n, int m, int tries) {
+    static int batched = -1;
+    if (batched < 0) {
+        const char* e = getenv("NSB_GS_BATCHED");
+        batched = (e && atoi(e) == 0) ? 0 : 1;
+    }
+    const RedMode red = red_mode(c);
+    if (!batched || m > kGsMax || red.kind == kRedStore) return gs_pairwise(c, Q, n, m, tries);
+    DevBuf<GsState> st;
+    NSB_CHECK(st.allocs(c, 1));
+    const int vg = vec_grid(n, c.num_sms);
+    GsPtrs B;
+    for (int k = 0; k < kGsMax; ++k) B.q[k] = Q + (int64_t)(k < m ? k : 0) * n;
+    for (int t = 0; t < tries; ++t) {                                   // :8
+        for (int j = 0; j < m; ++j) {                                   // :9
+            double* bj = Q + (int64_t)j * n;
+            int rc = NSB_OK;
+            switch (j) {
+                case 0: rc = gs_column<0>(c, B, bj, n, st.p, j, vg, red); break;
+                case 1: rc = gs_column<1>(c, B, bj, n, st.p, j, vg, red); break;
+                case 2: rc = gs_column<2>(c, B, bj, n, st.p, j, vg, red); break;
+                case 3: rc = gs_column<3>(c, B, bj, n, st.p, j, vg, red); break;
+                case 4: rc = gs_column<4>(c, B, bj, n, st.p, j, vg, red); break;
+                case 5: rc = gs_column<5>(c, B, bj, n, st.p, j, vg, red); break;
+                case 6: rc = gs_column<6>(c, B, bj, n, st.p, j, vg, red); break;
+                default: rc = gs_column<7>(c, B, bj, n, st.p, j, vg, red); break;
+            }
+            NSB_CHECK(rc);
+        }
+    }
+    NSB_CUDA(cudaGetLastError());
+    return check_fault(c, "nsb_orthonormalize");
 }
 
 extern "C" int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* start, int maxsteps, double tol,

@@ -9,6 +9,7 @@
 
 #include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/nsb200.h"
@@ -102,6 +103,13 @@ struct Context {
     // -DNSB_SYNC_STATS builds only (tools/sync_stats.sh): nanoseconds spent polling peer flags and poll counts,
     // [0,1] all-reduce  [2,3] push waiting for "consumed"  [4,5] SpMV block 0 waiting for the halo  [6,7] wait/copy kernel
     unsigned long long* sync_stats = nullptr;
+    // failure detection of the peer-memory protocol: a wait on a peer flag that exceeds spin_timeout_ns raises *fault (device
+    // word) and is abandoned; the solver call then returns NSB_ERR_NCCL (check_fault).  NSB_SPIN_TIMEOUT_MS, default 30 s, 0 = never
+    int* fault = nullptr;
+    unsigned long long spin_timeout_ns = 30000000000ull;
+    int fault_skip_publish = 0;   // NSB_FAULT_SKIP_PUBLISH=<rank>: that rank never publishes "halo ready" (tests of the bound)
+    // launch geometry of the SELL kernels per (instantiation, shared-memory size): blocks per SM (spmv.cuh)
+    std::vector<std::pair<std::pair<const void*, size_t>, int>> sell_occupancy;
 };
 
 // device buffer with RAII (host-side owner).  alloc(): cudaMalloc, for long-lived storage (operators, IPC
@@ -387,11 +395,15 @@ int drive_batches(Context& c, const int* stop_dev, int maxsteps, int batch_iters
         if (rc != NSB_OK) break;
         launched += batch_iters;
         h_flags[slot] = 0;
+        h_flags[2 + slot] = 0;
         e = cudaMemcpyAsync((void*)&h_flags[slot], stop_dev, sizeof(int), cudaMemcpyDeviceToHost, c.stream);
+        // row-partitioned: a peer exchange that timed out (p2p.cuh: spin_until) ends the loop as well; the caller reports it
+        if (e == cudaSuccess && c.nranks > 1 && c.fault)
+            e = cudaMemcpyAsync((void*)&h_flags[2 + slot], c.fault, sizeof(int), cudaMemcpyDeviceToHost, c.stream);
         if (e == cudaSuccess) e = cudaEventRecord(ev[slot], c.stream);
         if (e == cudaSuccess && have_prev) {
             e = cudaEventSynchronize(ev[slot ^ 1]);
-            stop = h_flags[slot ^ 1] != 0;
+            stop = h_flags[slot ^ 1] != 0 || h_flags[2 + (slot ^ 1)] != 0;
         }
         have_prev = true;
         slot ^= 1;
@@ -461,6 +473,8 @@ struct GraphExecHolder {
 
 int build_sell(Context& c, nsb_mat_s* m);   // sell.cu
 int build_halo_order(Context& c, nsb_mat_s* m);   // sell.cu: (re)build the interior-first chunk order of every panel for m->halo
+// context.cu: NSB_OK, or NSB_ERR_NCCL (fault word cleared, error text set) when a peer exchange timed out since the last check
+int check_fault(Context& c, const char* who);
 // exchange steps of the fused path (p2p.cu): push only; the consuming SpMV waits inside the kernel
 int p2p_halo_push(Context& c, nsb_halo_s* h, double* x, double* x2 = nullptr);
 bool halo_fused_ok(const Context& c, const nsb_mat_s* m);   // p2p.cu: operator and exchange qualify for the in-kernel wait

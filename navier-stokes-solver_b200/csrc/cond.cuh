@@ -54,6 +54,13 @@ struct SubThenOp {   // hands (q - M q)_r to the inner row op
     __device__ bool skip() const { return in.skip(); }
     __device__ void row(int64_t r, double ax, double (&acc)[NSA]) const { in.row(r, q[r] - ax, acc); }
     __device__ void finish(const double (&tot)[NSA]) const { in.finish(tot); }
+    using BlockFinish = void;   // all threads of the last block: the inner op may end its reduction in a peer all-reduce
+    __device__ void finish_block(const double (&tot)[NSA]) const {
+        double t[NSA];
+#pragma unroll
+        for (int k = 0; k < NSA; ++k) t[k] = tot[k];
+        finish_last_block(in, t);
+    }
 };
 
 // fin.row(r, (matA x)_r, acc) for every row.  x is a length-n device vector (not K->t / K->q).

@@ -51,6 +51,8 @@ int ctx_init(Context& c, int device) {
         if (f) c.sell_flags = atoi(f);
         const char* g = getenv("NSB_GRAPHS");
         if (g) c.use_graphs = atoi(g) != 0;
+        const char* t = getenv("NSB_SPIN_TIMEOUT_MS");
+        if (t) c.spin_timeout_ns = (unsigned long long)(atof(t) * 1e6);
     }
     NSB_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
     {   // keep freed work vectors in the device's default pool between solves
@@ -68,11 +70,27 @@ int ctx_init(Context& c, int device) {
     NSB_CUDA(cudaMallocHost((void**)&c.h_mail, sizeof(double) * 64));
     NSB_CUDA(cudaMalloc((void**)&c.d_mail, sizeof(double) * 64));
     NSB_CUDA(cudaMemset(c.d_mail, 0, sizeof(double) * 64));
+    NSB_CUDA(cudaMalloc((void**)&c.fault, sizeof(int)));
+    NSB_CUDA(cudaMemset(c.fault, 0, sizeof(int)));
 #ifdef NSB_SYNC_STATS
     NSB_CUDA(cudaMalloc((void**)&c.sync_stats, sizeof(unsigned long long) * 16));
     NSB_CUDA(cudaMemset(c.sync_stats, 0, sizeof(unsigned long long) * 16));
 #endif
     return NSB_OK;
+}
+
+int check_fault(Context& c, const char* who) {
+    if (!c.fault || c.nranks <= 1) return NSB_OK;
+    int f = 0;
+    NSB_CUDA(cudaMemcpyAsync(&f, c.fault, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    if (!f) return NSB_OK;
+    NSB_CUDA(cudaMemsetAsync(c.fault, 0, sizeof(int), c.stream));
+    static const char* what[] = {"", "scalar all-reduce: a peer's partial sums", "halo push: a neighbour's \"consumed\" word",
+                                 "SpMV: a neighbour's interface entries"};
+    set_error("%s: rank %d waited more than %.1f s for %s (peer exchange timed out; a rank died or left the solve)", who, c.rank,
+              1e-9 * (double)c.spin_timeout_ns, what[f >= 1 && f <= 3 ? f : 0]);
+    return NSB_ERR_NCCL;
 }
 
 int dist_init(Context& c, int rank, int nranks, const char* uid);  // dist.cu
@@ -120,7 +138,11 @@ int nsb_ctx_create_dist(int device, int rank, int nranks, const char unique_id[1
         }
         // CUDA graphs stay on when both exchange steps run over peer memory (no host-side communication call
         // inside the iteration); with the NCCL fallback the iteration is launched kernel by kernel
-        (*out)->c.use_graphs = (*out)->c.p2p != nullptr;
+        Context& cc = (*out)->c;
+        const char* g = getenv("NSB_GRAPHS");
+        cc.use_graphs = (g ? atoi(g) != 0 : true) && cc.p2p != nullptr;
+        const char* sk = getenv("NSB_FAULT_SKIP_PUBLISH");
+        cc.fault_skip_publish = (sk && atoi(sk) == rank) ? 1 : 0;
     }
     return NSB_OK;
 }
@@ -136,6 +158,7 @@ int nsb_ctx_destroy(nsb_ctx ctx) {
     if (c.chain) cudaFree(c.chain);
     if (c.d_mail) cudaFree(c.d_mail);
     if (c.sync_stats) cudaFree(c.sync_stats);
+    if (c.fault) cudaFree(c.fault);
     if (c.h_mail) cudaFreeHost(c.h_mail);
     if (c.stream) cudaStreamDestroy(c.stream);
     delete ctx;

@@ -104,7 +104,7 @@ struct MinresK1Op {
     MinresState* S;
     double* __restrict__ t;
     const double* __restrict__ zh;
-    bool fused_scalar;
+    RedMode red;
     __device__ bool skip() const {
         const bool st = S->stop != 0;
         if (st && blockIdx.x == 0 && threadIdx.x == 0) S->done = 1;
@@ -119,10 +119,13 @@ struct MinresK1Op {
         acc[0] = fma(ax, p.z, acc[0]);
     }
     __device__ void row(int64_t r, double ax, double (&acc)[1]) const { apply(r, ax, load(r), acc); }
-    __device__ void finish(const double (&tot)[1]) const {
-        if (fused_scalar) minres_after_delta(S, tot[0]);
-        else S->red[0] = tot[0];
+    using BlockFinish = void;   // last block, all threads: delta summed over the ranks (:98)
+    __device__ void finish_block(const double (&tot)[1]) const {
+        if (threadIdx.x == 0) S->red[0] = tot[0];
+        MinresState* St = S;
+        reduce_finish(red, &S->red[0], 1, [St]() { minres_after_delta(St, St->red[0]); });
     }
+    __device__ void finish(const double (&tot)[1]) const { S->red[0] = tot[0]; }
 };
 
 // ---- K2 ---------------------------------------------------------------------------------------
@@ -130,9 +133,14 @@ __global__ void __launch_bounds__(kBlock) k_minres_k2(MinresState* S, const doub
                                                       const double* __restrict__ vh, const double* __restrict__ vh_old,
                                                       const double* __restrict__ dinv, double* __restrict__ vh_new,
                                                       double* __restrict__ zh_new, int64_t n, double* hist,
-                                                      double* partials, unsigned int* ticket, bool fused_scalar, bool defer_pre) {
+                                                      double* partials, unsigned int* ticket, RedMode red, bool defer_pre, PushOut P) {
     pdl_enter();
     if (S->stop) return;
+    u64 push_e = 0;
+    if (P.nruns > 0) {   // row-partitioned: the interface rows of the new zh go straight to the neighbours (next pass's K zh)
+        push_e = push_begin(P);
+        push_wait_consumed(P, push_e);
+    }
     const double ig = S->ig;
     const double c1 = S->delta * ig;            // delta * v      = delta * ig * vh
     const double c2 = S->gamma * S->ig_old;     // gamma * v_old  = gamma * ig_old * vh_old
@@ -143,15 +151,15 @@ __global__ void __launch_bounds__(kBlock) k_minres_k2(MinresState* S, const doub
         if (defer_pre) continue;                // a general preconditioner is applied by its own kernels behind this one
         const double zn = dinv ? dinv[i] * vn : vn;
         zh_new[i] = zn;
+        if (P.nruns > 0 && push_tile(P, i)) push_store<false>(P, i, zn, 0.0);
         acc[0] = fma(zn, vn, acc[0]);
     }
     if (defer_pre) return;
-    if (grid_sum<1>(acc, partials, ticket)) {
-        if (threadIdx.x == 0) {
-            if (fused_scalar) minres_after_gamma(S, acc[0], hist);
-            else S->red[1] = acc[0];
-        }
+    if (grid_sum<1>(acc, partials, ticket)) {   // last block: gamma_new^2 over the ranks, then the Givens step and the stop test
+        if (threadIdx.x == 0) S->red[1] = acc[0];
+        reduce_finish(red, &S->red[1], 1, [S, hist]() { minres_after_gamma(S, S->red[1], hist); });
     }
+    if (P.nruns > 0) push_end(P, push_e);
 }
 
 // ---- K3 ---------------------------------------------------------------------------------------
@@ -243,7 +251,6 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
     NSB_REQUIRE(K->halo ? K->halo->n_owned == n : K->cols == K->rows, "nsb_minres: operator must be square");
     if (pre) NSB_REQUIRE(pre->n == n, "nsb_minres: preconditioner size %lld != %lld", (long long)pre->n, (long long)n);
     const bool dist = c.nranks > 1;
-    const bool fused = !dist;
     // pre: diagonal (fused into K2) or any other device preconditioner -- block smoother, auxiliary-space composite (run.py:61-62
     // and stokes_hcurldiv.py:48 configure non-Jacobi ones) -- applied by its own kernels between K2 and the gamma reduction
     const bool general_pre = pre != nullptr && pre->kind != 0;
@@ -292,6 +299,20 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
     NSB_CHECK(ev.create());
     NSB_CUDA(cudaEventRecord(ev.e0, c.stream));
 
+    // Row-partitioned over peer memory: both reductions end in the last block of the kernel that formed the partial sums, and K2
+    // ships the interface rows of the zh it writes -- three launches per iteration, as on one GPU.
+    const RedMode red = red_mode(c);
+    PushOut push_z;
+    memset(&push_z, 0, sizeof(push_z));
+    if (K->halo && push_fused_ok(c, K) && !general_pre) push_z = p2p_push_out(K->halo);
+    if (push_z.nruns > 0) NSB_CHECK(p2p_halo_push(c, K->halo, z[0].p));   // the first pass finds zh's interface entries pushed
+    auto reduce_unfused = [&](double* vals, int which) -> int {   // NCCL fallback: all-reduce + scalar kernel
+        if (red.kind != kRedStore) return NSB_OK;
+        NSB_CHECK(allreduce_sum(c, vals, 1));
+        k_minres_scalar<<<1, 1, 0, c.stream>>>(S, which, hist.p);
+        c.launches++;
+        return NSB_OK;
+    };
     // ---- iteration; pointer rotation has period 6 (v,w: 3-cycles, z: 2-cycle)  (:131-133)
     auto launch_iteration = [&](int j) -> int {
         double* v_old = v[j % 3].p;
@@ -302,25 +323,18 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
         double* w_new = w[(j + 2) % 3].p;
         double* zc = z[j % 2].p;
         double* z_new = z[(j + 1) % 2].p;
-        NSB_CHECK(spmv_exchange_launch<1>(c, K, zc, MinresK1Op{S, t.p, zc, fused}));
-        if (!fused && !p2p_allreduce_then(c, &S->red[0], 1, MinresPost{S, 0, hist.p})) {
-            NSB_CHECK(allreduce_sum(c, &S->red[0], 1));
-            k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 0, hist.p);
-            c.launches++;
-        }
-        NSB_CUDA(launch_k(c, 2, k_minres_k2, vg, kBlock, 0, S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, fused,
-                          general_pre));
+        if (push_z.nruns > 0) NSB_CHECK(spmv_launch_halo_in<1>(c, K, zc, MinresK1Op{S, t.p, zc, red}, 0));   // zh was pushed by K2
+        else NSB_CHECK(spmv_exchange_launch<1>(c, K, zc, MinresK1Op{S, t.p, zc, red}));
+        NSB_CHECK(reduce_unfused(&S->red[0], 0));
+        NSB_CUDA(launch_k(c, 2, k_minres_k2, vg, kBlock, 0, S, t.p, vc, v_old, dinv, v_new, z_new, n, hist.p, c.partials, c.ticket, red,
+                          general_pre, push_z));
         c.launches++;
         if (general_pre) {   // z_new = C v_new (:101), gamma_new^2 = <z_new, v_new> (:103); ignored once the stop flag is up
             NSB_CHECK(pre_apply_device(c, pre, v_new, z_new));
             NSB_CHECK(vec_dot(c, z_new, v_new, n, &S->red[1]));
             k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
             c.launches++;
-        } else if (!fused && !p2p_allreduce_then(c, &S->red[1], 1, MinresPost{S, 1, hist.p})) {
-            NSB_CHECK(allreduce_sum(c, &S->red[1], 1));
-            k_minres_scalar<<<1, 1, 0, c.stream>>>(S, 1, hist.p);
-            c.launches++;
-        }
+        } else NSB_CHECK(reduce_unfused(&S->red[1], 1));
         NSB_CUDA(launch_k(c, 2, k_minres_k3, vg, kBlock, 0, S, zc, w_old, wc, w_new, u.p, n));
         c.launches++;
         NSB_CUDA(cudaGetLastError());
@@ -352,6 +366,7 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
             return NSB_OK;
         });
     NSB_CHECK(rc);
+    NSB_CHECK(check_fault(c, "nsb_minres"));
 
     NSB_CUDA(cudaEventRecord(ev.e1, c.stream));
     MinresState hs;

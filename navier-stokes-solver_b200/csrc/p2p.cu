@@ -113,7 +113,21 @@ struct P2PReduce {
 
 P2PReduceView p2p_reduce_view(Context& c) {
     P2PReduce* P = c.p2p;
-    return P2PReduceView{P->peer_box.p, P->peer_flag.p, P->my_box, P->my_flag, P->seq, c.rank, c.nranks, c.sync_stats};
+    return P2PReduceView{P->peer_box.p, P->peer_flag.p, P->my_box, P->my_flag, P->seq, c.rank, c.nranks, c.sync_stats,
+                         SpinGuard{c.fault, c.spin_timeout_ns}};
+}
+
+RedMode red_mode(Context& c) {
+    RedMode M;
+    memset(&M, 0, sizeof(M));
+    static int inblock = -1;
+    if (inblock < 0) {
+        const char* e = getenv("NSB_REDUCE_INBLOCK");   // 0: the all-reduce runs as a kernel of its own (A/B measurements)
+        inblock = (e && atoi(e) == 0) ? 0 : 1;
+    }
+    M.kind = c.nranks <= 1 ? kRedLocal : ((c.p2p && inblock) ? kRedPeer : kRedStore);
+    if (M.kind == kRedPeer) M.R = p2p_reduce_view(c);
+    return M;
 }
 
 int p2p_reduce_init(Context& c) {
@@ -149,8 +163,7 @@ int p2p_reduce_init(Context& c) {
         delete P;
         return rc;
     }
-    c.p2p = P;
-    c.use_graphs = true;   // no host-side communication call is left inside the iteration
+    c.p2p = P;   // (whether the iteration loops are captured in graphs is decided in nsb_ctx_create_dist: NSB_GRAPHS is honoured)
     return NSB_OK;
 }
 
@@ -168,24 +181,6 @@ int p2p_allreduce(Context& c, double* dev, int count) {
 }
 
 // ---- halo exchange -----------------------------------------------------------------------------------
-struct HaloDev {
-    int nnb;
-    int64_t n_send, n_halo;
-    const int* send_idx;     // owned entries to ship, neighbour by neighbour
-    const int64_t* send_off; // nnb + 1 offsets into send_idx
-    double* const* peer_land;   // per neighbour: where my entries land in its landing buffer
-    u64* const* peer_ready;     // per neighbour: its ready flag for me
-    u64* const* peer_consumed;  // per neighbour: its "neighbour consumed" word for me
-    const double* my_land;
-    int64_t land2;              // offset (doubles) of the second vector's area in every landing buffer
-    const int64_t* peer_land2;  // per neighbour: the same offset in ITS landing buffer
-    const u64* my_ready;        // written by the neighbours
-    const u64* my_consumed;     // written by the neighbours
-    u64* seq;
-    unsigned int* ticket;
-    u64* stats;   // NSB_SYNC_STATS builds; else null
-};
-
 struct P2PHalo {
     IpcBlock blk;   // [ landing: 2 x n_halo doubles (padded; one area per vector of a dual exchange) | ready: nnb u64 | consumed: nnb u64 | seq u64 | ticket u32 ]
     DevBuf<int64_t> send_off;
@@ -194,6 +189,10 @@ struct P2PHalo {
     DevBuf<int64_t> peer_land2;
     HaloDev dev;
     int push_grid = 1, copy_grid = 1;
+    // the send lists as runs of consecutive owned rows (fused push from the producing kernel); nruns == 0: not run-shaped
+    int nruns = 0;
+    int run_start[kPushRuns], run_len[kPushRuns], run_nb[kPushRuns], run_slot0[kPushRuns];
+    DevBuf<unsigned char> tiles;   // one byte per 256 owned rows: the tile holds a row that is sent
 };
 
 __global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* __restrict__ x, const double* __restrict__ x2) {
@@ -203,8 +202,7 @@ __global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* _
     if (blockIdx.x == 0 && threadIdx.x < H.nnb) st_release_sys(H.peer_consumed[threadIdx.x], e - 1);
     if (threadIdx.x < H.nnb) {
         NSB_STATS_T0();
-        while (ld_acquire_sys(H.my_consumed + threadIdx.x) < e - 1) {
-        }
+        spin_until(H.my_consumed + threadIdx.x, e - 1, H.guard, kFaultHaloConsumed);
         if (blockIdx.x == 0 && threadIdx.x == 0) NSB_STATS_ADD(H.stats, 2);
     }
     __syncthreads();
@@ -222,7 +220,7 @@ __global__ void __launch_bounds__(kBlock) k_halo_push(HaloDev H, const double* _
     __syncthreads();
     if (last) {
         __threadfence_system();
-        if (threadIdx.x < H.nnb) st_release_sys(H.peer_ready[threadIdx.x], e);
+        if (threadIdx.x < H.nnb && !H.skip_publish) st_release_sys(H.peer_ready[threadIdx.x], e);
         if (threadIdx.x == 0) {
             *H.ticket = 0u;
             *H.seq = e;
@@ -234,8 +232,7 @@ __global__ void __launch_bounds__(kBlock) k_halo_wait_copy(HaloDev H, double* __
     const u64 e = *H.seq;   // the push of this exchange is earlier in the stream
     if (threadIdx.x < H.nnb) {
         NSB_STATS_T0();
-        while (ld_acquire_sys(H.my_ready + threadIdx.x) < e) {
-        }
+        spin_until(H.my_ready + threadIdx.x, e, H.guard, kFaultHaloReady);
         if (blockIdx.x == 0 && threadIdx.x == 0) NSB_STATS_ADD(H.stats, 6);
     }
     __syncthreads();
@@ -345,6 +342,41 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     D.seq = flags + 2 * nnb;
     D.ticket = (unsigned int*)(flags + 2 * nnb + 1);
     D.stats = c.sync_stats;
+    D.guard = SpinGuard{c.fault, c.spin_timeout_ns};
+    D.skip_publish = c.fault_skip_publish;
+    // the send lists as runs of consecutive owned rows
+    {
+        std::vector<int32_t> sidx((size_t)(h->n_send > 0 ? h->n_send : 0));
+        if (h->n_send > 0) cudaMemcpy(sidx.data(), h->send_idx.p, sizeof(int32_t) * (size_t)h->n_send, cudaMemcpyDeviceToHost);
+        int nr = 0;
+        bool ok = true;
+        for (int k = 0; k < nnb && ok; ++k) {
+            const int64_t a = so[k], b = so[k + 1];
+            for (int64_t i = a; i < b && ok;) {
+                int64_t j = i + 1;
+                while (j < b && sidx[(size_t)j] == sidx[(size_t)j - 1] + 1) ++j;
+                if (nr == kPushRuns) {
+                    ok = false;
+                    break;
+                }
+                P->run_start[nr] = sidx[(size_t)i];
+                P->run_len[nr] = (int)(j - i);
+                P->run_nb[nr] = k;
+                P->run_slot0[nr] = (int)(i - a);
+                ++nr;
+                i = j;
+            }
+        }
+        P->nruns = ok ? nr : 0;
+        if (P->nruns > 0) {
+            const int64_t nt = (h->n_owned >> kPushTileLog2) + 2;
+            std::vector<unsigned char> tf((size_t)nt, 0);
+            for (int r = 0; r < nr; ++r)
+                for (int64_t t = (int64_t)P->run_start[r] >> kPushTileLog2; t <= ((int64_t)P->run_start[r] + P->run_len[r] - 1) >> kPushTileLog2; ++t)
+                    tf[(size_t)t] = 1;
+            if (P->tiles.alloc(nt) != NSB_OK || cudaMemcpy(P->tiles.p, tf.data(), (size_t)nt, cudaMemcpyHostToDevice) != cudaSuccess) P->nruns = 0;
+        }
+    }
     auto grid_for = [&](int64_t n) {
         int64_t g = (n + (int64_t)kBlock * 4 - 1) / ((int64_t)kBlock * 4);
         if (g < 1) g = 1;
@@ -382,7 +414,35 @@ int p2p_halo_push(Context& c, nsb_halo_s* h, double* x, double* x2) {
 // View for a SpMV that reads the halo entries of vector `area` (0: x, 1: x2 of the last push) from the landing buffer.
 HaloIn p2p_halo_in(const nsb_halo_s* h, int area, const int* order, int n_interior) {
     const HaloDev& D = h->p2p->dev;
-    return HaloIn{D.my_ready, D.seq, D.my_land + (area ? D.land2 : 0), h->n_owned, D.nnb, order, n_interior, D.stats};
+    return HaloIn{D.my_ready, D.seq, D.my_land + (area ? D.land2 : 0), h->n_owned, D.nnb, order, n_interior, D.stats, D.guard};
+}
+
+PushOut p2p_push_out(const nsb_halo_s* h) {
+    PushOut P;
+    memset(&P, 0, sizeof(P));
+    if (!h || !h->p2p || h->p2p->dev.nnb == 0) return P;
+    const P2PHalo* Q = h->p2p;
+    P.H = Q->dev;
+    P.nruns = Q->nruns;
+    P.tiles = Q->tiles.p;
+    for (int k = 0; k < Q->nruns; ++k) {
+        P.start[k] = Q->run_start[k];
+        P.len[k] = Q->run_len[k];
+        P.nb[k] = Q->run_nb[k];
+        P.slot0[k] = Q->run_slot0[k];
+    }
+    return P;
+}
+
+// The vector this operator multiplies can be pushed from the epilogue of the kernel that produces it: the operator takes its halo
+// inside the SpMV kernel (so nothing else needs the exchange) and the send lists are a few runs of consecutive rows.
+bool push_fused_ok(const Context& c, const nsb_mat_s* m) {
+    static int enabled = -1;
+    if (enabled < 0) {
+        const char* e = getenv("NSB_PUSH_FUSED");
+        enabled = (e && atoi(e) == 0) ? 0 : 1;
+    }
+    return enabled && halo_fused_ok(c, m) && m->halo->p2p->nruns > 0;
 }
 
 bool halo_fused_ok(const Context& c, const nsb_mat_s* m) {

@@ -103,9 +103,7 @@ __global__ void __launch_bounds__(kBlock) spmv_csrvec_kernel(CsrView A, const do
         if (lane == 0 && valid) op.row(r, s, acc);
     }
     if constexpr (NS > 0) {
-        if (grid_sum<NSA>(acc, partials, ticket)) {
-            if (threadIdx.x == 0) op.finish(acc);
-        }
+        if (grid_sum<NSA>(acc, partials, ticket)) finish_last_block(op, acc);
     }
 }
 
@@ -222,6 +220,27 @@ struct pre_of<Op, std::void_t<typename Op::Pre>> {
     using type = typename Op::Pre;
 };
 
+// finish_block(tot): like finish(tot) (totals valid in thread 0) but called by ALL threads of the last block, for row ops whose
+// reduction ends in a peer all-reduce run by that block (p2p.cuh: reduce_finish)
+template <class Op, class = void>
+struct has_finish_block : std::false_type {};
+template <class Op>
+struct has_finish_block<Op, std::void_t<typename Op::BlockFinish>> : std::true_type {};   // marker: `using BlockFinish = void;`
+// push_out(): the row op ships interface rows of a vector it writes to the neighbours (p2p.cuh: PushOut); the kernel runs the
+// protocol around the row epilogues (push_begin / push_wait_consumed / push_end), the op calls push_store for its rows
+template <class Op, class = void>
+struct has_push : std::false_type {};
+template <class Op>
+struct has_push<Op, std::void_t<decltype(std::declval<const Op&>().push_out())>> : std::true_type {};
+
+template <class Op, int NSA>
+__device__ __forceinline__ void finish_last_block(const Op& op, double (&acc)[NSA]) {
+    if constexpr (has_finish_block<Op>::value) op.finish_block(acc);
+    else {
+        if (threadIdx.x == 0) op.finish(acc);
+    }
+}
+
 template <int T, int NS, class RowOp, class HI>
 __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kernel(SellView S, const double* __restrict__ x, RowOp op,
                                                                double* partials, unsigned int* ticket, HI H) {
@@ -257,7 +276,12 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
     if (op.skip()) return;
     u64 exch = 0;
     bool landed = false;
-    if constexpr (HALO) exch = *H.seq;   // written by k_halo_push, earlier in the stream
+    if constexpr (HALO) exch = *H.seq;   // written by the push of this exchange, earlier in the stream
+    u64 push_e = 0;
+    bool push_open = false;   // the neighbours have consumed the previous exchange: this block may store into their landing buffers
+    if constexpr (has_push<RowOp>::value) {
+        if (op.push_out().nruns > 0) push_e = push_begin(op.push_out());
+    }
     double* sx = smem;
     double* sy = smem + S.cap;
     unsigned int* soff = reinterpret_cast<unsigned int*>(sy + S.R);
@@ -322,7 +346,9 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
     const bool async_stage = (S.sell_flags & 8) != 0;
     // with bit 4 the next chunk of the block is staged right behind the compute phase, so its latency runs under the
     // (latency-bound) row epilogue of the current chunk; one buffer is enough: the compute phase is done with sx
-    const bool pipelined = !HALO && async_stage && (S.sell_flags & 16);   // row-partitioned: the wait for the halo sits at the loop top
+    // row-partitioned: the wait for the halo sits at the loop top, so a chunk with halo columns is staged ahead only once the
+    // neighbours' entries have landed; interior chunks (the bulk) are always staged ahead
+    const bool pipelined = async_stage && (S.sell_flags & 16);
     bool staged = false;   // this chunk's copies were issued during the previous chunk's epilogue
 
     for (int ci = blockIdx.x; ci < S.nchunks; ci += gridDim.x) {
@@ -334,8 +360,7 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
                 // barrier below orders the other threads of the block behind these acquires.
                 if (threadIdx.x < H.nnb) {
                     NSB_STATS_T0();
-                    while (ld_acquire_sys(H.my_ready + threadIdx.x) < exch) {
-                    }
+                    spin_until(H.my_ready + threadIdx.x, exch, H.guard, kFaultHaloReady);
                     if (blockIdx.x == 0 && threadIdx.x == 0) NSB_STATS_ADD(H.stats, 4);
                 }
                 landed = true;
@@ -435,13 +460,34 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
         }
         __syncthreads();
         staged = false;
-        if constexpr (!HALO) {
-            if (pipelined && ci + (int)gridDim.x < S.nchunks) {
-                stage_async(ci + (int)gridDim.x);
+        if (pipelined && ci + (int)gridDim.x < S.nchunks) {
+            const int cn = ci + (int)gridDim.x;
+            if constexpr (HALO) {
+                if (cn < H.n_interior || landed) {
+                    stage_async(__ldg(H.order + cn));
+                    staged = true;
+                }
+            } else {
+                stage_async(cn);
                 staged = true;
             }
         }
         const int64_t r0 = (int64_t)chunk << S.log2R;
+        if constexpr (has_push<RowOp>::value) {
+            // a chunk with rows the op ships to a neighbour (one flag byte per 256 rows): its epilogue also stores those rows into the
+            // neighbours' landing buffers; before the first such chunk of this block, wait (bounded) until they consumed the previous exchange
+            if (op.push_out().nruns > 0 && push_touches(op.push_out(), S.row0 + r0, S.row0 + r0 + S.R)) {
+                if (!push_open) {
+                    push_wait_consumed(op.push_out(), push_e);
+                    push_open = true;
+                }
+                for (int t = threadIdx.x; t < S.R; t += kSellBlock) {
+                    const int64_t r = r0 + t;
+                    if (r < S.rows) op.row_pushing(S.row0 + r, sy[t], acc);
+                }
+                continue;
+            }
+        }
         if constexpr (has_load<RowOp>::value) {
             if (S.sell_flags & 4) {
                 using Pre = typename pre_of<RowOp>::type;
@@ -463,9 +509,10 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
         }
     }
     if constexpr (NS > 0) {
-        if (grid_sum<NSA>(acc, partials, ticket)) {
-            if (threadIdx.x == 0) op.finish(acc);
-        }
+        if (grid_sum<NSA>(acc, partials, ticket)) finish_last_block(op, acc);
+    }
+    if constexpr (has_push<RowOp>::value) {
+        if (op.push_out().nruns > 0) push_end(op.push_out(), push_e);
     }
 }
 
@@ -482,22 +529,29 @@ inline size_t sell_smem_bytes(const SellData* m) {
 
 template <int T, int NS, class RowOp, class HI>
 int spmv_sell_launch_t(Context& c, const SellData* m, const double* x, RowOp op, HI H) {
-    static unsigned long long attr_devices = 0;   // per instantiation: devices (bit = ordinal) the attribute was set on
-    static size_t cached_smem = ~(size_t)0;
-    static int cached_bps = 0;
+    // blocks per SM of this instantiation at this shared-memory size, remembered PER CONTEXT (a context belongs to one device and
+    // is driven by one host thread at a time); the first use on a context also raises the kernel's shared-memory limit there
     const size_t smem = sell_smem_bytes(m);
-    const unsigned long long dev_bit = 1ull << (c.device & 63);
-    if (!(attr_devices & dev_bit)) {   // function attributes are per device: a second context on another GPU sets its own
-        NSB_CUDA(cudaFuncSetAttribute(spmv_sell_kernel<T, NS, RowOp, HI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSellMaxSmem));
-        attr_devices |= dev_bit;
+    const void* kern = (const void*)spmv_sell_kernel<T, NS, RowOp, HI>;
+    int bps = 0;
+    bool seen_kernel = false;
+    for (const auto& e : c.sell_occupancy) {
+        if (e.first.first != kern) continue;
+        seen_kernel = true;
+        if (e.first.second == smem) {
+            bps = e.second;
+            break;
+        }
     }
-    if (smem != cached_smem) {
+    if (bps == 0) {
+        if (!seen_kernel)
+            NSB_CUDA(cudaFuncSetAttribute(spmv_sell_kernel<T, NS, RowOp, HI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSellMaxSmem));
         int b = 0;
         NSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, spmv_sell_kernel<T, NS, RowOp, HI>, kSellBlock, smem));
-        cached_bps = b > 0 ? b : 1;
-        cached_smem = smem;
+        bps = b > 0 ? b : 1;
+        c.sell_occupancy.push_back({{kern, smem}, bps});
     }
-    int grid = c.num_sms * cached_bps;
+    int grid = c.num_sms * bps;
     if (grid > m->sell_nchunks) grid = m->sell_nchunks;
     if (grid > c.max_grid) grid = c.max_grid;
     SellView V = sell_view_of(m);
@@ -542,8 +596,22 @@ struct ChainOp {
             for (int k = 0; k < NSA; ++k) chain[k] = t[k];
         }
     }
+    // all threads of the last block of this panel's launch; the totals are valid in thread 0 only
+    using BlockFinish = void;
+    __device__ void finish_block(const double (&tot)[NSA]) const {
+        double t[NSA];
+#pragma unroll
+        for (int k = 0; k < NSA; ++k) t[k] = first ? tot[k] : chain[k] + tot[k];
+        if (last) finish_last_block(in, t);
+        else if (threadIdx.x == 0) {
+#pragma unroll
+            for (int k = 0; k < NSA; ++k) chain[k] = t[k];
+        }
+    }
 };
 
+template <class Inner, int NSA>
+struct has_push<ChainOp<Inner, NSA>, void> : std::false_type {};   // a multi-panel SpMV never pushes (one push per exchange)
 template <class Inner, int NSA>
 struct has_load<ChainOp<Inner, NSA>, void> : has_load<Inner> {};
 template <class Inner, int NSA>

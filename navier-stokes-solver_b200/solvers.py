@@ -332,27 +332,30 @@ def heat_large_step(diffusion, mass, heat, pre_heat, temperature, time_step, wei
 
 
 # ------------------------------------------------------------------------------------------------
-# Gauss collocation on the projected (m x m, m = 5) system: host-side dense algebra, as in the
-# reference (runge_kutta_method.py; SURVEY.md a12: "negligible; stays on host").
-def _lagrange(c, n, x):
-    return np.prod(c[:n] - x, axis=0) * np.prod(c[n + 1:] - x, axis=0) / np.prod(c[:n] - c[n]) / np.prod(c[n + 1:] - c[n])
-
-
+# Gauss collocation on the projected (m x m, m = 5) system: host-side dense algebra ("negligible; stays on host").
 class ImplicitRungeKuttaMethodWeights:
-    """runge_kutta_method.py:10-23."""
+    """Butcher tableau of the ``deg``-stage Gauss collocation method on [0, 1] (the object runge_kutta_method.py:10-23 builds):
+    nodes ``c`` = Gauss-Legendre points, ``a[i, j]`` = integral of the j-th Lagrange basis polynomial over [0, c_i], ``b[j]`` the
+    same over [0, 1].  The integrals are exact: a ``deg``-point Gauss rule mapped onto [0, c_i] integrates the degree ``deg - 1``
+    basis polynomials exactly (no adaptive quadrature)."""
 
     def __init__(self, deg=3):
-        import scipy.integrate as integrate
-        c_big, self.b_numpy = np.polynomial.legendre.leggauss(deg)
-        self.c = (c_big + 1) / 2
-        self.b_numpy = self.b_numpy / deg
-        ca = np.array([self.c]).T
-        self.a = np.zeros((deg, deg))
-        self.b = np.zeros(deg)
-        for i in range(deg):
-            self.b[i] = integrate.quad(lambda xx: _lagrange(ca, i, xx).item(), 0, 1)[0]
-            for j in range(deg):
-                self.a[i, j] = integrate.quad(lambda xx: _lagrange(ca, j, xx).item(), 0, self.c[i])[0]
+        from numpy.polynomial.legendre import leggauss
+        nodes, gauss_w = leggauss(deg)
+        self.c = 0.5 * (nodes + 1.0)
+        self.b_numpy = gauss_w / deg
+        # basis[j](x) in product form (stable for deg = 10, where the power basis loses five digits), for an array of points x
+        denom = np.array([np.prod(self.c[j] - np.delete(self.c, j)) for j in range(deg)])
+
+        def basis(x):                                    # -> (deg, len(x))
+            diff = x[None, :] - self.c[:, None]          # (node, point)
+            return np.stack([np.prod(np.delete(diff, j, axis=0), axis=0) / denom[j] for j in range(deg)])
+
+        def integrate_to(upper):                         # every basis polynomial over [0, upper]: deg Gauss points are exact (degree deg-1)
+            x = 0.5 * upper * (nodes + 1.0)
+            return 0.5 * upper * (basis(x) @ gauss_w)
+        self.a = np.stack([integrate_to(ci) for ci in self.c])      # a[i, j] = int_0^{c_i} basis_j
+        self.b = integrate_to(1.0)
 
 
 def linear_implicit_runge_kutta_step(weights, matrix, current_value, step_width):

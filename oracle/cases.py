@@ -161,3 +161,21 @@ def simple_case(mesh_cells=(12, 4), lengths=(2.0, 0.41), dt=1e-3, seed=5, perm="
     dS = Smat.diagonal()
     return dict(A=A, mstar=mstar, free=free, Bf=Bf, S=Smat, H=H, HT=H.T.tocsr(), inner=inner, bproj=bproj, perm=perm,
                 dS=np.where(dS > 0, 1.0 / np.where(dS > 0, dS, 1.0), 0.0), n_u=n_u, n_p=n_p, N=N, f=S.f.numpy(), u0=S.u0.numpy(), dt=dt)
+
+
+def dof_blocks(c, size=5):
+    """Disjoint blocks of consecutive free velocity dofs: stand where the reference has its facet blocks
+    (templates/NavierStokesSIMPLE_iterative.py:360-362)."""
+    free_idx = np.nonzero(c.free_u)[0]
+    return [free_idx[i:i + size] for i in range(0, len(free_idx), size)]
+
+
+def aggregation_transform(c, size=6):
+    """Piecewise-constant transform from an auxiliary space of aggregates (consecutive free dofs) to the velocity space and the
+    Galerkin coarse matrix; stands where the reference has the H(div) <- H1 `transform` (:282-290)."""
+    import scipy.sparse as sp
+    free_idx = np.nonzero(c.free_u)[0]
+    agg = np.arange(len(free_idx)) // size
+    T = sp.csr_matrix((np.ones(len(free_idx)), (free_idx, agg)), shape=(c.n_u, int(agg.max()) + 1))
+    Ac = (T.T @ c.A @ T).tocsr()
+    return T, Ac

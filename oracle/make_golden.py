@@ -236,6 +236,46 @@ def gold_simple():
           "plain vs cond", float(np.linalg.norm(out["gfu_plain"][-1] - out["gfu_cond"][-1])))
 
 
+def gold_mypreA():
+    """MypreA.Mult (templates/NavierStokesSIMPLE_iterative.py:364-391): the class is defined inside SolveInitial, so its source
+    is cut out of the reference file with ast and executed, unmodified, over the stand-in with `transform` and `preAh1` in scope
+    (as they are in the enclosing function).  Both variants (GS True / False), two inputs each."""
+    import ast
+    import textwrap
+    from navier_stokes_solver_b200.la import color_blocks
+    from oracle.cases import aggregation_transform, dof_blocks
+    path = os.path.join(REF, "templates", "NavierStokesSIMPLE_iterative.py")
+    src = open(path).read()
+    node = next(n for n in ast.walk(ast.parse(src)) if isinstance(n, ast.ClassDef) and n.name == "MypreA")
+    lines = src.splitlines()[node.lineno - 1:node.end_lineno]
+    code = textwrap.dedent("\n".join(lines))
+    c = Case("chan2d")
+    T, Ac = aggregation_transform(c)
+    dc = 1.0 / Ac.diagonal()
+    blocks = dof_blocks(c, 4)
+    order, color_ptr = color_blocks(c.A, blocks)          # the device smoother sweeps colour by colour: fix that block order
+    blocks = [blocks[i] for i in order]
+    ns = {"BaseMatrix": ngsolve.BaseMatrix, "transform": SparseMatrix(T), "preAh1": DiagonalMatrix(dc)}
+    exec(compile(code, path + ":MypreA", "exec"), ns)
+    space = type("Space", (), {"ndof": c.n_u})()
+    blf = type("Blf", (), {"mat": SparseMatrix(c.A), "space": space})()
+    rng = np.random.default_rng(11)
+    xs = np.stack([rng.uniform(-1, 1, c.n_u) * c.free_u for _ in range(2)])
+    out = dict(x=xs, block_ptr=np.concatenate([[0], np.cumsum([len(b) for b in blocks])]), block_dofs=np.concatenate(blocks),
+               fingerprint=np.append(c.fingerprint(), [T.nnz, float(dc.sum())]), source_lines=np.array([node.lineno, node.end_lineno]))
+    for GS in (True, False):
+        pre = ns["MypreA"](space, blf, blocks, GS=GS)
+        assert pre.Height() == c.n_u and pre.Width() == c.n_u
+        ys = []
+        for x in xs:
+            y = BaseVector(np.full(c.n_u, 7.0))           # Mult must overwrite, not accumulate
+            pre.Mult(BaseVector(x.copy()), y)
+            ys.append(y.NumPy().copy())
+        out["y_gs" if GS else "y_add"] = np.stack(ys)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "mypreA"), **out)
+    print("mypreA lines", node.lineno, node.end_lineno, "|y_gs|", float(np.linalg.norm(out["y_gs"])), "|y_add|", float(np.linalg.norm(out["y_add"])))
+
+
 def gold_orth():
     rng = np.random.default_rng(7)
     n, m = 777, 5
@@ -287,3 +327,4 @@ if __name__ == "__main__":
     gold_rk()
     gold_heat()
     gold_simple()
+    gold_mypreA()

@@ -444,6 +444,43 @@ class SparseMatrix(BaseMatrix):
     def T(self):
         return _Transposed(self)
 
+    def CreateBlockSmoother(self, blocks):
+        return _BlockSmoother(self.csr, blocks)
+
+
+class _BlockSmoother(BaseMatrix):
+    """``mat.CreateBlockSmoother(blocks)`` (NGSolve, third-party: restated).  As an operator it is additive block Jacobi,
+    y = sum_b P_b^T A_bb^-1 P_b x; ``Smooth(u, f)`` is one block Gauss-Seidel sweep over the blocks in list order,
+    u_b += A_bb^-1 (f - A u)_b, ``SmoothBack`` the same sweep in reverse order."""
+
+    def __init__(self, csr, blocks):
+        self.csr = csr
+        self.blocks = [_np.asarray(b, dtype=_np.int64) for b in blocks if len(b)]
+        self.inv = [_np.linalg.inv(csr[b][:, b].toarray()) for b in self.blocks]
+
+    def MultAdd(self, s, x, y):
+        for b, inv in zip(self.blocks, self.inv):
+            y._a[b] += s * (inv @ x._a[b])
+
+    MultTransAdd = MultAdd
+
+    def _sweep(self, u, f, order):
+        for k in order:
+            b = self.blocks[k]
+            u._a[b] += self.inv[k] @ (f._a[b] - self.csr[b] @ u._a)
+
+    def Smooth(self, u, f):
+        self._sweep(u, f, range(len(self.blocks)))
+
+    def SmoothBack(self, u, f):
+        self._sweep(u, f, range(len(self.blocks) - 1, -1, -1))
+
+    def Height(self):
+        return self.csr.shape[0]
+
+    def Width(self):
+        return self.csr.shape[1]
+
 
 class DiagonalMatrix(BaseMatrix):
     """Jacobi ('local') preconditioner: y = d .* x, with d = 0 on constrained dofs."""

@@ -45,3 +45,21 @@ def test_two_rank_bpcg_and_minres_match_single_gpu(sell, fused_halo):
         assert r["minres_sol_rel"] < 1e-8, r
         assert r["simple_gfu_rel"] < 1e-8 and r["simple_gfup_rel"] < 1e-6, r
         assert all(abs(a - b) <= 1 for a, b in zip(r["simple_its"], r["simple_its1"])), r
+
+
+@pytest.mark.gpu
+def test_dead_exchange_returns_an_error():
+    """Failure detection of the peer-memory protocol: with one rank never publishing its interface entries the waits are abandoned
+    after NSB_SPIN_TIMEOUT_MS and every rank's solver call returns NSB_ERR_NCCL (raised as NsbError) instead of hanging in a kernel."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    env = dict(os.environ, NSB_SELL_MIN_NNZ="0", NSB_FAULT_SKIP_PUBLISH="1", NSB_SPIN_TIMEOUT_MS="400")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "dist_fault_worker.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env, cwd=ROOT)
+    rows = [json.loads(m) for m in re.findall(r"FAULTRESULT (\{.*?\})", res.stdout)]
+    assert len(rows) == 2, res.stdout[-2000:] + res.stderr[-2000:]
+    for r in rows:
+        assert r["error"] is not None and "timed out" in r["error"], r
+        assert r["seconds"] < 60, r

@@ -332,3 +332,20 @@ def test_simple_oracle_matches_reference_steps(tag):
                                 dt, n_u, conv=lambda g: conv @ g, f=T["f"])
         assert relerr(gfu, gold["gfu_" + tag][step]) < 1e-11
         assert relerr(p, gold["gfup_" + tag][step]) < 1e-9
+
+
+@pytest.mark.parametrize("GS", [True, False])
+def test_oracle_aux_space_pre_matches_reference_mypreA(cases, GS):
+    """krylov_oracle.aux_space_pre against MypreA.Mult of the reference run unmodified (tests/golden/mypreA.npz)."""
+    from oracle import krylov_oracle as ko
+    from oracle.cases import aggregation_transform, load_golden
+    gold = load_golden("mypreA")
+    c = cases("chan2d")
+    T, Ac = aggregation_transform(c)
+    dc = 1.0 / Ac.diagonal()
+    bp = gold["block_ptr"]
+    blocks = [gold["block_dofs"][bp[k]:bp[k + 1]] for k in range(len(bp) - 1)]
+    sm = ko.BlockSmoother(c.A, blocks)
+    want = gold["y_gs" if GS else "y_add"]
+    for x, y in zip(gold["x"], want):
+        np.testing.assert_allclose(ko.aux_space_pre(sm, c.A, T, dc, x, GS=GS), y, rtol=0, atol=1e-13 * np.abs(y).max())
