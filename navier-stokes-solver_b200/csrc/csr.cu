@@ -387,9 +387,32 @@ int nsb_spmv_bench(nsb_ctx ctx, nsb_mat m, int warmup, int reps, double* ms_per_
     cudaEvent_t e0, e1;
     NSB_CUDA(cudaEventCreate(&e0));
     NSB_CUDA(cudaEventCreate(&e1));
-    for (int i = 0; i < warmup; ++i) NSB_CHECK(spmv_plain(c, m, dx.p, dy.p));
+    // NSB_BENCH_HALOIN=1 (diagnostic): the same SpMV through the kernel variant that takes halo columns from a landing buffer
+    // (p2p.cuh: HaloIn) with an empty halo and the identity chunk order -- what that variant costs by itself, on one GPU
+    const char* hb = getenv("NSB_BENCH_HALOIN");
+    std::vector<std::unique_ptr<DevBuf<int>>> orders;
+    const bool halo_variant = hb && atoi(hb) != 0 && !m->panels.empty() && !m->halo;
+    if (halo_variant) {
+        for (const auto& P : m->panels) {
+            std::vector<int> id((size_t)P->sell_nchunks);
+            for (int k = 0; k < P->sell_nchunks; ++k) id[(size_t)k] = k;
+            orders.emplace_back(new DevBuf<int>());
+            NSB_CHECK(orders.back()->alloc(P->sell_nchunks));
+            NSB_CUDA(cudaMemcpy(orders.back()->p, id.data(), sizeof(int) * id.size(), cudaMemcpyHostToDevice));
+        }
+    }
+    auto one = [&]() -> int {
+        if (!halo_variant) return spmv_plain(c, m, dx.p, dy.p);
+        for (size_t k = 0; k < m->panels.size(); ++k) {
+            const HaloIn H{nullptr, (const u64*)c.d_mail, dx.p, m->cols, 0, orders[k]->p, m->panels[k]->sell_nchunks, nullptr,
+                           SpinGuard{c.fault, 0}};
+            NSB_CHECK((spmv_sell_panel<0, PlainRowOp, HaloIn>(c, m->panels[k].get(), dx.p, PlainRowOp{dy.p}, H)));
+        }
+        return NSB_OK;
+    };
+    for (int i = 0; i < warmup; ++i) NSB_CHECK(one());
     NSB_CUDA(cudaEventRecord(e0, c.stream));
-    for (int i = 0; i < reps; ++i) NSB_CHECK(spmv_plain(c, m, dx.p, dy.p));
+    for (int i = 0; i < reps; ++i) NSB_CHECK(one());
     NSB_CUDA(cudaEventRecord(e1, c.stream));
     NSB_CUDA(cudaEventSynchronize(e1));
     float ms = 0.f;

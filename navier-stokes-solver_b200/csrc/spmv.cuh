@@ -311,15 +311,21 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
                     const int cs = __shfl_sync(0xffffffffu, cs_l, k);
                     const int p0 = __shfl_sync(0xffffffffu, p0_l, k) - u0;
                     const int len = __shfl_sync(0xffffffffu, p1_l, k) - u0 - p0;
-                    for (int l = lane; l < len; l += 32) {
-                        if constexpr (HALO) {
-                            // halo columns come from the landing buffer the neighbours store into: coherent loads, no L1
-                            if (cs + l >= H.n_owned) {
-                                sx[p0 + l] = __ldcv(H.land + (cs + l - H.n_owned));
-                                continue;
+                    if constexpr (HALO) {
+                        // halo columns come from the landing buffer the neighbours store into: coherent loads, no L1.  Owned and
+                        // halo columns are numbered apart, so a run is one or the other (a run across the border is cut here)
+                        if (cs + len <= H.n_owned) {          // (warp-uniform) an owned run: the same loop as the plain kernel
+                            for (int l = lane; l < len; l += 32) cp_async_f64(sx + p0 + l, x + cs + l);
+                        } else if (cs >= H.n_owned) {
+                            for (int l = lane; l < len; l += 32) sx[p0 + l] = __ldcv(H.land + (cs + l - H.n_owned));
+                        } else {                              // a run across the owned | halo border
+                            for (int l = lane; l < len; l += 32) {
+                                if (cs + l >= H.n_owned) sx[p0 + l] = __ldcv(H.land + (cs + l - H.n_owned));
+                                else cp_async_f64(sx + p0 + l, x + cs + l);
                             }
                         }
-                        cp_async_f64(sx + p0 + l, x + cs + l);
+                    } else {
+                        for (int l = lane; l < len; l += 32) cp_async_f64(sx + p0 + l, x + cs + l);
                     }
                 }
             }
@@ -351,10 +357,15 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
     const bool pipelined = async_stage && (S.sell_flags & 16);
     bool staged = false;   // this chunk's copies were issued during the previous chunk's epilogue
 
+    // row-partitioned: the chunk visiting order (interior chunks first) is read ONE ITERATION AHEAD -- a load of order[ci] at the
+    // top of the iteration sat in front of every other load of the chunk (uptr, the runs, the streams: +6..19 % per SpMV)
+    int chunk_ahead = 0;
+    if constexpr (HALO) chunk_ahead = blockIdx.x < S.nchunks ? __ldg(H.order + blockIdx.x) : 0;
     for (int ci = blockIdx.x; ci < S.nchunks; ci += gridDim.x) {
         int chunk = ci;
         if constexpr (HALO) {
-            chunk = __ldg(H.order + ci);
+            chunk = chunk_ahead;
+            chunk_ahead = ci + (int)gridDim.x < S.nchunks ? __ldg(H.order + ci + (int)gridDim.x) : 0;
             if (ci >= H.n_interior && !landed) {
                 // first chunk with halo columns: the neighbours' entries of this exchange must have landed.  The
                 // barrier below orders the other threads of the block behind these acquires.
@@ -464,7 +475,7 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
             const int cn = ci + (int)gridDim.x;
             if constexpr (HALO) {
                 if (cn < H.n_interior || landed) {
-                    stage_async(__ldg(H.order + cn));
+                    stage_async(chunk_ahead);
                     staged = true;
                 }
             } else {
