@@ -207,6 +207,17 @@ NSB_API int nsb_lanczos_eigs(nsb_ctx ctx, nsb_mat A, nsb_pre pre, const double* 
  * in place.  basis = m vectors of length n stored one after another (stride n). */
 NSB_API int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, int tries);
 
+/* orthonormalize(basis, tries) as nsb_orthonormalize, for callers that must not allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The call allocates nothing -- no cudaMalloc / cudaFree / stream-ordered allocation: its scratch (Gram-Schmidt state, per-block
+ * partial sums, arrival ticket) is a file-scope device array of 96 KiB that every GPU loading the library holds until exit.
+ * Limits (larger requests are refused with NSB_ERR_INVALID): m <= NSB_NOALLOC_MAX_VECTORS, n <= NSB_NOALLOC_MAX_LENGTH, basis
+ * device-resident (m vectors of length n, stride n), single-GPU context.  All calls on a device share the array and it keeps the
+ * last call's contents (the call clears what must start at zero): calls that overlap on the GPU race -- one call at a time per device. */
+#define NSB_NOALLOC_MAX_VECTORS 8
+#define NSB_NOALLOC_MAX_LENGTH ((int64_t)1 << 31)
+NSB_API int nsb_orthonormalize_noalloc(nsb_ctx ctx, double* basis, int64_t n, int m, int tries);
+
 /* Device-resident vector helpers for the time-stepper chains (DoTimeStep / Project,
  * templates/NavierStokesSIMPLE_iterative.py:427-443): all pointers must be device pointers.
  *   nsb_vec_axpby:        y = a x + b y          (temp.data += ..., gfu.vec.data += timestep * temp2.data, :432-438)

@@ -60,6 +60,7 @@ SIGNATURES = {
                          P(C.c_int), P(C.c_double), P(C.c_int)]),
     "nsb_lanczos_eigs": (C.c_int, [c_ctx, c_mat, c_pre, C.c_void_p, C.c_int, C.c_double, P(C.c_double), P(C.c_double), P(C.c_int)]),
     "nsb_orthonormalize": (C.c_int, [c_ctx, C.c_void_p, C.c_int64, C.c_int, C.c_int]),
+    "nsb_orthonormalize_noalloc": (C.c_int, [c_ctx, C.c_void_p, C.c_int64, C.c_int, C.c_int]),
     "nsb_cond_create": (C.c_int, [c_ctx, c_mat, c_mat, c_mat, c_mat, c_mat, P(C.c_void_p)]),
     "nsb_cond_destroy": (C.c_int, [C.c_void_p]),
     "nsb_cond_apply": (C.c_int, [c_ctx, C.c_void_p, C.c_void_p, C.c_void_p]),

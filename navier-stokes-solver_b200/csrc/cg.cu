@@ -660,6 +660,101 @@ extern "C" int nsb_orthonormalize(nsb_ctx ctx, double* basis, int64_t n, int m, 
     return NSB_OK;
 }
 
+// ---- orthonormalize without any allocation ------------------------------------------------------------------------------
+// nsb_orthonormalize_noalloc: the column-batched modified Gram-Schmidt above for callers that must not allocate (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every byte of scratch the kernels need -- the GsState (Gram entries, coefficients, reduction landing zone),
+// the per-block partial sums of the grid reductions and their arrival ticket -- lives in ONE file-scope device array that every
+// GPU loading the library holds until exit (kNoAllocScratchBytes = 96 KiB).  In host code the array's name is only a stand-in:
+// its device address is taken once per device with cudaGetSymbolAddress (that device current) and passed to the kernels.
+// All calls share the array: calls that overlap on the GPU (two streams, two host threads) race on it.
+namespace nsb {
+
+constexpr int kNoAllocMaxGrid = 148 * 8;   // blocks of a vector kernel (vec_grid's cap on a 148-SM part)
+constexpr size_t kNoAllocStateBytes = (sizeof(GsState) + 255) / 256 * 256;
+constexpr size_t kNoAllocPartialBytes = sizeof(double) * (size_t)(kGsMax + 1) * kNoAllocMaxGrid;
+constexpr size_t kNoAllocScratchBytes = 96 * 1024;
+static_assert(kNoAllocStateBytes + kNoAllocPartialBytes + 256 <= kNoAllocScratchBytes, "no-alloc scratch too small");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// device address of g_noalloc_scratch on device `dev` (current), resolved once per device
+static int noalloc_scratch_ptr(int dev, unsigned char** out) {
+    static unsigned char* cached[64] = {nullptr};
+    if (dev < 0 || dev >= 64) {
+        set_error("nsb_orthonormalize_noalloc: device ordinal %d out of range", dev);
+        return NSB_ERR_INVALID;
+    }
+    if (!cached[dev]) {
+        unsigned char* p = nullptr;
+        NSB_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return NSB_OK;
+}
+
+template <int J>
+static void gs_column_static(Context& c, const GsPtrs& B, double* bj, int64_t n, GsState* S, double* partials, unsigned int* ticket,
+                             int j, int vg, const RedMode& red) {
+    if (J > 0) {
+        k_gs_dots<(J > 0 ? J : 1)><<<vg, kBlock, 0, c.stream>>>(B, bj, n, S, partials, ticket, red);
+        c.launches++;
+    }
+    k_gs_update<J><<<vg, kBlock, 0, c.stream>>>(B, bj, n, S, j, partials, ticket, red);
+    k_gs_scale_by<<<vg, kBlock, 0, c.stream>>>(bj, S, n);
+    c.launches += 2;
+}
+
+}  // namespace nsb
+
+extern "C" int nsb_orthonormalize_noalloc(nsb_ctx ctx, double* basis, int64_t n, int m, int tries) {
+    NSB_REQUIRE(ctx && basis && n >= 0 && m >= 0 && tries >= 0, "nsb_orthonormalize_noalloc: bad argument");
+    Context& c = ctx->c;
+    NSB_REQUIRE(c.nranks == 1, "nsb_orthonormalize_noalloc: single-GPU contexts only");
+    NSB_REQUIRE(m <= NSB_NOALLOC_MAX_VECTORS, "nsb_orthonormalize_noalloc: m = %d vectors exceeds the maximum of %d the static scratch holds",
+                m, NSB_NOALLOC_MAX_VECTORS);
+    NSB_REQUIRE(n <= NSB_NOALLOC_MAX_LENGTH, "nsb_orthonormalize_noalloc: n = %lld exceeds the maximum length %lld", (long long)n,
+                (long long)NSB_NOALLOC_MAX_LENGTH);
+    NSB_CUDA(cudaSetDevice(c.device));
+    if (m == 0 || n == 0) return NSB_OK;
+    NSB_REQUIRE(is_device_ptr(basis), "nsb_orthonormalize_noalloc: basis must be device-resident (a host basis would need a staging allocation)");
+    const int vg = vec_grid(n, c.num_sms);
+    NSB_REQUIRE(vg <= kNoAllocMaxGrid, "nsb_orthonormalize_noalloc: a grid of %d blocks exceeds the %d the static scratch holds", vg,
+                kNoAllocMaxGrid);
+    unsigned char* base = nullptr;
+    NSB_CHECK(noalloc_scratch_ptr(c.device, &base));
+    GsState* S = (GsState*)base;
+    double* partials = (double*)(base + kNoAllocStateBytes);
+    unsigned int* ticket = (unsigned int*)(base + kNoAllocStateBytes + kNoAllocPartialBytes);
+    // the array keeps the last call's contents: the state and the arrival ticket must start at zero
+    NSB_CUDA(cudaMemsetAsync(base, 0, kNoAllocStateBytes, c.stream));
+    NSB_CUDA(cudaMemsetAsync(ticket, 0, 256, c.stream));
+    RedMode red;
+    memset(&red, 0, sizeof(red));
+    red.kind = kRedLocal;
+    GsPtrs B;
+    for (int k = 0; k < kGsMax; ++k) B.q[k] = basis + (int64_t)(k < m ? k : 0) * n;
+    for (int t = 0; t < tries; ++t) {                                   // orthonormalization.py:8
+        for (int j = 0; j < m; ++j) {                                   // :9
+            double* bj = basis + (int64_t)j * n;
+            switch (j) {
+                case 0: gs_column_static<0>(c, B, bj, n, S, partials, ticket, j, vg, red); break;
+                case 1: gs_column_static<1>(c, B, bj, n, S, partials, ticket, j, vg, red); break;
+                case 2: gs_column_static<2>(c, B, bj, n, S, partials, ticket, j, vg, red); break;
+                case 3: gs_column_static<3>(c, B, bj, n, S, partials, ticket, j, vg, red); break;
+                case 4: gs_column_static<4>(c, B, bj, n, S, partials, ticket, j, vg, red); break;
+                case 5: gs_column_static<5>(c, B, bj, n, S, partials, ticket, j, vg, red); break;
+                case 6: gs_column_static<6>(c, B, bj, n, S, partials, ticket, j, vg, red); break;
+                default: gs_column_static<7>(c, B, bj, n, S, partials, ticket, j, vg, red); break;
+            }
+        }
+    }
+    NSB_CUDA(cudaGetLastError());
+    NSB_CUDA(cudaStreamSynchronize(c.stream));
+    return NSB_OK;
+}
+
 // ---- heat.py time-loop body (exponential-integrator step in a Krylov-like subspace) ----------------
 namespace nsb {
 
