@@ -263,6 +263,8 @@ def main():
     ap.add_argument("--simple-steps", type=int, default=2)
     ap.add_argument("--simple-proj-maxsteps", type=int, default=200)
     ap.add_argument("--no-gs", action="store_true", help="skip the Gram-Schmidt leg")
+    ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the weak-scaling leg (--weak-dofs unknowns per GPU)")
+    ap.add_argument("--weak-dofs", type=float, default=20e6, help="unknowns per GPU of the weak-scaling leg")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -483,6 +485,11 @@ def main():
     if not args.no_simple:
         simple_info = benchlegs.guarded(benchlegs.simple_step_leg, env, peak, spmv_bytes, CG_VEC_PASSES)
 
+    # ---- weak scaling beside the strong-scaling headline: --weak-dofs unknowns PER GPU (N > 1)
+    weak_info = None
+    if world > 1 and not args.no_weak:
+        weak_info = benchlegs.guarded(benchlegs.weak_scaling_leg, env, args.weak_dofs, args.iters, peak, bpcg_iter_bytes)
+
     # ---- parity where the driver can see it
     parity = None
     if not args.no_parity:
@@ -555,6 +562,8 @@ def main():
         line["gram_schmidt"] = gs_info
     if simple_info:
         line["simple_step"] = simple_info
+    if weak_info:
+        line["weak_scaling"] = weak_info
     if parity:
         line["parity_at_sample" if world == 1 else "parity_vs_single"] = parity
     if cpu_line:

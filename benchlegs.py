@@ -336,3 +336,38 @@ def simple_step_leg(env, peak, spmv_bytes, cg_vec_passes):
     del D, st
     torch.cuda.empty_cache()
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+def weak_scaling_leg(env, dofs_per_gpu, iters, peak, bpcg_iter_bytes):
+    """N > 1: the same channel refined until every GPU holds ~dofs_per_gpu unknowns (the headline is the strong-scaling run of ONE
+    20M-dof system); BramblePasciakCG iterations/s in the loop and the per-GPU fraction of the HBM roofline."""
+    import torch
+    nsb, syn, P = env.nsb, env.syn, env.partition
+    cells = syn.stokes_cells_for_dofs(dofs_per_gpu * env.world)
+    D = P.build_distributed_stokes(cells, env.lengths, env.ctx, env.rank, env.world, device="cuda:%d" % env.local)
+    pA = nsb.DiagonalPreconditioner.from_diagonal(D.dA, env.ctx)
+    pM = nsb.DiagonalPreconditioner.from_diagonal(D.dM, env.ctx)
+    with env.quiet():
+        lam = 0.8 * min(nsb.EigenValues_Preconditioner(D.A, pA, tol=1e-3, maxsteps=300, start=D.lanczos_start))
+    best = None
+    for rep in range(3):
+        sol = D.u_start.clone()
+        env.barrier()
+        with env.quiet():
+            nsb.BramblePasciakCG(D.A, D.B, None, D.f, D.g, pA, pM, sol, tol=0.0, maxsteps=iters, printrates=False, initialize=False, lam_min=lam)
+        secs = torch.tensor([nsb.solvers.last_info["seconds"]], dtype=torch.float64, device="cuda")
+        _allreduce(env, secs, "max")
+        if rep > 0 and (best is None or float(secs[0]) < best):
+            best = float(secs[0])
+    hist = nsb.solvers.last_info["history"]
+    nb = bpcg_iter_bytes(D.n_u_global, D.n_p_global, D.nnzA_global, D.nnzB_global)
+    rate = iters / best
+    out = {"dofs": int(D.n_u_global + D.n_p_global), "dofs_per_gpu": int((D.n_u_global + D.n_p_global) // env.world), "cells": list(cells),
+           "iterations_per_s": rate, "us_per_iteration": 1e6 * best / iters, "algorithmic_bytes_per_iteration": nb,
+           "achieved_gbs_per_gpu": nb * rate / 1e9 / env.world, "frac_of_measured_peak": nb * rate / 1e9 / env.world / peak,
+           "frac_of_nominal_8TBs": nb * rate / 1e9 / env.world / 8000.0, "lambda_min_used": lam,
+           "history_checkpoints": {"err0": float(hist[0]), "err_%d" % iters: float(hist[iters])}}
+    del D, pA, pM
+    torch.cuda.empty_cache()
+    return out

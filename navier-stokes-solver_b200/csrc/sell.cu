@@ -161,6 +161,78 @@ __global__ void k_sell_fill(CsrView A, int pbase, const unsigned short* __restri
     }
 }
 
+// Bank-aware placement of a row's entries (T >= 4 lanes per row).  The compute phase gathers x from shared memory with one
+// 64-bit load per stored entry; the 16 lanes of a half-warp -- 16 / T rows, T lanes each -- are served in one pass only when their
+// 16 chunk-local column indices differ mod 16 (16 eight-byte banks).  With the entries of a row in ascending column order the
+// long pressure rows of B (189 entries, 8 lanes per row) ran at 3 extra passes per load (ncu, round 1: 16.2M bank conflicts on
+// 5.3M loads, short-scoreboard and MIO-throttle stalls, 0.76 of the DRAM rate of the other SpMVs).  The order of the entries inside a
+// row is free, so each row is laid out group by group (a group = the T entries its lanes load together): the 16 residues are cut
+// into 16 / T sectors of T residues, row rho of the half-warp takes its T entries of group g from sector (g + rho) mod (16 / T), one
+// per residue -- the rows of a half-warp then hit disjoint banks -- and falls back to its fullest other residue when one runs dry.
+constexpr int kBankRowMax = 1024;   // rows longer than this keep the ascending order
+
+__global__ void __launch_bounds__(128) k_sell_fill_banked(CsrView A, int pbase, const unsigned short* __restrict__ lcol_csr, int log2R,
+                                                          int64_t nvr, int rps, int T, const unsigned short* __restrict__ perm,
+                                                          const unsigned int* __restrict__ off, double* __restrict__ vals,
+                                                          unsigned short* __restrict__ lcol) {
+    const int Q = 16 / T;   // rows per half-warp = residue sectors
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvr; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = ((i >> log2R) << log2R) + perm[i];
+        if (r >= A.rows) continue;
+        const int p0 = A.rowptr[r], len = A.rowptr[r + 1] - p0;
+        const int64_t base = (int64_t)off[i / rps] * 64;
+        const int ris = (int)(i % rps);
+        auto put = [&](int pos, int e) {   // entry e of the row goes to position pos = (group, member): group = 2 * pair-block + slot
+            const int g = pos / T, t = pos % T;
+            const int64_t dst = base + (int64_t)(g >> 1) * 64 + (ris * T + t) * 2 + (g & 1);
+            vals[dst] = A.values[p0 + e];
+            lcol[dst] = lcol_csr[p0 + e - pbase];
+        };
+        if (len > kBankRowMax) {
+            for (int e = 0; e < len; ++e) put((e >> 1) / T * 2 * T + (e & 1) * T + (e >> 1) % T, e);   // ascending order, as k_sell_fill
+            continue;
+        }
+        unsigned short byres[kBankRowMax];   // the row's entries bucketed by residue (counting sort, stable)
+        int cnt[16], head[16];
+        for (int b = 0; b < 16; ++b) cnt[b] = 0;
+        for (int e = 0; e < len; ++e) cnt[lcol_csr[p0 + e - pbase] & 15]++;
+        int acc = 0;
+        for (int b = 0; b < 16; ++b) {
+            head[b] = acc;
+            acc += cnt[b];
+        }
+        {
+            int fill[16];
+            for (int b = 0; b < 16; ++b) fill[b] = head[b];
+            for (int e = 0; e < len; ++e) byres[fill[lcol_csr[p0 + e - pbase] & 15]++] = (unsigned short)e;
+        }
+        const int rho = ris % Q;
+        int placed = 0;
+        for (int g = 0; placed < len; ++g) {
+            const int sector = (g + rho) % Q;
+            unsigned int used = 0;   // residues this row already used in this group
+            for (int t = 0; t < T && placed < len; ++t) {
+                int b = sector * T + t;
+                if (cnt[b] == 0 || (used >> b & 1u)) {   // preferred residue dry: the fullest residue not yet used in this group
+                    int best = -1;
+                    for (int c = 0; c < 16; ++c)
+                        if (!(used >> c & 1u) && cnt[c] > 0 && (best < 0 || cnt[c] > cnt[best])) best = c;
+                    if (best < 0) {   // fewer distinct residues left than lanes: any entry
+                        for (int c = 0; c < 16; ++c)
+                            if (cnt[c] > 0 && (best < 0 || cnt[c] > cnt[best])) best = c;
+                    }
+                    b = best;
+                }
+                used |= 1u << b;
+                put(g * T + t, byres[head[b]]);
+                head[b]++;
+                cnt[b]--;
+                placed++;
+            }
+        }
+    }
+}
+
 static int ilog2(int64_t v) {
     int l = 0;
     while ((1LL << (l + 1)) <= v) ++l;
@@ -399,9 +471,17 @@ static int build_sell_panel(Context& c, nsb_mat_s* m, int64_t row0, int64_t rows
     NSB_CHECK(ms->sell_lcol.alloc(stored > 0 ? stored : 64));
     NSB_CUDA(cudaMemsetAsync(ms->sell_vals.p, 0, sizeof(double) * (size_t)(stored > 0 ? stored : 64), c.stream));
     NSB_CUDA(cudaMemsetAsync(ms->sell_lcol.p, 0, sizeof(unsigned short) * (size_t)(stored > 0 ? stored : 64), c.stream));
-    const int64_t fg = (nvr + 7) / 8 < (int64_t)c.num_sms * 8 ? (nvr + 7) / 8 : (int64_t)c.num_sms * 8;
-    k_sell_fill<<<(int)fg, kBlock, 0, c.stream>>>(A, pbase, lcol_csr.p, log2R, nvr, rps, T, ms->sell_perm.p, ms->sell_off.p,
-                                                 ms->sell_vals.p, ms->sell_lcol.p);
+    const char* envb = getenv("NSB_SELL_BANKED");   // 1: bank-aware entry order inside the rows of T >= 4 panels (see k_sell_fill_banked)
+    const bool banked = T >= 4 && T <= 16 && envb && atoi(envb) != 0;
+    if (banked) {
+        const int64_t bg = (nvr + 127) / 128 < (int64_t)c.num_sms * 16 ? (nvr + 127) / 128 : (int64_t)c.num_sms * 16;
+        k_sell_fill_banked<<<(int)bg, 128, 0, c.stream>>>(A, pbase, lcol_csr.p, log2R, nvr, rps, T, ms->sell_perm.p, ms->sell_off.p,
+                                                          ms->sell_vals.p, ms->sell_lcol.p);
+    } else {
+        const int64_t fg = (nvr + 7) / 8 < (int64_t)c.num_sms * 8 ? (nvr + 7) / 8 : (int64_t)c.num_sms * 8;
+        k_sell_fill<<<(int)fg, kBlock, 0, c.stream>>>(A, pbase, lcol_csr.p, log2R, nvr, rps, T, ms->sell_perm.p, ms->sell_off.p,
+                                                     ms->sell_vals.p, ms->sell_lcol.p);
+    }
     NSB_CUDA(cudaGetLastError());
     NSB_CUDA(cudaStreamSynchronize(c.stream));
     ms->sell_R = (int)R;

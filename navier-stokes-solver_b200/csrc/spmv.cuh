@@ -487,7 +487,7 @@ __global__ void __launch_bounds__(kSellBlock, NSB_SELL_MINBLOCKS) spmv_sell_kern
         if constexpr (has_push<RowOp>::value) {
             // a chunk with rows the op ships to a neighbour (one flag byte per 256 rows): its epilogue also stores those rows into the
             // neighbours' landing buffers; before the first such chunk of this block, wait (bounded) until they consumed the previous exchange
-            if (op.push_out().nruns > 0 && push_touches(op.push_out(), S.row0 + r0, S.row0 + r0 + S.R)) {
+            if (op.push_out().nruns > 0 && push_touches(op.push_out(), S.row0 + r0, S.row0 + min(r0 + (int64_t)S.R, S.rows))) {   // (the last chunk is padded)
                 if (!push_open) {
                     push_wait_consumed(op.push_out(), push_e);
                     push_open = true;
