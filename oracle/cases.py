@@ -179,3 +179,21 @@ def aggregation_transform(c, size=6):
     T = sp.csr_matrix((np.ones(len(free_idx)), (free_idx, agg)), shape=(c.n_u, int(agg.max()) + 1))
     Ac = (T.T @ c.A @ T).tocsr()
     return T, Ac
+
+
+def direct_stokes_solution(c):
+    """Sparse direct solve of the saddle-point system of a Case on its free dofs, Dirichlet values from ``c.u0`` (the
+    reference's own cross-check idea: umfpack at run.py:205, sparsecholesky at NavierStokesSIMPLE_iterative.py:403).
+    Returns the (u | p) vector in the layout of ``c.start()``."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    fr = c.free_u
+    nf = int(fr.sum())
+    A, B = c.A.tocsr(), c.B.tocsr()
+    Aff, Afc, Bf, Bc = A[fr][:, fr], A[fr][:, ~fr], B[:, fr], B[:, ~fr]
+    uc = c.u0[~fr]
+    K = sp.bmat([[Aff, Bf.T], [Bf, None]]).tocsc()
+    x = spl.spsolve(K, np.concatenate([c.f[fr] - Afc @ uc, c.g - Bc @ uc]))
+    u = c.u0.copy()
+    u[fr] = x[:nf]
+    return np.concatenate([u, x[nf:]])

@@ -18,6 +18,28 @@ def relerr(a, b):
     return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
 
 
+_DIRECT = {}
+
+
+def direct_solution(c):
+    """Sparse direct solve of the case's saddle-point system (the reference's own cross-check: run.py:205, :403), cached."""
+    from oracle.cases import direct_stokes_solution
+    if c.mesh not in _DIRECT:
+        _DIRECT[c.mesh] = direct_stokes_solution(c)
+    return _DIRECT[c.mesh]
+
+
+def assert_close_to_direct(c, sol, ref_sol):
+    """Where a parity window against the reference's iterate had to be wider than 1e-8 (ill-conditioned recurrences: two roundings of
+    the same loop end on different iterates), the honest yardstick is the solution of the system itself: the device's iterate must be
+    as close to the direct solve as the reference's own iterate is (within a factor 10, floor 2e-8)."""
+    d = direct_solution(c)
+    dist_ref = relerr(np.asarray(ref_sol), d)
+    dist_dev = relerr(np.asarray(sol), d)
+    assert dist_dev <= max(2e-8, 10.0 * dist_ref), (dist_dev, dist_ref)
+    return dist_dev, dist_ref
+
+
 @pytest.fixture(scope="module")
 def nsb():
     import torch
@@ -309,6 +331,9 @@ def test_bpcg_v1_and_v2_match_reference_golden(nsb, dev, name, mesh):
     m = min(50, len(ref), len(h2))
     np.testing.assert_allclose(h2[:m], ref[:m], rtol=HIST_RTOL)
     assert relerr(sol2.NumPy(), gold["sol_v2"]) < sol_rtol
+    if int(maxsteps) > 100:   # (not the step-capped case) both variants against the sparse direct solve of the same system
+        assert_close_to_direct(c, solution.NumPy(), gold["sol_v1"])
+        assert_close_to_direct(c, sol2.NumPy(), gold["sol_v2"])
     # the printed history has the reference's line format (bramblepasciak_new.py:245)
     assert out.count("it = ") == it2 + 1
 
@@ -515,6 +540,13 @@ def test_bpcg_static_condensation_matches_oracle(nsb, cases, mesh):
         # the exit index and the last digits of the iterate are not comparable -- only that both converged.
         assert nsb.solvers.last_info["status"] == "converged" and info["converged"]
         assert relerr(sol, sol_ref) < 5e-3
+        # Against the sparse direct solve of the same system the reference's algorithm itself ends 3e-4 away on this case (and
+        # does not converge at all with a larger lambda margin: oracle, 20000 iterations at 0.7 lambda_min): the gap is the
+        # algorithm's on a semi-definite form, not the device's -- the device iterate is as close to the true solution as the
+        # reference iterate is.
+        d = direct_solution(c)
+        dist_dev, dist_ref = relerr(sol, d), relerr(sol_ref, d)
+        assert dist_ref > 1e-6 and dist_dev < 5e-3, (dist_dev, dist_ref)
 
 
 @pytest.mark.gpu
@@ -713,6 +745,7 @@ def test_bpcg_with_block_smoother_preconditioner(nsb, cases, gauss_seidel):
     m = min(35, len(h), len(h_ref))
     np.testing.assert_allclose(h[:m], np.array(h_ref[:m]), rtol=HIST_RTOL)
     assert relerr(sol, sol_ref) < 1e-8
+    assert assert_close_to_direct(c, sol, sol_ref)[0] < 1e-8      # and both solved the system: 1e-8 of the sparse direct solve
     # the same smoother preconditions plain CG on A restricted to the free dofs
     rhs = c.A @ (c.free_u * np.random.default_rng(2).uniform(-1, 1, c.n_u)) * c.free_u
     u, errs = nsb.CGSolve(A, rhs, pre, None, 1e-10, 2000)
