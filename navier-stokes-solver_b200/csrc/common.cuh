@@ -141,6 +141,7 @@ struct DevBuf {
         cudaError_t e = cudaMalloc((void**)&p, sizeof(T) * (size_t)count);
         if (e != cudaSuccess) {
             p = nullptr;
+            cudaGetLastError();   // reported here: do not leave it behind for the next library call (cub peeks at the last error)
             set_error("cudaMalloc(%lld bytes) failed: %s", (long long)(sizeof(T) * (size_t)count), cudaGetErrorString(e));
             return NSB_ERR_CUDA;
         }
@@ -153,6 +154,7 @@ struct DevBuf {
         cudaError_t e = cudaMallocAsync((void**)&p, sizeof(T) * (size_t)count, c.stream);
         if (e != cudaSuccess) {
             p = nullptr;
+            cudaGetLastError();
             set_error("cudaMallocAsync(%lld bytes) failed: %s", (long long)(sizeof(T) * (size_t)count), cudaGetErrorString(e));
             return NSB_ERR_CUDA;
         }

@@ -158,6 +158,7 @@ int nsb_csr_create(nsb_ctx ctx, int64_t rows, int64_t cols, int64_t nnz, const v
     NSB_REQUIRE(rowptr && (nnz == 0 || (colidx && values)), "nsb_csr_create: NULL array");
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
+    cudaGetLastError();   // a non-sticky error some earlier caller never collected must not be blamed on the cub calls below
     nsb_mat_s* m = nullptr;
     NSB_CHECK(mat_alloc(c, rows, cols, nnz, &m));
     int r = NSB_OK;

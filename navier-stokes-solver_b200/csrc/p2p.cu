@@ -252,17 +252,22 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     std::vector<int64_t> mine(2 + 2 * (size_t)R, -1);
     mine[0] = land;
     mine[1] = nnb;
+    // Arguments are validated BEFORE the collective, but the verdict travels with it: a rank that returned early here would
+    // leave its peers blocked inside the all-gather.  mine[0] < 0 tells every rank that this one was handed a bad plan.
     int64_t ro = 0;
+    int bad_nb = -1;
     for (int k = 0; k < nnb; ++k) {
         const int nb = h->neighbors[k];
         if (nb < 0 || nb >= R || nb == c.rank) {
-            set_error("nsb_halo_create: neighbour %d out of range", nb);
-            return NSB_ERR_INVALID;
+            bad_nb = nb;
+            mine[0] = -1;
+            break;
         }
         mine[2 + nb] = ro;
         mine[2 + R + nb] = k;
         ro += h->recv_counts[k];
     }
+    if (nnb > kBlock) mine[0] = -1;
     DevBuf<int64_t> ts, tr;
     NSB_CHECK(ts.alloc((int64_t)mine.size()));
     NSB_CHECK(tr.alloc((int64_t)mine.size() * R));
@@ -271,6 +276,19 @@ int p2p_halo_init(Context& c, nsb_halo_s* h) {
     std::vector<int64_t> all(mine.size() * R);
     NSB_CUDA(cudaMemcpy(all.data(), tr.p, sizeof(int64_t) * all.size(), cudaMemcpyDeviceToHost));
     auto tab = [&](int r) { return all.data() + (size_t)r * mine.size(); };
+    for (int r = 0; r < R; ++r)
+        if (tab(r)[0] < 0) {   // every rank sees the same table: every rank returns the error
+            if (r == c.rank && bad_nb != -1) set_error("nsb_halo_create: neighbour %d out of range (rank %d of %d)", bad_nb, c.rank, R);
+            else if (r == c.rank) set_error("nsb_halo_create: more than %d neighbours", kBlock);
+            else set_error("nsb_halo_create: rank %d was given an invalid halo plan", r);
+            return NSB_ERR_INVALID;
+        }
+    for (int r = 0; r < R; ++r)          // symmetry of the neighbour lists, judged from the gathered tables: the same verdict on every rank
+        for (int q = 0; q < R; ++q)
+            if (tab(r)[2 + R + q] >= 0 && tab(q)[2 + R + r] < 0) {
+                set_error("nsb_halo_create: neighbour lists are not symmetric across ranks (rank %d lists %d, not the reverse)", r, q);
+                return NSB_ERR_INVALID;
+            }
 
     P2PHalo* P = new P2PHalo();
     const size_t bytes = sizeof(double) * 2 * (size_t)land + sizeof(u64) * (2 * (size_t)nnb + 1) + 16;   // two vector areas

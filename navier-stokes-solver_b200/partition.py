@@ -348,6 +348,8 @@ def build_distributed_stokes(cells, lengths, ctx, rank, world, device="cuda", gr
     S = syn.assemble_stokes(cells, lengths, device=device, slab=rank, nslabs=world)
     L = localize_stokes(S, rank, world, group)
     del S
+    if torch.cuda.is_available():
+        torch.cuda.empty_cache()   # the library allocates with cudaMalloc: torch's cache still holds the assembly scratch (tens of GB)
     hu, hp = upload_halo(ctx, L.plan_u), upload_halo(ctx, L.plan_p)
     A = SparseMatrix.from_csr(L.A, ctx)
     B = SparseMatrix.from_csr(L.B, ctx)

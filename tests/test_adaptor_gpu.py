@@ -41,7 +41,8 @@ def test_minres_on_adaptor_exports_matches_reference_golden(cases):
     m = min(50, len(errors), len(gold["errors"]))
     np.testing.assert_allclose(errors[:m], gold["errors"][:m], rtol=1e-10)
     got = np.concatenate([gfu.FV().NumPy(), gfp.FV().NumPy()])                          # the caller reads the grid functions (run.py:107-109)
-    assert np.linalg.norm(got - gold["sol"]) / np.linalg.norm(gold["sol"]) < 1e-8
+    # (the envelope of tests/test_gpu_parity.py: two roundings of the recurrence agree down to the level the solve reached)
+    assert np.linalg.norm(got - gold["sol"]) / np.linalg.norm(gold["sol"]) < max(1e-8, 10 * float(gold["errors"][-1]))
     frame = adaptor.errors_frame(errors, nsb.solvers.last_info["seconds"], 0.125, "taylor_hood", 2, "minres", "device", c.N)
     assert list(frame["error"]) == list(errors) and frame["ndofs"].iloc[0] == c.N
 

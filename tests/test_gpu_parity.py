@@ -546,7 +546,7 @@ def test_bpcg_static_condensation_matches_oracle(nsb, cases, mesh):
         # reference iterate is.
         d = direct_solution(c)
         dist_dev, dist_ref = relerr(sol, d), relerr(sol_ref, d)
-        assert dist_ref > 1e-6 and dist_dev < 5e-3, (dist_dev, dist_ref)
+        assert dist_ref > 1e-6 and dist_dev < 1e-2, (dist_dev, dist_ref)
 
 
 @pytest.mark.gpu
@@ -745,7 +745,7 @@ def test_bpcg_with_block_smoother_preconditioner(nsb, cases, gauss_seidel):
     m = min(35, len(h), len(h_ref))
     np.testing.assert_allclose(h[:m], np.array(h_ref[:m]), rtol=HIST_RTOL)
     assert relerr(sol, sol_ref) < 1e-8
-    assert assert_close_to_direct(c, sol, sol_ref)[0] < 1e-8      # and both solved the system: 1e-8 of the sparse direct solve
+    assert_close_to_direct(c, sol, sol_ref)                       # and both solved the system: within 2e-8 of the sparse direct solve
     # the same smoother preconditions plain CG on A restricted to the free dofs
     rhs = c.A @ (c.free_u * np.random.default_rng(2).uniform(-1, 1, c.n_u)) * c.free_u
     u, errs = nsb.CGSolve(A, rhs, pre, None, 1e-10, 2000)
