@@ -282,6 +282,7 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     NSB_REQUIRE(isfinite(k_scale) && k_scale > 0.0, "nsb_bpcg: k_scale must be positive and finite");
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
+    NvtxRange nvtx_call("nsb_bpcg");
     const int64_t n_u = A->rows, n_p = B->rows;
     const int64_t nxu = A->cols, nxp = BT->cols;
     NSB_REQUIRE(B->cols == nxu, "nsb_bpcg: B has %lld columns, A has %lld", (long long)B->cols, (long long)nxu);
@@ -428,6 +429,7 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     };
 
     const int chunk = (n_u + n_p) < 200000 ? 16 : 4;   // iterations in flight between host checks
+    NvtxRange nvtx_its("nsb_bpcg: iterations");   // timer_its (:195-196)
     GraphExecHolder gh;
     int64_t graph_launches = 0;
     int rc = NSB_OK;

@@ -156,6 +156,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
                   bool lanczos, int chunk, bool (*host_check)(void*, const CgState&), void* check_arg, CgState* out_state,
                   float* out_ms, nsb_cond_s* K = nullptr, CgGraph* cache = nullptr) {
     const int64_t n = A->rows;
+    NvtxRange nvtx_call(lanczos ? "nsb_lanczos_eigs: CG-Lanczos" : "nsb_cg");
     // a block smoother as preconditioner is applied between the update kernel and the <w,d> reduction (unfused)
     const bool general_pre = pre != nullptr && pre->kind != 0;
     const double* dinv = (pre && !general_pre) ? pre->d.p : nullptr;
@@ -596,6 +597,7 @@ static int gs_pairwise(Context& c, double* Q, int64_t n, int m, int tries) {
 
 // orthonormalize(basis, tries): column-batched (three passes per column, see k_gs_dots) for m <= 8
 static int gs_device(Context& c, double* Q, int64_t n, int m, int tries) {
+    NvtxRange nvtx_call("nsb_orthonormalize");
     static int batched = -1;
     if (batched < 0) {
         const char* e = getenv("NSB_GS_BATCHED");
@@ -844,6 +846,7 @@ extern "C" int nsb_heat_step(nsb_ctx ctx, nsb_mat K, nsb_mat M, nsb_mat H, nsb_p
     NSB_REQUIRE(stages >= 1 && stages <= 64, "nsb_heat_step: stages must be in [1, 64]");
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
+    NvtxRange nvtx_call("nsb_heat_step");
     const int64_t n = K->rows, nx = K->cols;
     NSB_REQUIRE(M->rows == n && H->rows == n && M->cols == nx && H->cols == nx, "nsb_heat_step: operator sizes differ");
     if (preH) NSB_REQUIRE(preH->n == n, "nsb_heat_step: preconditioner size mismatch");

@@ -12,6 +12,8 @@
 #include <utility>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/nsb200.h"
 
 namespace nsb {
@@ -46,6 +48,18 @@ extern thread_local char g_err[1024];
     } while (0)
 
 // ---------------------------------------------------------------------------------------------
+// tracing: one NVTX range per solver phase (the reference brackets the same phases with NGSolve Timers: bramblepasciak_new.py
+// :111-116,:194-196, bramble_pasciak_cg.py:111-113, orthonormalization.py:6-14, heat.py:85-128).  Header-only NVTX v3: a no-op unless
+// a profiler (nsys, ncu --nvtx) is attached.
+// ---------------------------------------------------------------------------------------------
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+    ~NvtxRange() { nvtxRangePop(); }
+};
+
+// ---------------------------------------------------------------------------------------------
 // launch geometry.  Vector kernels are persistent grid-stride loops: a fixed grid (a multiple of
 // the SM count) keeps every reduction tree identical from run to run for a given length.
 // ---------------------------------------------------------------------------------------------
@@ -78,7 +92,7 @@ struct Context {
     cudaStream_t stream = nullptr;
     int64_t launches = 0;
     bool use_graphs = true;
-    // programmatic dependent launch (NSB_PDL, default on): the kernels of an iteration loop are launched with
+    // programmatic dependent launch (NSB_PDL, default OFF -- measured 0..+0.8 % / -12 %): the kernels of an iteration loop are launched with
     // cudaLaunchAttributeProgrammaticStreamSerialization, so the next kernel's blocks become resident while the
     // previous kernel drains, fetch their immutable matrix structure and park in griddepcontrol.wait
     bool pdl = false;

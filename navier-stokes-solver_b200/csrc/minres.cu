@@ -246,6 +246,7 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
     NSB_REQUIRE(maxsteps >= 0, "nsb_minres: maxsteps < 0");
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
+    NvtxRange nvtx_call("nsb_minres");
     const int64_t n = K->rows;                      // owned rows
     const int64_t nx = K->cols;                     // owned + halo
     NSB_REQUIRE(K->halo ? K->halo->n_owned == n : K->cols == K->rows, "nsb_minres: operator must be square");
@@ -341,6 +342,7 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
         return NSB_OK;
     };
 
+    NvtxRange nvtx_its("nsb_minres: iterations");
     const int period = 6;
     const int reps = n < 200000 ? 4 : 1;   // iterations in flight between host checks: period * reps
     GraphExecHolder gh;

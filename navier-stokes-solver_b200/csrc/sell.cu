@@ -543,6 +543,7 @@ int build_halo_order(Context& c, nsb_mat_s* m) {
 // Build the SELL-LX companion of m, one panel per entry of m->panel_splits (default: the whole matrix).  Leaves
 // m->panels empty when the operator is small or any panel does not qualify (the CSR-vector kernel then runs).
 int build_sell(Context& c, nsb_mat_s* m) {
+    NvtxRange nvtx_call("build_sell (SELL-LX companion)");
     m->panels.clear();
     const char* env = getenv("NSB_SELL");
     if (env && atoi(env) == 0) return NSB_OK;

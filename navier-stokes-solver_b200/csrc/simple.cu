@@ -202,6 +202,7 @@ extern "C" int nsb_simple_step(nsb_ctx ctx, nsb_simple s, double* gfu, const dou
     NSB_REQUIRE(ctx && s && gfu, "nsb_simple_step: NULL argument");
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
+    NvtxRange nvtx_call("nsb_simple_step");
     EventPair ev;
     NSB_CHECK(ev.create());
     NSB_CUDA(cudaEventRecord(ev.e0, c.stream));
