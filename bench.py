@@ -125,6 +125,63 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+class LegWatchdog:
+    """Bounds each OPTIONAL leg that follows the headline measurement.
+
+    The legs after the timed region contain collectives; when one rank of N fails in such a leg (the 4-GPU weak-scaling run: device
+    memory on rank 0 only) the others wait for it forever and the job dies without its JSON line.  The line is therefore assembled
+    BEFORE these legs, each leg adds its key when it returns, and a leg that does not return within `limit` seconds ends the run:
+    rank 0 prints the line with what finished plus a `watchdog` note, every rank leaves with os._exit(0) (a rank blocked inside a
+    collective cannot be unwound any other way).  The headline leg itself is not covered: a hang there has no number to save."""
+
+    def __init__(self, limit, rank, line):
+        self.limit, self.rank, self.line = float(limit), rank, line
+        self.lock = threading.Lock()
+        self.name, self.deadline, self.printed = None, None, False
+        if self.limit > 0:
+            threading.Thread(target=self._watch, daemon=True).start()
+
+    def arm(self, name):
+        with self.lock:
+            self.name, self.deadline = name, time.monotonic() + self.limit
+
+    def disarm(self):
+        with self.lock:
+            self.name, self.deadline = None, None
+
+    @contextlib.contextmanager
+    def leg(self, name):
+        self.arm(name)
+        try:
+            yield
+        finally:
+            self.disarm()
+
+    def emit(self):
+        """Print the line once (rank 0); used by the normal end of main() and by the expiry path."""
+        with self.lock:
+            if self.printed or self.rank != 0:
+                return
+            self.printed = True
+            text = json.dumps(self.line)
+        sys.stdout.write(text + "\n")
+        sys.stdout.flush()
+
+    def _watch(self):
+        while True:
+            time.sleep(1.0)
+            with self.lock:
+                expired = self.deadline is not None and time.monotonic() > self.deadline
+                name = self.name
+                if expired and not self.printed:
+                    self.line["watchdog"] = {"leg": name, "limit_s": self.limit,
+                                             "note": "this optional leg did not return; the keys before it are complete, it and later legs are absent"}
+            if expired:
+                print("bench.py: leg '%s' exceeded %.0f s on rank %d; leaving" % (name, self.limit, self.rank), file=sys.stderr, flush=True)
+                self.emit()
+                os._exit(0)
+
+
 # ------------------------------------------------------------------------------------------------
 # CPU side: the C + OpenMP oracle port (oracle/c/krylov_omp.c) on the SAME assembled blocks
 # ------------------------------------------------------------------------------------------------
@@ -267,6 +324,8 @@ def main():
                     help="N > 1: add the weak-scaling leg (--weak-dofs unknowns per GPU).  Off by default: its first run (4 GPUs) ran out of "
                          "device memory on one rank only and the other ranks then waited in a collective forever (DESIGN.md 6)")
     ap.add_argument("--weak-dofs", type=float, default=20e6, help="unknowns per GPU of the weak-scaling leg")
+    ap.add_argument("--leg-timeout", type=float, default=420.0,
+                    help="seconds each optional leg after the headline may take before the run prints what it has and leaves (0 = no limit)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -440,80 +499,6 @@ def main():
     fmtA = A.format()
     stream_A = sell_stream_bytes(fmtA, A.shape[0], A.shape[1])
 
-    # ---- MINRES on the merged saddle-point operator K = [[A, B^T], [B, 0]] (minres.py; BASELINE metric names both), every N
-    minres_info = None
-    if not args.no_minres:
-        minres_info = benchlegs.minres_leg(env, A, B, BTm, pA, pM, dA, dM, f_d, g_d, u_start, P, n_u, n_p, nnzA, nnzB, peak,
-                                           spmv_bytes, MINRES_VEC_PASSES)
-    if P is not None:
-        P.local.A = P.local.B = P.local.BT = None
-        torch.cuda.empty_cache()
-
-    # ---- time to tolerance (the reference's call: tol 1e-10 relative), every N; the solution's fingerprint
-    ttt = None
-    if args.solve_to_tol > 0:
-        tsol = u_start.clone()
-        barrier()
-        t0 = time.perf_counter()
-        try:   # an extra leg after the timed ones: a failure here is reported, it does not take the headline line down
-            with quiet():
-                it_t, secs_t = nsb.BramblePasciakCG(A, B, None, f_d, g_d, pA, pM, tsol, tol=args.solve_to_tol, maxsteps=args.solve_maxsteps,
-                                                    printrates=False, initialize=False, rel_err=True, lam_min=lam_min)
-            barrier()
-            info = dict(nsb.solvers.last_info)
-            th = info["history"]
-            ttt = {"tol": args.solve_to_tol, "rel_err": True, "preA": "Jacobi", "iterations": int(info["updates"]), "loop_seconds": secs_t,
-                   "call_seconds": time.perf_counter() - t0, "status": info["status"],
-                   "final_relative_error": float(th[-1] / th[0]) if th[0] > 0 else None,
-                   "solution_fingerprint": benchlegs.fingerprint(env, tsol, n_u_loc, space_u, space_p, n_u, n_p)}
-        except Exception as ex:   # noqa: BLE001  (NsbError or a CUDA error surfaced by torch)
-            ttt = {"tol": args.solve_to_tol, "error": str(ex)[:200]}
-        del tsol
-
-    # ---- Gram-Schmidt (orthonormalization.py) at the bench's vector length
-    gs_info = None
-    if not args.no_gs:
-        gs_info = benchlegs.guarded(benchlegs.gram_schmidt_leg, env, n_u_loc + int(g_d.numel()), n_u + n_p, peak, GS_BYTES_PER_ROW)
-
-    # ---- the operators of the headline are no longer needed: free them before the legs that assemble their own
-    del A, B, BT, BTm, pA, pM, sol_d
-    if P is not None:
-        P.A = P.B = P.BT = None
-    P = None
-    torch.cuda.empty_cache()
-
-    # ---- SIMPLE time step (DoTimeStep / Project, NavierStokesSIMPLE_iterative.py:427-443) on the same mesh, every N
-    simple_info = None
-    if not args.no_simple:
-        simple_info = benchlegs.guarded(benchlegs.simple_step_leg, env, peak, spmv_bytes, CG_VEC_PASSES)
-
-    # ---- weak scaling beside the strong-scaling headline: --weak-dofs unknowns PER GPU (N > 1)
-    weak_info = None
-    if world > 1 and args.weak:
-        weak_info = benchlegs.guarded(benchlegs.weak_scaling_leg, env, args.weak_dofs, args.iters, peak, bpcg_iter_bytes)
-
-    # ---- parity where the driver can see it
-    parity = None
-    if not args.no_parity:
-        if world == 1:
-            parity = benchlegs.guarded(benchlegs.parity_at_sample, env, assemble_host, cpu_bpcg)
-        else:
-            parity = benchlegs.guarded(benchlegs.parity_vs_single, env)
-
-    cpu_line = None
-    if host is not None and rank == 0:
-        from oracle import krylov_oracle as ko
-        best, nt = None, None
-        for _ in range(3):
-            _, _, loop_s, _, nt = cpu_bpcg(host, k_scale, 20)
-            best = loop_s if best is None or loop_s < best else best
-        cpu_line = {"value": 20 / best, "unit": "iterations/s", "cores": nt, "kind": "port",
-                    "sample": "C+OpenMP oracle port of bramblepasciak_new.py (oracle/c/krylov_omp.c), 20 iterations on the SAME "
-                              "%d-dof blocks the device solves (no dof scaling), best of 3, %d threads set explicitly" % (n_u + n_p, nt)}
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
     # DRAM bytes per launch of the same kernel from a committed ncu --set full capture (never measured under this run); used only
     # when the capture was taken on the same storage format (fingerprint), else null -- the by-construction stream bytes stand in
     traffic, traffic_src = None, None
@@ -556,23 +541,97 @@ def main():
                    "host_clock_ms_per_step": 1e3 * wall_check.get("device", 0.0) / args.steps,
                    "host_clock_ms_per_step_e2e": 1e3 * wall_check.get("e2e", 0.0) / args.steps},
     }
-    if minres_info:
-        line["minres"] = minres_info
-    if ttt:
+    # The headline line is complete here.  Every leg below is optional, adds its key when it returns, and is bounded by the
+    # watchdog: an asymmetric failure in one of them (one rank out of memory, the others waiting in a collective) costs that leg,
+    # not the line.
+    wd = LegWatchdog(args.leg_timeout, rank, line)
+
+    # ---- MINRES on the merged saddle-point operator K = [[A, B^T], [B, 0]] (minres.py; BASELINE metric names both), every N
+    if not args.no_minres:
+        with wd.leg("minres"):
+            minres_info = benchlegs.minres_leg(env, A, B, BTm, pA, pM, dA, dM, f_d, g_d, u_start, P, n_u, n_p, nnzA, nnzB, peak,
+                                               spmv_bytes, MINRES_VEC_PASSES)
+        if minres_info:
+            line["minres"] = minres_info
+    if P is not None:
+        P.local.A = P.local.B = P.local.BT = None
+        torch.cuda.empty_cache()
+
+    # ---- time to tolerance (the reference's call: tol 1e-10 relative), every N; the solution's fingerprint
+    if args.solve_to_tol > 0:
+        tsol = u_start.clone()
+        with wd.leg("time_to_tolerance"):
+            barrier()
+            t0 = time.perf_counter()
+            try:   # an extra leg after the timed ones: a failure here is reported, it does not take the headline line down
+                with quiet():
+                    it_t, secs_t = nsb.BramblePasciakCG(A, B, None, f_d, g_d, pA, pM, tsol, tol=args.solve_to_tol,
+                                                        maxsteps=args.solve_maxsteps, printrates=False, initialize=False, rel_err=True,
+                                                        lam_min=lam_min)
+                barrier()
+                info = dict(nsb.solvers.last_info)
+                th = info["history"]
+                ttt = {"tol": args.solve_to_tol, "rel_err": True, "preA": "Jacobi", "iterations": int(info["updates"]),
+                       "loop_seconds": secs_t, "call_seconds": time.perf_counter() - t0, "status": info["status"],
+                       "final_relative_error": float(th[-1] / th[0]) if th[0] > 0 else None,
+                       "solution_fingerprint": benchlegs.fingerprint(env, tsol, n_u_loc, space_u, space_p, n_u, n_p)}
+            except Exception as ex:   # noqa: BLE001  (NsbError or a CUDA error surfaced by torch)
+                ttt = {"tol": args.solve_to_tol, "error": str(ex)[:200]}
         line["time_to_tolerance"] = ttt
-    if gs_info:
-        line["gram_schmidt"] = gs_info
-    if simple_info:
-        line["simple_step"] = simple_info
-    if weak_info:
-        line["weak_scaling"] = weak_info
-    if parity:
-        line["parity_at_sample" if world == 1 else "parity_vs_single"] = parity
-    if cpu_line:
-        line["cpu_baseline"] = cpu_line
-    print(json.dumps(line))
+        del tsol
+
+    # ---- Gram-Schmidt (orthonormalization.py) at the bench's vector length
+    if not args.no_gs:
+        with wd.leg("gram_schmidt"):
+            gs_info = benchlegs.guarded(benchlegs.gram_schmidt_leg, env, n_u_loc + int(g_d.numel()), n_u + n_p, peak, GS_BYTES_PER_ROW)
+        if gs_info:
+            line["gram_schmidt"] = gs_info
+
+    # ---- the operators of the headline are no longer needed: free them before the legs that assemble their own
+    del A, B, BT, BTm, pA, pM, sol_d
+    if P is not None:
+        P.A = P.B = P.BT = None
+    P = None
+    torch.cuda.empty_cache()
+
+    # ---- SIMPLE time step (DoTimeStep / Project, NavierStokesSIMPLE_iterative.py:427-443) on the same mesh, every N
+    if not args.no_simple:
+        with wd.leg("simple_step"):
+            simple_info = benchlegs.guarded(benchlegs.simple_step_leg, env, peak, spmv_bytes, CG_VEC_PASSES)
+        if simple_info:
+            line["simple_step"] = simple_info
+
+    # ---- weak scaling beside the strong-scaling headline: --weak-dofs unknowns PER GPU (N > 1)
+    if world > 1 and args.weak:
+        with wd.leg("weak_scaling"):
+            weak_info = benchlegs.guarded(benchlegs.weak_scaling_leg, env, args.weak_dofs, args.iters, peak, bpcg_iter_bytes)
+        if weak_info:
+            line["weak_scaling"] = weak_info
+
+    # ---- parity where the driver can see it
+    if not args.no_parity:
+        with wd.leg("parity"):
+            if world == 1:
+                parity = benchlegs.guarded(benchlegs.parity_at_sample, env, assemble_host, cpu_bpcg)
+            else:
+                parity = benchlegs.guarded(benchlegs.parity_vs_single, env)
+        if parity:
+            line["parity_at_sample" if world == 1 else "parity_vs_single"] = parity
+
+    if host is not None and rank == 0:
+        from oracle import krylov_oracle as ko   # noqa: F401  (builds / loads the C oracle before the timed CPU runs)
+        best, nt = None, None
+        for _ in range(3):
+            _, _, loop_s, _, nt = cpu_bpcg(host, k_scale, 20)
+            best = loop_s if best is None or loop_s < best else best
+        line["cpu_baseline"] = {"value": 20 / best, "unit": "iterations/s", "cores": nt, "kind": "port",
+                                "sample": "C+OpenMP oracle port of bramblepasciak_new.py (oracle/c/krylov_omp.c), 20 iterations on the SAME "
+                                          "%d-dof blocks the device solves (no dof scaling), best of 3, %d threads set explicitly"
+                                          % (n_u + n_p, nt)}
+    wd.emit()
     if world > 1:
-        dist.destroy_process_group()
+        with wd.leg("teardown"):
+            dist.destroy_process_group()
 
 
 def _shape_nnz(r, c, z, world):
