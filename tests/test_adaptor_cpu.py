@@ -12,7 +12,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 class FakeNgsMatrix:
     def __init__(self, m):
-        self.m = m.tocsr()
+        self.m = m.tocsr().copy()
+        self.m.sort_indices()                # NGSolve rows are sorted by column
         self.height, self.width = self.m.shape
 
     def CSR(self):                       # NGSolve order: values, columns, row pointers

@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_dist.py -m gpu -x -q 2>&1 | tail -4
 T="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N"
 timeout 600 $T --steps 5 --warmup 3 > gpurun_out/r2l_bench$N.json 2> gpurun_out/r2l_bench$N.err; echo "bench rc=$?"; tail -3 gpurun_out/r2l_bench$N.err | cut -c1-400
-NSB_HALO_FUSED=0 timeout 300 $T --steps 2 --warmup 3 --no-parity --no-simple --no-gs --solve-to-tol 0 --no-cpu-baseline --no-weak > gpurun_out/r2l_n${N}_nohalofused.json 2> gpurun_out/r2l_n${N}_nohalofused.err
+NSB_HALO_FUSED=0 timeout 300 $T --steps 2 --warmup 3 --no-parity --no-simple --no-gs --solve-to-tol 0 --no-cpu-baseline > gpurun_out/r2l_n${N}_nohalofused.json 2> gpurun_out/r2l_n${N}_nohalofused.err
 python - <<PY
 import json
 d=json.loads(open("gpurun_out/r2l_bench$N.json").read().strip().splitlines()[-1])
