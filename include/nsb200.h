@@ -177,7 +177,11 @@ NSB_API int nsb_bpcg(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_pre preA
 /* Statically condensed velocity operator of BramblePasciakCG (blfA.condense == True, bramblepasciak_new.py:8-21,84-103):
  *   matA = (I - HT)(A + inner_matrix)(I - H)     with A = blfA.mat (the condensed matrix), H = blfA.harmonic_extension,
  *   HT = blfA.harmonic_extension_trans, inner_solve = blfA.inner_solve, inner_matrix = blfA.inner_matrix, all exported as
- *   CSR of the full velocity size.  The handle borrows the five operators (they must outlive it).  Single GPU. */
+ *   CSR of the full velocity size.  The handle borrows the five operators (they must outlive it).
+ *   Row-partitioned context: each operator holds this rank's rows with columns numbered [owned | halo] over ONE velocity halo
+ *   plan (nsb_mat_set_halo with the same nsb_halo on each; B of nsb_bpcg_condensed shares it); an operator that references owned
+ *   columns only (element-local inner_solve / inner_matrix) may come with n_owned columns and no plan.  The chains exchange the
+ *   halo of every SpMV input themselves.  (Row-partitioned use has not run on a device yet: DESIGN.md 7.) */
 NSB_API int nsb_cond_create(nsb_ctx ctx, nsb_mat A, nsb_mat H, nsb_mat HT, nsb_mat inner_solve, nsb_mat inner_matrix, nsb_cond* out);
 NSB_API int nsb_cond_destroy(nsb_cond k);
 /* y = matA x  (myAmatrix.Mult, bramblepasciak_new.py:90-91) */

@@ -296,20 +296,23 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     const double* dA = general_pre ? nullptr : preA->d.p;
     if (preM) NSB_REQUIRE(preM->kind == 0, "nsb_bpcg: preM must be diagonal");
     const double* dM = preM ? preM->d.p : nullptr;
-    if (K) NSB_REQUIRE(c.nranks == 1 && mode == 2, "nsb_bpcg_condensed: single-GPU, v2 semantics only");
+    if (K) NSB_REQUIRE(mode == 2, "nsb_bpcg_condensed: v2 semantics only");
     if (K) NSB_REQUIRE(!general_pre, "nsb_bpcg_condensed: diagonal preA_unscaled only");
+    if (K) NSB_REQUIRE(K->n == n_u && K->nx == nxu, "nsb_bpcg_condensed: operator and B disagree on the velocity vector (%lld | %lld entries "
+                       "against %lld | %lld): row-partitioned, all velocity-column operators share one halo plan",
+                       (long long)K->n, (long long)K->nx, (long long)n_u, (long long)nxu);
     if (general_pre) NSB_REQUIRE(c.nranks == 1, "nsb_bpcg: block smoothers are single-GPU");
-    DevBuf<double> cr, cy;   // scratch of the condensed preconditioner chain
+    DevBuf<double> cr, cy;   // scratch of the condensed preconditioner chain (SpMV inputs: owned + halo entries)
     if (K) {
-        NSB_CHECK(cr.allocs(c, n_u));
-        NSB_CHECK(cy.allocs(c, n_u));
+        NSB_CHECK(cr.allocs(c, nxu));
+        NSB_CHECK(cy.allocs(c, nxu));
     }
     // matA x -> y and preA x -> y (k * preA_unscaled, extended harmonically when condensed: :8-21,:84-103,:122)
     auto applyA = [&](double* x, double* y) -> int {
         if (K) return cond_apply_A<0>(c, K, x, PlainRowOp{y});
         return apply(c, A, x, y);
     };
-    auto applyPre = [&](const double* x, double* y) -> int {
+    auto applyPre = [&](double* x, double* y) -> int {   // condensed and row-partitioned: x's halo tail is filled (x holds nxu entries)
         if (K) return cond_apply_pre(c, K, x, dA, k_scale, cr.p, cy.p, y);
         if (general_pre) {
             NSB_CHECK(pre_apply_device(c, preA, x, y));
@@ -320,8 +323,8 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
 
     DevBuf<double> u0, u1, d0, d1, w0, w1, s0, s1, z0, As0, tmp0, tmp1, tmp2, tmp3, tmp4, df, dg, fnew, gnew, hist;
     DevBuf<BpcgState> st;
-    for (DevBuf<double>* b : {&u0, &s0, &tmp0, &tmp1, &tmp4}) NSB_CHECK(b->allocs(c, nxu));
-    for (DevBuf<double>* b : {&d0, &w0, &z0, &As0, &tmp2, &df, &fnew}) NSB_CHECK(b->allocs(c, n_u));
+    for (DevBuf<double>* b : {&u0, &s0, &tmp0, &tmp1, &tmp4, &df}) NSB_CHECK(b->allocs(c, nxu));   // (df: SpMV input of the condensed chain)
+    for (DevBuf<double>* b : {&d0, &w0, &z0, &As0, &tmp2, &fnew}) NSB_CHECK(b->allocs(c, n_u));
     for (DevBuf<double>* b : {&u1, &s1}) NSB_CHECK(b->allocs(c, nxp));
     for (DevBuf<double>* b : {&d1, &w1, &tmp3, &dg, &gnew}) NSB_CHECK(b->allocs(c, n_p > 0 ? n_p : 1));
     NSB_CHECK(hist.allocs(c, maxsteps + 2));
@@ -480,9 +483,20 @@ extern "C" int nsb_cond_create(nsb_ctx ctx, nsb_mat A, nsb_mat H, nsb_mat HT, ns
                                nsb_cond* out) {
     NSB_REQUIRE(ctx && A && H && HT && inner_solve && inner_matrix && out, "nsb_cond_create: NULL argument");
     const int64_t n = A->rows;
+    // One GPU: five square operators.  Row-partitioned: this rank's rows of each, columns numbered [owned | halo] over ONE velocity
+    // halo plan (an operator that references owned columns only may come without a plan and with n columns).
+    nsb_halo_s* plan = nullptr;
     for (nsb_mat m : {A, H, HT, inner_solve, inner_matrix})
-        NSB_REQUIRE(m->rows == n && m->cols == n && m->halo == nullptr,
-                    "nsb_cond_create: all five operators must be square of the same size and not row-partitioned");
+        if (m->halo) {
+            NSB_REQUIRE(plan == nullptr || plan == m->halo, "nsb_cond_create: the row-partitioned operators must share one halo plan");
+            plan = m->halo;
+        }
+    const int64_t nx = plan ? plan->n_owned + plan->n_halo : n;
+    if (plan) NSB_REQUIRE(plan->n_owned == n, "nsb_cond_create: the halo plan owns %lld entries, the operators have %lld rows",
+                          (long long)plan->n_owned, (long long)n);
+    for (nsb_mat m : {A, H, HT, inner_solve, inner_matrix})
+        NSB_REQUIRE(m->rows == n && m->cols == (m->halo ? nx : n),
+                    "nsb_cond_create: all five operators must have the same rows and be square (owned + halo columns when row-partitioned)");
     nsb_cond_s* K = new nsb_cond_s();
     K->ctx = &ctx->c;
     K->A = A;
@@ -491,8 +505,9 @@ extern "C" int nsb_cond_create(nsb_ctx ctx, nsb_mat A, nsb_mat H, nsb_mat HT, ns
     K->inner_solve = inner_solve;
     K->inner_matrix = inner_matrix;
     K->n = n;
-    int r = K->t.alloc(n);
-    if (r == NSB_OK) r = K->q.alloc(n);
+    K->nx = nx;
+    int r = K->t.alloc(nx);
+    if (r == NSB_OK) r = K->q.alloc(nx);
     if (r != NSB_OK) {
         delete K;
         return r;
@@ -511,7 +526,7 @@ extern "C" int nsb_cond_apply(nsb_ctx ctx, nsb_cond k, const double* x, double* 
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
     DevBuf<double> dx, dy;
-    NSB_CHECK(dx.allocs(c, k->n));
+    NSB_CHECK(dx.allocs(c, k->nx));
     NSB_CHECK(dy.allocs(c, k->n));
     NSB_CHECK(copy_in(c, dx.p, x, k->n));
     NSB_CHECK(cond_apply_A<0>(c, k, dx.p, PlainRowOp{dy.p}));

@@ -192,7 +192,7 @@ static int cg_run(Context& c, nsb_mat_s* A, nsb_pre_s* pre, CgBuffers& b, bool w
     };
     auto launch_iteration = [&]() -> int {
         const CgC1Op c1{S, b.q.p, b.s.p, alphas, red};
-        if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, c1)));   // condensed: single-GPU
+        if (K) NSB_CHECK((cond_apply_A<1>(c, K, b.s.p, c1)));   // condensed: the chain exchanges its own inputs (cond.cuh)
         else if (push_s.nruns > 0) NSB_CHECK(spmv_launch_halo_in<1>(c, A, b.s.p, c1, 0));
         else NSB_CHECK(spmv_exchange_launch<1>(c, A, b.s.p, c1));
         NSB_CHECK(reduce_unfused(&S->red[0], 0));

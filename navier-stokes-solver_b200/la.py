@@ -394,7 +394,8 @@ class SparseMatrix(BaseMatrix):
 
 class CondensedOperator(BaseMatrix):
     """matA = (I - HT)(A + inner_matrix)(I - H) of a statically condensed BilinearForm
-    (myAmatrix, solvers/bramblepasciak_new.py:84-103).  Holds references to the five device matrices."""
+    (myAmatrix, solvers/bramblepasciak_new.py:84-103).  Holds references to the five device matrices.  Row-partitioned: this
+    rank's rows of each, over one shared velocity halo plan (partition.build_distributed_condensed)."""
 
     def __init__(self, mat, harmonic_extension, harmonic_extension_trans, inner_solve, inner_matrix):
         parts = (mat, harmonic_extension, harmonic_extension_trans, inner_solve, inner_matrix)
@@ -424,8 +425,8 @@ class CondensedOperator(BaseMatrix):
 
     def __mul__(self, v):
         px, nx, keep = buffer_of(v)
-        if nx != self.width:
-            raise ValueError("vector length %d != %d" % (nx, self.width))
+        if nx != self.height:      # row-partitioned: the owned entries; the chain exchanges the halo itself (csrc/cond.cuh)
+            raise ValueError("vector length %d != %d" % (nx, self.height))
         out = keep.new_empty(self.height) if _is_torch(keep) else np.empty(self.height)
         py, _, _ = buffer_of(out)
         _lib.check(self.ctx._lib.nsb_cond_apply(self.ctx.h, self.h, px, py), "nsb_cond_apply")

@@ -310,6 +310,136 @@ def local_saddle(L: LocalStokes):
 
 
 # ------------------------------------------------------------------------------------------------
+# any set of operators over one column index space (the statically condensed velocity operator: A, harmonic_extension,
+# harmonic_extension_trans, inner_solve, inner_matrix -- solvers/bramblepasciak_new.py:8-21,84-103 -- and B beside them)
+# ------------------------------------------------------------------------------------------------
+def _as_csr(op, device):
+    """synthetic.CSR (torch) of a synthetic.CSR or a scipy sparse matrix."""
+    import navier_stokes_solver_b200.synthetic as syn
+    if isinstance(op, syn.CSR):
+        return op
+    m = op.tocsr()
+    m.sort_indices()
+    return syn.CSR(tuple(m.shape), torch.as_tensor(m.indptr.astype(np.int64), device=device),
+                   torch.as_tensor(m.indices.astype(np.int32), device=device), torch.as_tensor(m.data.astype(np.float64), device=device))
+
+
+def take_rows(csr, row_ids: torch.Tensor):
+    """Rows ``row_ids`` (int64, any order) of a CSR, in that order, column ids unchanged."""
+    import navier_stokes_solver_b200.synthetic as syn
+    row_ids = row_ids.to(torch.int64)
+    start = csr.rowptr[row_ids]
+    cnt = csr.rowptr[row_ids + 1] - start
+    rowptr = torch.zeros(row_ids.numel() + 1, dtype=torch.int64, device=csr.rowptr.device)
+    rowptr[1:] = torch.cumsum(cnt, 0)
+    total = int(rowptr[-1])
+    # position p of the output belongs to output row k = searchsorted(rowptr, p, right) - 1 and is entry start[k] + (p - rowptr[k])
+    p = torch.arange(total, dtype=torch.int64, device=csr.rowptr.device)
+    k = torch.repeat_interleave(torch.arange(row_ids.numel(), dtype=torch.int64, device=p.device), cnt)
+    src = start[k] + (p - rowptr[k])
+    return syn.CSR((int(row_ids.numel()), csr.shape[1]), rowptr, csr.colidx[src], csr.values[src])
+
+
+@dataclass
+class LocalOperators:
+    """One rank's rows of several operators that share a column index space, renumbered over ONE halo plan."""
+    plan: Plan
+    ops: list            # synthetic.CSR, columns in [owned | halo] numbering; a compact operator has only the owned columns
+    touches_halo: list   # per operator: some owned row references an off-rank column (then the plan must be attached to it)
+
+    @property
+    def nx(self):
+        return self.plan.n_owned + self.plan.n_halo
+
+
+def distribute_operators(ops, row_spaces, col_space: IndexSpace, rank: int, group=None, compact=None, plan=None) -> LocalOperators:
+    """Row partition of operators over one column space with ONE shared halo plan: every vector of that space is then exchanged
+    the same way whichever operator reads it (csrc/cond.cuh applies five of them in a chain).
+
+    ops         global operators (synthetic.CSR with global column ids, or scipy sparse), or already this rank's rows of them
+                (row count == row_spaces[k].n_owned(rank))
+    row_spaces  the IndexSpace of each operator's rows (the velocity space for A, H, ...; the pressure space for B)
+    compact     per operator: True = must reference owned columns only (element-local inner_solve / inner_matrix with elements kept
+                inside a slab); it is returned with n_owned columns, gets no plan, and its input needs no exchange.  ValueError if
+                it does touch another rank's columns.
+    Collective over ``group`` (one make_plan) unless ``plan`` is given."""
+    import navier_stokes_solver_b200.synthetic as syn
+    compact = list(compact) if compact is not None else [False] * len(ops)
+    dev = None
+    for op in ops:
+        if isinstance(op, syn.CSR):
+            dev = op.values.device
+            break
+    dev = dev if dev is not None else torch.device("cpu")
+    mine = []
+    for op, rs in zip(ops, row_spaces):
+        csr = _as_csr(op, dev)
+        if csr.shape[0] == rs.n_owned(rank) and csr.shape[0] != rs.n_global():
+            mine.append(csr)
+        else:
+            if csr.shape[0] != rs.n_global():
+                raise ValueError("distribute_operators: operator has %d rows, its row space %d (owned here: %d)"
+                                 % (csr.shape[0], rs.n_global(), rs.n_owned(rank)))
+            mine.append(take_rows(csr, rs.owned_ids(rank, device=csr.rowptr.device)))
+    if plan is None:
+        cols = [m.colidx.to(torch.int64) for m, cp in zip(mine, compact) if not cp]
+        needed = torch.cat(cols) if cols else torch.zeros(0, dtype=torch.int64, device=dev)
+        plan = make_plan(col_space, rank, needed, group)
+    nx = plan.n_owned + plan.n_halo
+    out, touches = [], []
+    for k, (m, cp) in enumerate(zip(mine, compact)):
+        owner, _ = col_space.lookup(m.colidx.to(torch.int64)) if m.colidx.numel() else (torch.zeros(0, dtype=torch.int64), None)
+        off = bool((owner != rank).any()) if m.colidx.numel() else False
+        if cp and off:
+            raise ValueError("distribute_operators: operator %d is declared compact (element-local) but its rows on rank %d reference "
+                             "columns owned elsewhere" % (k, rank))
+        if cp:
+            _, loc = col_space.lookup(m.colidx.to(torch.int64)) if m.colidx.numel() else (None, torch.zeros(0, dtype=torch.int64))
+            out.append(syn.CSR((m.shape[0], plan.n_owned), m.rowptr, loc.to(torch.int32), m.values))
+        else:
+            out.append(syn.CSR((m.shape[0], nx), m.rowptr, plan.localize(col_space, m.colidx), m.values))
+        touches.append(off)
+    return LocalOperators(plan, out, touches)
+
+
+@dataclass
+class DistributedCondensed:
+    """Device side of a row-partitioned statically condensed form: an object with the attributes of a condensed BilinearForm
+    (what solvers.BramblePasciakCG / la.CondensedOperator.from_bilinear_form read) plus B, B^T and the plans that keep them alive."""
+    mat: object
+    harmonic_extension: object
+    harmonic_extension_trans: object
+    inner_solve: object
+    inner_matrix: object
+    B: object
+    BT: object
+    plan_u: Plan
+    plan_p: Plan
+    halos: tuple = ()
+    condense: bool = True
+
+
+def build_distributed_condensed(ctx, rank, space_u: IndexSpace, space_p: IndexSpace, mat, H, HT, inner_solve, inner_matrix, B, BT,
+                                group=None, inner_is_local=True) -> DistributedCondensed:
+    """Upload this rank's rows of the five operators of a condensed velocity form and of B / B^T, with one velocity halo plan shared by
+    everything that reads a velocity vector and one pressure plan for B^T.  Collective (two make_plan calls + the plans' device set-up).
+    ``inner_is_local``: inner_solve / inner_matrix couple dofs of one element only and elements are not split across ranks."""
+    from .la import SparseMatrix
+    Lu = distribute_operators([mat, H, HT, inner_solve, inner_matrix, B], [space_u] * 5 + [space_p], space_u, rank, group,
+                              compact=[False, False, False, inner_is_local, inner_is_local, False])
+    Lp = distribute_operators([BT], [space_u], space_p, rank, group)
+    hu, hp = upload_halo(ctx, Lu.plan), upload_halo(ctx, Lp.plan)
+    dev = [SparseMatrix.from_csr(m, ctx) for m in Lu.ops]
+    for m, cp in zip(dev, [False, False, False, inner_is_local, inner_is_local, False]):
+        if not cp:
+            hu.attach(m)
+    dBT = SparseMatrix.from_csr(Lp.ops[0], ctx)
+    hp.attach(dBT)
+    dev[5].set_transpose(dBT)
+    return DistributedCondensed(dev[0], dev[1], dev[2], dev[3], dev[4], dev[5], dBT, Lu.plan, Lp.plan, (hu, hp))
+
+
+# ------------------------------------------------------------------------------------------------
 # device upload (needs libnsb200 + a row-partitioned Context)
 # ------------------------------------------------------------------------------------------------
 @dataclass
