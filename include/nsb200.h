@@ -130,14 +130,18 @@ NSB_API int nsb_pre_create_diag(nsb_ctx ctx, int64_t n, const double* d, nsb_pre
 NSB_API int nsb_pre_create_jacobi(nsb_ctx ctx, nsb_mat m, const uint8_t* free_mask, nsb_pre* out);
 /* BlockMatrix([[preA, None], [None, preS]]) (run.py:46).  Two diagonal preconditioners are merged into one diagonal; with a
  * block smoother / auxiliary-space composite in either block the result applies them block by block and borrows the two handles
- * (they must outlive it; single-GPU contexts). */
+ * (they must outlive it). */
 NSB_API int nsb_pre_create_blockdiag2(nsb_ctx ctx, nsb_pre a, nsb_pre b, nsb_pre* out);
 /* Block smoother: a.mat.CreateBlockSmoother(blocks) with the facet blocks of NavierStokesSIMPLE_iterative.py:360-373.
  * Disjoint dof blocks (at most 64 dofs each) in CSR-like form, listed colour by colour: blocks [color_ptr[c], color_ptr[c+1])
  * are mutually uncoupled through A, so one colour is one parallel launch and a sweep equals the sequential block
  * Gauss-Seidel sweep in the given block order.  ncolors == 0: additive use only.  As a preconditioner (nsb_pre_apply,
  * nsb_bpcg preA, nsb_cg pre) the handle acts as  jacobi * x  (gauss_seidel == 0; MypreA with GS = False without the
- * auxiliary-space term, :383)  or as  y = 0; Smooth(y, x); SmoothBack(y, x)  (gauss_seidel != 0; :375-381). */
+ * auxiliary-space term, :383)  or as  y = 0; Smooth(y, x); SmoothBack(y, x)  (gauss_seidel != 0; :375-381).
+ * Row-partitioned context: A holds this rank's rows (columns [owned | halo]); the blocks list owned dofs only (local numbering; a
+ * block is never cut by the partition) under a colouring of the GLOBAL block graph -- every rank passes the same ncolors, a colour
+ * may be empty on a rank -- and a sweep exchanges the iterate's halo before every colour, which makes it the sequential sweep in the
+ * global colour-major order.  (Row-partitioned use of the smoother and of the composite below has not run on a device: DESIGN.md 7.) */
 NSB_API int nsb_pre_create_blocks(nsb_ctx ctx, nsb_mat A, int64_t nblocks, const int64_t* block_ptr, const int32_t* block_dofs,
                                   int ncolors, const int64_t* color_ptr, int gauss_seidel, nsb_pre* out);
 /* jacobi.Smooth(y, x) (backward == 0) / jacobi.SmoothBack(y, x) (backward != 0): one block Gauss-Seidel sweep on y for the
@@ -149,7 +153,10 @@ NSB_API int nsb_pre_smooth(nsb_ctx ctx, nsb_pre p, const double* x, double* y, i
  * smoother: a handle from nsb_pre_create_blocks on A (its matrix is the A of the residual); transform (n x n_c) and its
  * explicit transpose as device matrices; coarse: any preconditioner handle of size n_c (the reference puts component-wise
  * h1amg there, which is NGSolve-internal; a Jacobi or block smoother of the H1 matrix, or another composite, goes here).
- * The handles passed in are not owned and must outlive the result. */
+ * The handles passed in are not owned and must outlive the result.
+ * Row-partitioned context: transform = this rank's velocity rows with columns over a halo plan of the auxiliary space, transform_t =
+ * this rank's auxiliary rows of the global transpose with columns over a halo plan of the velocity space, coarse of the owned
+ * auxiliary size; the composite exchanges the input of each of its SpMVs. */
 NSB_API int nsb_pre_create_auxspace(nsb_ctx ctx, nsb_pre smoother, nsb_mat transform, nsb_mat transform_t, nsb_pre coarse,
                                     int gauss_seidel, nsb_pre* out);
 NSB_API int nsb_pre_destroy(nsb_pre p);

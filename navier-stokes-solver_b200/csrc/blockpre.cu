@@ -6,6 +6,12 @@
 // Blocks are disjoint dof lists (the facet blocks of :360-362), handed over colour by colour: blocks of one
 // colour are not coupled through A, so a colour is one parallel launch and the sweep equals the sequential
 // sweep in that block order.  Dense inverses are computed once on the device (Gauss-Jordan in shared memory).
+// Row-partitioned: the smoother belongs to this rank's rows of A (columns [owned | halo]); blocks list OWNED dofs
+// only (a block is never cut by the partition) under a colouring of the GLOBAL block graph, every rank passing all colours (some may
+// be empty on a rank).  Block Jacobi is then purely local.  A Gauss-Seidel sweep reads y at halo columns in its residual rows, so it
+// runs on a copy of y with a halo tail that is exchanged before every colour -- the values the neighbours wrote in the colours before
+// -- which is the sequential sweep in the global colour-major block order.  The auxiliary-space composite exchanges the input of each
+// of its SpMVs (smoother matrix, transform^T over the velocity space, transform over the auxiliary space) the same way.
 #include "cond.cuh"
 
 namespace nsb {
@@ -104,15 +110,24 @@ static int block_jacobi(Context& c, nsb_pre_s* p, const double* x, double* y) {
 
 // jacobi.Smooth(y, x) / jacobi.SmoothBack(y, x): colours ascending / descending
 int block_gs_sweep(Context& c, nsb_pre_s* p, const double* x, double* y, bool backward) {
+    nsb_halo_s* plan = p->mat->halo;
+    double* yy = y;
+    if (plan) {   // row-partitioned: sweep on a copy of y that has a halo tail (y itself holds the owned entries only)
+        NSB_CHECK(vec_lincomb(c, p->ybuf.p, 1.0, y, 0, nullptr, 0, nullptr, p->n));
+        yy = p->ybuf.p;
+    }
     for (int k = 0; k < p->ncolors; ++k) {
         const int col = backward ? p->ncolors - 1 - k : k;
         const int64_t b0 = p->color_ptr[col], b1 = p->color_ptr[col + 1];
+        // what the neighbours wrote in the colours before; every rank takes part, also one without blocks of this colour
+        if (plan) NSB_CHECK(halo_exchange(c, plan, yy));
         if (b1 <= b0) continue;
         k_block_apply<true><<<block_grid(c, b1 - b0), kBlock, 0, c.stream>>>(view_of(p->mat), p->block_ptr.p, p->block_dofs.p,
-                                                                            p->inv_ptr.p, p->inv.p, b0, b1, x, y);
+                                                                            p->inv_ptr.p, p->inv.p, b0, b1, x, yy);
         c.launches++;
     }
     NSB_CUDA(cudaGetLastError());
+    if (plan) NSB_CHECK(vec_lincomb(c, y, 1.0, yy, 0, nullptr, 0, nullptr, p->n));
     return NSB_OK;
 }
 
@@ -123,13 +138,25 @@ static int auxspace_apply(Context& c, nsb_pre_s* p, const double* x, double* y) 
     if (p->gs) {
         NSB_CHECK(vec_set(c, y, 0.0, p->n));                                                  // y[:] = 0
         NSB_CHECK(block_gs_sweep(c, sm, x, y, false));                                        // jacobi.Smooth(y, x)
-        NSB_CHECK(spmv_launch<0>(c, sm->mat, y, SubInOp{x, p->aux_t.p}));                     // temp = x - mat * y
+        const double* yin = y;
+        if (sm->mat->halo) {   // row-partitioned: mat * y reads y's halo tail
+            NSB_CHECK(vec_lincomb(c, sm->ybuf.p, 1.0, y, 0, nullptr, 0, nullptr, p->n));
+            NSB_CHECK(halo_exchange(c, sm->mat->halo, sm->ybuf.p));
+            yin = sm->ybuf.p;
+        }
+        NSB_CHECK(spmv_launch<0>(c, sm->mat, yin, SubInOp{x, p->aux_t.p}));                   // temp = x - mat * y
         coarse_in = p->aux_t.p;
     } else {
         NSB_CHECK(block_jacobi(c, sm, x, y));                                                 // jacobi * x
     }
+    if (p->transform_t->halo) {   // row-partitioned: transform.T reads the velocity halo of its input (aux_t has the tail)
+        if (coarse_in != p->aux_t.p) NSB_CHECK(vec_lincomb(c, p->aux_t.p, 1.0, x, 0, nullptr, 0, nullptr, p->n));
+        coarse_in = p->aux_t.p;
+        NSB_CHECK(halo_exchange(c, p->transform_t->halo, p->aux_t.p));
+    }
     NSB_CHECK(spmv_launch<0>(c, p->transform_t, coarse_in, PlainRowOp{p->aux_c.p}));          // transform.T * temp
     NSB_CHECK(pre_apply_device(c, p->coarse, p->aux_c.p, p->aux_z.p));                        // preAh1 * ..
+    NSB_CHECK(halo_exchange(c, p->transform->halo, p->aux_z.p));                              // (no-op on one GPU)
     NSB_CHECK(spmv_launch<0>(c, p->transform, p->aux_z.p, AddInOp{y, y}));                    // y += transform * ..
     if (p->gs) NSB_CHECK(block_gs_sweep(c, sm, x, y, true));                                  // jacobi.SmoothBack(y, x)
     return NSB_OK;
@@ -156,7 +183,8 @@ using namespace nsb;
 extern "C" int nsb_pre_create_blocks(nsb_ctx ctx, nsb_mat A, int64_t nblocks, const int64_t* block_ptr, const int32_t* block_dofs,
                                      int ncolors, const int64_t* color_ptr, int gauss_seidel, nsb_pre* out) {
     NSB_REQUIRE(ctx && A && out && block_ptr && nblocks >= 0, "nsb_pre_create_blocks: bad argument");
-    NSB_REQUIRE(A->rows == A->cols && A->halo == nullptr, "nsb_pre_create_blocks: square, not row-partitioned operator needed");
+    NSB_REQUIRE(A->halo ? (A->rows == A->halo->n_owned && A->cols == A->halo->n_owned + A->halo->n_halo) : A->rows == A->cols,
+                "nsb_pre_create_blocks: square operator needed (row-partitioned: owned rows, [owned | halo] columns)");
     NSB_REQUIRE(ncolors >= 0 && (ncolors == 0 || color_ptr), "nsb_pre_create_blocks: colour table missing");
     NSB_REQUIRE(!gauss_seidel || ncolors > 0, "nsb_pre_create_blocks: Gauss-Seidel sweeps need the colouring");
     Context& c = ctx->c;
@@ -189,6 +217,7 @@ extern "C" int nsb_pre_create_blocks(nsb_ctx ctx, nsb_mat A, int64_t nblocks, co
     if (r == NSB_OK) r = p->inv_ptr.alloc(nblocks + 1);
     if (r == NSB_OK) r = p->inv.alloc(iptr[nblocks] > 0 ? iptr[nblocks] : 1);
     if (r == NSB_OK) r = bad.alloc(1);
+    if (r == NSB_OK && A->halo) r = p->ybuf.alloc(A->cols);   // Gauss-Seidel sweeps of a row-partitioned smoother (block_gs_sweep)
     cudaError_t e = cudaSuccess;
     if (r == NSB_OK) {
         e = cudaMemcpy(p->block_ptr.p, block_ptr, sizeof(int64_t) * (nblocks + 1), cudaMemcpyDefault);
@@ -242,9 +271,12 @@ extern "C" int nsb_pre_create_auxspace(nsb_ctx ctx, nsb_pre smoother, nsb_mat tr
     NSB_REQUIRE(smoother->kind == 1, "nsb_pre_create_auxspace: the smoother must come from nsb_pre_create_blocks");
     NSB_REQUIRE(!gauss_seidel || smoother->ncolors > 0, "nsb_pre_create_auxspace: the multiplicative variant needs a coloured smoother");
     const int64_t n = smoother->n, nc = coarse->n;
-    NSB_REQUIRE(transform->rows == n && transform->cols == nc && transform_t->rows == nc && transform_t->cols == n,
+    // one GPU: transform is n x nc, transform_t nc x n.  Row-partitioned: the owned rows of each, transform's columns numbered over a
+    // halo plan of the auxiliary space (n_owned == nc), transform_t's over a halo plan of the velocity space (n_owned == n)
+    NSB_REQUIRE(transform->rows == n && transform_t->rows == nc &&
+                    (transform->halo ? transform->halo->n_owned == nc : transform->cols == nc) &&
+                    (transform_t->halo ? transform_t->halo->n_owned == n : transform_t->cols == n),
                 "nsb_pre_create_auxspace: transform must be %lld x %lld and transform_t its transpose", (long long)n, (long long)nc);
-    NSB_REQUIRE(!transform->halo && !transform_t->halo, "nsb_pre_create_auxspace: row-partitioned transforms are not supported");
     Context& c = ctx->c;
     NSB_CUDA(cudaSetDevice(c.device));
     nsb_pre_s* p = new nsb_pre_s();
@@ -256,9 +288,9 @@ extern "C" int nsb_pre_create_auxspace(nsb_ctx ctx, nsb_pre smoother, nsb_mat tr
     p->coarse = coarse;
     p->transform = transform;
     p->transform_t = transform_t;
-    int rc = p->aux_t.alloc(n);
+    int rc = p->aux_t.alloc(transform_t->cols > n ? transform_t->cols : n);   // SpMV input of transform_t: owned + halo entries
     if (rc == NSB_OK) rc = p->aux_c.alloc(nc);
-    if (rc == NSB_OK) rc = p->aux_z.alloc(nc);
+    if (rc == NSB_OK) rc = p->aux_z.alloc(transform->cols > nc ? transform->cols : nc);   // SpMV input of transform
     if (rc != NSB_OK) {
         delete p;
         return rc;

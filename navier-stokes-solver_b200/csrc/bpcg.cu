@@ -301,7 +301,6 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
     if (K) NSB_REQUIRE(K->n == n_u && K->nx == nxu, "nsb_bpcg_condensed: operator and B disagree on the velocity vector (%lld | %lld entries "
                        "against %lld | %lld): row-partitioned, all velocity-column operators share one halo plan",
                        (long long)K->n, (long long)K->nx, (long long)n_u, (long long)nxu);
-    if (general_pre) NSB_REQUIRE(c.nranks == 1, "nsb_bpcg: block smoothers are single-GPU");
     DevBuf<double> cr, cy;   // scratch of the condensed preconditioner chain (SpMV inputs: owned + halo entries)
     if (K) {
         NSB_CHECK(cr.allocs(c, nxu));
@@ -402,7 +401,10 @@ static int bpcg_core(nsb_ctx ctx, nsb_mat A, nsb_cond_s* K, nsb_mat B, nsb_mat B
             NSB_CHECK(applyPre(tmp0.p, tmp1.p));                                                   // :209
             NSB_CHECK(vec_lincomb(c, tmp4.p, 1.0, tmp1.p, -1.0, s0.p, 0, nullptr, n_u));           // :212
             if (K) NSB_CHECK((cond_apply_A<1>(c, K, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, rk})));   // :210,:218,:222
-            else NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, rk}));
+            else {
+                NSB_CHECK(halo_exchange(c, A->halo, tmp1.p));   // (no-op on one GPU)
+                NSB_CHECK(spmv_launch<1>(c, A, tmp1.p, BpcgB2Op{S, tmp2.p, tmp0.p, s0.p, rk}));
+            }
         } else {
             const BpcgB1Op b1{S, As0.p, z0.p, dA, s0.p, w0.p, tmp0.p, tmp1.p, tmp4.p, push_u};
             if (push_p.nruns > 0) NSB_CHECK(spmv_launch_halo_in<0>(c, BT, s1.p, b1, 0));      // s1 was pushed by b5 (or before the loop)

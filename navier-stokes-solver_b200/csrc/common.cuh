@@ -251,12 +251,13 @@ struct nsb_pre_s {
     nsb::DevBuf<int32_t> block_dofs;
     nsb::DevBuf<int64_t> inv_ptr;          // nblocks + 1, into inv (block b: size^2 entries, row-major)
     nsb::DevBuf<double> inv;
+    nsb::DevBuf<double> ybuf;              // row-partitioned smoother only: y with a halo tail (mat->cols entries) for the GS sweeps
     // kind 2: auxiliary-space preconditioner MypreA (:364-383) = block smoother + transform coarse transform^T.
     // Nothing below is owned.  gs selects the multiplicative (:375-381) or the additive (:383) variant.
     nsb_pre_s* smoother = nullptr;         // kind 1
     nsb_pre_s* coarse = nullptr;           // any kind, size = transform columns
     nsb_mat_s *transform = nullptr, *transform_t = nullptr;
-    nsb::DevBuf<double> aux_t, aux_c, aux_z;   // scratch: n, n_coarse, n_coarse
+    nsb::DevBuf<double> aux_t, aux_c, aux_z;   // scratch: n, n_coarse, n_coarse (aux_t / aux_z with a halo tail when row-partitioned)
     // kind 3: BlockMatrix([[blk0, None], [None, blk1]]) of two preconditioners of any kind (run.py:46), not owned
     nsb_pre_s *blk0 = nullptr, *blk1 = nullptr;
 };

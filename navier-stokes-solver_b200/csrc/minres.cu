@@ -251,11 +251,9 @@ extern "C" int nsb_minres(nsb_ctx ctx, nsb_mat K, nsb_pre pre, const double* rhs
     const int64_t nx = K->cols;                     // owned + halo
     NSB_REQUIRE(K->halo ? K->halo->n_owned == n : K->cols == K->rows, "nsb_minres: operator must be square");
     if (pre) NSB_REQUIRE(pre->n == n, "nsb_minres: preconditioner size %lld != %lld", (long long)pre->n, (long long)n);
-    const bool dist = c.nranks > 1;
     // pre: diagonal (fused into K2) or any other device preconditioner -- block smoother, auxiliary-space composite (run.py:61-62
     // and stokes_hcurldiv.py:48 configure non-Jacobi ones) -- applied by its own kernels between K2 and the gamma reduction
     const bool general_pre = pre != nullptr && pre->kind != 0;
-    if (general_pre) NSB_REQUIRE(!dist, "nsb_minres: block smoothers / composite preconditioners are single-GPU");
     const double* dinv = (pre && !general_pre) ? pre->d.p : nullptr;
 
     DevBuf<double> u, t, v[3], w[3], z[2], hist, drhs;

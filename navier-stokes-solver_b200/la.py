@@ -561,12 +561,25 @@ class BlockSmoother(BaseMatrix):
     object acts as ``jacobi * x`` (``gauss_seidel=False``, :383) or as ``y=0; Smooth(y,x); SmoothBack(y,x)``
     (``gauss_seidel=True``, MypreA.Mult :375-381 without the NGSolve-internal auxiliary-space term)."""
 
-    def __init__(self, mat, blocks, pattern=None, gauss_seidel=False):
+    def __init__(self, mat, blocks, pattern=None, gauss_seidel=False, color_ptr=None):
         if not isinstance(mat, SparseMatrix):
             raise TypeError("BlockSmoother needs a device SparseMatrix")
         self.ctx, self.mat, self.n = mat.ctx, mat, mat.height
-        blocks = [np.asarray(b, dtype=np.int32) for b in blocks if len(b) > 0]
-        if pattern is not None:
+        if color_ptr is not None:
+            # row-partitioned (partition.localize_blocks): this rank's blocks in LOCAL numbering, already colour-major under a
+            # colouring of the GLOBAL block graph; every rank passes every colour (possibly empty here), so no block is dropped
+            blocks = [np.asarray(b, dtype=np.int32) for b in blocks]
+            color_ptr = np.ascontiguousarray(color_ptr, dtype=np.int64)
+            if any(len(b) == 0 for b in blocks) or color_ptr[0] != 0 or color_ptr[-1] != len(blocks):
+                raise ValueError("BlockSmoother: colour table does not cover the (non-empty) blocks")
+        else:
+            if getattr(mat, "_halo", None) is not None:
+                raise ValueError("a row-partitioned BlockSmoother needs the global colouring: pass the blocks and color_ptr of "
+                                 "partition.localize_blocks")
+            blocks = [np.asarray(b, dtype=np.int32) for b in blocks if len(b) > 0]
+        if color_ptr is not None:
+            pass
+        elif pattern is not None:
             order, color_ptr = color_blocks(pattern, blocks)
             blocks = [blocks[i] for i in order]
         else:
@@ -639,6 +652,8 @@ class AuxiliarySpacePreconditioner(BaseMatrix):
             raise TypeError("the coarse preconditioner must be a device preconditioner (Jacobi, BlockSmoother, ...)")
         self.ctx, self.n = smoother.ctx, smoother.n
         self.smoother, self.transform, self.coarse = smoother, transform, coarse
+        if transform_t is None and getattr(transform, "_halo", None) is not None:
+            raise ValueError("row-partitioned: pass transform_t (this rank's rows of the global transpose, partition.distribute_operators)")
         self.transform_t = transform_t if transform_t is not None else transform.CreateTranspose()
         h = _lib.c_pre()
         _lib.check(self.ctx._lib.nsb_pre_create_auxspace(self.ctx.h, smoother.h, transform.h, self.transform_t.h, coarse.h,

@@ -402,6 +402,28 @@ def distribute_operators(ops, row_spaces, col_space: IndexSpace, rank: int, grou
     return LocalOperators(plan, out, touches)
 
 
+def localize_blocks(blocks, color_ptr, space: IndexSpace, rank: int):
+    """This rank's share of a coloured block list (la.color_blocks of the GLOBAL pattern: ``blocks`` colour-major, ``color_ptr`` the
+    block ranges per colour): the blocks whose dofs it owns, in local numbering, with a colour table of the SAME number of colours
+    (a colour may be empty here) -- every rank walks all colours, the halo of the iterate is exchanged before each
+    (csrc/blockpre.cu).  A block that straddles two ranks is refused: the partition must keep a facet's dofs together."""
+    out, ptr = [], [0]
+    for c in range(len(color_ptr) - 1):
+        for b in range(int(color_ptr[c]), int(color_ptr[c + 1])):
+            gids = torch.as_tensor(np.asarray(blocks[b], dtype=np.int64))
+            if gids.numel() == 0:
+                continue
+            owner, loc = space.lookup(gids)
+            mine = owner == rank
+            if bool(mine.all()):
+                out.append(loc.numpy().astype(np.int32))
+            elif bool(mine.any()):
+                raise ValueError("localize_blocks: block %d has dofs on ranks %s; blocks must not be cut by the row partition"
+                                 % (b, sorted(set(owner.tolist()))))
+        ptr.append(len(out))
+    return out, np.asarray(ptr, dtype=np.int64)
+
+
 @dataclass
 class DistributedCondensed:
     """Device side of a row-partitioned statically condensed form: an object with the attributes of a condensed BilinearForm
