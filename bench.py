@@ -324,6 +324,9 @@ def main():
                     help="N > 1: add the weak-scaling leg (--weak-dofs unknowns per GPU).  Off by default: its first run (4 GPUs) ran out of "
                          "device memory on one rank only and the other ranks then waited in a collective forever (DESIGN.md 6)")
     ap.add_argument("--weak-dofs", type=float, default=20e6, help="unknowns per GPU of the weak-scaling leg")
+    ap.add_argument("--no-precond", action="store_true", help="skip the preconditioner comparison leg (N = 1)")
+    ap.add_argument("--precond-dofs", type=float, default=2.0e6)
+    ap.add_argument("--precond-timeout", type=float, default=240.0)
     ap.add_argument("--leg-timeout", type=float, default=420.0,
                     help="seconds each optional leg after the headline may take before the run prints what it has and leaves (0 = no limit)")
     args = ap.parse_args()
@@ -628,6 +631,12 @@ def main():
                                 "sample": "C+OpenMP oracle port of bramblepasciak_new.py (oracle/c/krylov_omp.c), 20 iterations on the SAME "
                                           "%d-dof blocks the device solves (no dof scaling), best of 3, %d threads set explicitly"
                                           % (n_u + n_p, nt)}
+    # ---- the preconditioners that cut the iteration count (block smoother, auxiliary-space MypreA) beside Jacobi: time to tolerance
+    # at --precond-dofs, N = 1, in a process of its own, last -- whatever happens there costs only this key
+    if world == 1 and not args.no_precond:
+        torch.cuda.empty_cache()
+        with wd.leg("preconditioners"):
+            line["preconditioners"] = benchlegs.precond_leg(args.precond_dofs, args.precond_timeout)
     wd.emit()
     if world > 1:
         with wd.leg("teardown"):

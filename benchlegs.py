@@ -37,6 +37,30 @@ def guarded(fn, env, *a, **k):
         return {"error": ("%s: %s" % (type(ex).__name__, ex))[:300], "where": traceback.format_exc().strip().splitlines()[-2][:200]}
 
 
+def precond_leg(dofs, timeout_s):
+    """Time to tolerance with each device preconditioner for A (Jacobi, block Jacobi, symmetric block Gauss-Seidel, auxiliary-space
+    MypreA) at `dofs` unknowns, in a process of its own (benchlegs_precond.py): these paths have run on small meshes only, and a
+    crash or a hang there must cost this key, not the line."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.abspath(__file__))
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT")}
+    try:
+        res = subprocess.run([sys.executable, os.path.join(root, "benchlegs_precond.py"), "--dofs", repr(float(dofs))],
+                             capture_output=True, text=True, timeout=timeout_s, env=env, cwd=root)
+    except subprocess.TimeoutExpired:
+        return {"error": "benchlegs_precond.py did not finish within %.0f s" % timeout_s}
+    rows = [ln for ln in res.stdout.splitlines() if ln.startswith("{")]
+    if res.returncode != 0 or not rows:
+        return {"error": "benchlegs_precond.py exited %d" % res.returncode, "stderr_tail": res.stderr.strip()[-300:]}
+    try:
+        return json.loads(rows[-1])
+    except ValueError as ex:
+        return {"error": "unreadable output: %s" % ex}
+
+
 def _allreduce(env, t, op="sum"):
     if env.world > 1:
         env.dist.all_reduce(t, op=env.dist.ReduceOp.SUM if op == "sum" else env.dist.ReduceOp.MAX)

@@ -64,3 +64,22 @@ def test_leg_watchdog_is_silent_on_the_normal_path():
     assert r0.returncode == 0
     lines = [ln for ln in r0.stdout.splitlines() if ln.startswith("{")]
     assert len(lines) == 1 and "watchdog" not in json.loads(lines[0])      # emit() twice prints once
+
+
+def test_preconditioner_leg_failure_is_a_key_not_a_crash():
+    """bench.py's `preconditioners` leg runs in its own process; here (no GPU) that process refuses to start, and the leg must come back
+    with an error object instead of raising -- the same path a crash or a timeout of that process takes on the GPU box."""
+    sys.path.insert(0, ROOT)
+    import benchlegs
+    env_backup = os.environ.get("CUDA_VISIBLE_DEVICES")
+    os.environ["CUDA_VISIBLE_DEVICES"] = ""
+    try:
+        out = benchlegs.precond_leg(6e4, 300)
+    finally:
+        if env_backup is None:
+            os.environ.pop("CUDA_VISIBLE_DEVICES", None)
+        else:
+            os.environ["CUDA_VISIBLE_DEVICES"] = env_backup
+    assert "error" in out and "exited" in out["error"] and "CUDA" in out.get("stderr_tail", "")
+    out = benchlegs.precond_leg(6e4, 0.05)
+    assert "did not finish" in out["error"]
