@@ -152,6 +152,12 @@ def _bpcg_engine(A, B, preA, preM, f, g, sol_flat, n_u, n_p, k, tol, maxsteps, i
     return hist[:upd.value + 1], upd.value, secs.value, status.value
 
 
+def _require_device_blocks(A, B):
+    """No CPU fallback: anything that is not a device operator is refused before any of its attributes is used."""
+    if not (isinstance(A, (SparseMatrix, CondensedOperator)) and isinstance(B, SparseMatrix)):
+        raise TypeError("Bramble-Pasciak CG needs device SparseMatrix blocks (got %r, %r)" % (type(A), type(B)))
+
+
 def _owned(m):
     return m._halo.n_owned if getattr(m, "_halo", None) is not None else None
 
@@ -166,6 +172,7 @@ def bramble_pasciak_cg(a_matrix, b_matrix, c_matrix, pre_a, pre_schur_complement
     in place of NGSolve's EigenValues_Preconditioner (:70)."""
     if c_matrix is not None:
         raise NotImplementedError("c_matrix is None at every reference call site; a (2,2) block is not supported")
+    _require_device_blocks(a_matrix, b_matrix)
     n_u, n_p = a_matrix.height, b_matrix.height
     if lam_min is None:
         lams = EigenValues_Preconditioner(a_matrix, pre_a)                # :70
@@ -203,6 +210,7 @@ def BramblePasciakCG(blfA, blfB, matC, f, g, preA_unscaled, preM, sol=None, tol=
         matA = blfA if isinstance(blfA, CondensedOperator) else CondensedOperator.from_bilinear_form(blfA)
     else:
         matA = getattr(blfA, "mat", blfA)
+    _require_device_blocks(matA, matB)
     n_u, n_p = matA.height, matB.height
     if lam_min is None:
         lams = EigenValues_Preconditioner(matA, preA_unscaled, tol=1e-3)  # :115
