@@ -118,6 +118,27 @@ def main():
     m = min(30, len(h), len(h1))
     res.update(it=int(it), it1=int(it1), hist_rel=float(np.max(np.abs(h[:m] - h1[:m]) / np.abs(h1[:m]))),
                sol_rel=float(np.linalg.norm(sol - ref_own) / np.linalg.norm(ref_own)))
+    # MinRes on the stacked saddle operator with the block-diagonal preconditioner [[MypreA, 0], [0, Jacobi(Mp)]] (run.py:45-52)
+    import types
+    K1 = nsb.BlockMatrix([[A1, B1.T], [B1, None]])
+    C1 = nsb.BlockMatrix([[pre1[True], None], [None, pM1]])
+    msol1 = start.copy()
+    _, merr1 = quiet(nsb.MinRes, K1, np.concatenate([f, g]), C1, msol1, 3000, False, False, 1e-8)
+    Lloc = types.SimpleNamespace(plan_u=Lu.plan, plan_p=Lp.plan, A=Lu.ops[0], B=Lu.ops[1], BT=Lp.ops[0], n_u=Lu.plan.n_owned,
+                                 n_p=Lp.plan.n_owned)
+    Kl, kplan = P.local_saddle(Lloc)
+    hk = P.upload_halo(ctx, kplan)
+    KN = nsb.SparseMatrix.from_csr(Kl, ctx)
+    KN.set_row_panels([0, Lloc.n_u, Lloc.n_u + Lloc.n_p])
+    hk.attach(KN)
+    CN = nsb.BlockMatrix([[preN[True], None], [None, pMN]])
+    msol = np.concatenate([start[:G.n_u][ou], start[G.n_u:][op_]])
+    _, merr = quiet(nsb.MinRes, KN, np.concatenate([f[ou], g[op_]]), CN, msol, 3000, False, False, 1e-8)
+    mref = np.concatenate([msol1[:G.n_u][ou], msol1[G.n_u:][op_]])
+    mm = min(30, len(merr), len(merr1))
+    res.update(minres_it=len(merr) - 1, minres_it1=len(merr1) - 1,
+               minres_hist_rel=float(np.max(np.abs(np.array(merr[:mm]) - np.array(merr1[:mm])) / np.abs(np.array(merr1[:mm])))),
+               minres_sol_rel=float(np.linalg.norm(msol - mref) / np.linalg.norm(mref)))
     print("SMOOTHRESULT " + json.dumps(res), flush=True)
     dist.barrier()
     dist.destroy_process_group()

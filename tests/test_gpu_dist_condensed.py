@@ -73,3 +73,4 @@ def test_two_rank_block_smoother_and_auxspace(sell):
             assert r[k] < 1e-12, (k, r)
         assert abs(r["cg_it"] - r["cg_it1"]) <= 1 and r["cg_hist_rel"] < 1e-9 and r["cg_sol_rel"] < 1e-8, r
         assert abs(r["it"] - r["it1"]) <= 2 and r["hist_rel"] < 1e-9 and r["sol_rel"] < 1e-7, r
+        assert abs(r["minres_it"] - r["minres_it1"]) <= 1 and r["minres_hist_rel"] < 1e-9 and r["minres_sol_rel"] < 1e-7, r
