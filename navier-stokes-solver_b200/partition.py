@@ -211,6 +211,8 @@ def stokes_slab_spaces(cells, nslabs):
     synthetic.assemble_stokes: slab s owns the vertex planes [(c_x+1)s/P, (c_x+1)(s+1)/P) and the midpoint
     plane right of each; velocity dofs are component-major, so a slab owns d global ranges."""
     d = len(cells)
+    if nslabs > cells[0] + 1:
+        raise ValueError("stokes_slab_spaces: %d slabs for %d vertex planes in x -- a rank would own no rows" % (nslabs, cells[0] + 1))
     dims2 = [2 * c + 1 for c in cells]
     dims1 = [c + 1 for c in cells]
     n2 = int(np.prod(dims2))

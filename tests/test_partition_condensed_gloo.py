@@ -24,10 +24,10 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _global_case():
+def _global_case(cells=CELLS):
     import navier_stokes_solver_b200.synthetic as syn
     from oracle.cases import synthetic_condensation
-    G = syn.assemble_stokes(CELLS, LENGTHS)
+    G = syn.assemble_stokes(cells, LENGTHS)
     A, B, BT = G.A.to_scipy(), G.B.to_scipy(), G.BT.to_scipy()
     free = G.free_u.numpy().astype(bool)
     cd = synthetic_condensation(A, free)
@@ -129,3 +129,61 @@ def test_take_rows_and_compact_contract_single_process():
         P.distribute_operators([cd["HT"]], [su], su, 1, compact=[True], plan=plans[1])
     with pytest.raises(ValueError):
         P.distribute_operators([cd["H"]], [su], su, 0, compact=[True], plan=plans[0])
+
+
+def _simulate_exchange(plans, owned):
+    """The exchange of dist.cu / p2p.cu played in one process for every rank at once: rank q's tail is filled neighbour by neighbour
+    (q.neighbors order) with what that neighbour's send list for q selects from the neighbour's owned entries."""
+    out = []
+    for q, pq in enumerate(plans):
+        tail = []
+        for k, r in enumerate(pq.neighbors):
+            pr = plans[int(r)]
+            j = int(np.nonzero(pr.neighbors == q)[0][0])            # q must be in r's list: the plans are symmetric
+            s0 = int(pr.send_counts[:j].sum())
+            seg = pr.send_idx[s0:s0 + int(pr.send_counts[j])]
+            assert len(seg) == int(pq.recv_counts[k])
+            tail.append(owned[int(r)][seg])
+        out.append(np.concatenate([owned[q]] + tail) if tail else owned[q].copy())
+    return out
+
+
+@pytest.mark.parametrize("world", [4, 8])
+def test_condensed_chain_at_the_bench_world_sizes_planned_in_one_process(world):
+    """World sizes 4 and 8 (ranks with two neighbours) without spawning processes: the plans of every rank are built in one process
+    (partition.make_plans_single_process) and the exchange is played for all ranks at once."""
+    import navier_stokes_solver_b200.partition as P
+    cells = (16, 2, 2)                                              # 17 vertex planes: every one of 8 slabs owns rows
+    G, A, B, BT, free, cd = _global_case(cells)
+    su, sp_ = P.stokes_slab_spaces(cells, world)
+    names = ("mat", "H", "HT", "inner_solve", "inner_matrix")
+    need = [torch.as_tensor(np.concatenate([cd[k][su.owned_ids(r).numpy()].indices for k in names[:3]] +
+                                           [B[sp_.owned_ids(r).numpy()].indices]).astype(np.int64)) for r in range(world)]
+    plans = P.make_plans_single_process(su, need)
+    L = [P.distribute_operators([cd[k] for k in names] + [B], [su] * 5 + [sp_], su, r, compact=[False, False, False, True, True, False],
+                                plan=plans[r]) for r in range(world)]
+    ou = [su.owned_ids(r).numpy() for r in range(world)]
+    rng = np.random.default_rng(17)
+    x = rng.uniform(-1, 1, G.n_u)
+    ops = [[m.to_scipy() for m in Lr.ops] for Lr in L]
+    n = [p.n_owned for p in plans]
+    xl = _simulate_exchange(plans, [x[o] for o in ou])
+    t = [xl[r][:n[r]] - ops[r][1] @ xl[r] for r in range(world)]
+    tl = _simulate_exchange(plans, t)
+    q = [ops[r][0] @ tl[r] + ops[r][4] @ tl[r][:n[r]] for r in range(world)]
+    ql = _simulate_exchange(plans, q)
+    ref = A @ x
+    for r in range(world):
+        y = ql[r][:n[r]] - ops[r][2] @ ql[r]
+        assert np.abs(y - ref[ou[r]]).max() < 1e-12 * np.abs(ref).max()
+        nb = [int(v) for v in plans[r].neighbors]
+        assert nb == [v for v in (r - 1, r + 1) if 0 <= v < world]
+        opp = sp_.owned_ids(r).numpy()
+        assert np.abs(ops[r][5] @ xl[r] - (B @ x)[opp]).max() < 1e-12
+
+
+def test_more_slabs_than_vertex_planes_is_refused():
+    import navier_stokes_solver_b200.partition as P
+    with pytest.raises(ValueError, match="no rows"):
+        P.stokes_slab_spaces((6, 2, 2), 8)
+    P.stokes_slab_spaces((7, 2, 2), 8)
