@@ -325,8 +325,9 @@ def main():
                          "device memory on one rank only and the other ranks then waited in a collective forever (DESIGN.md 6)")
     ap.add_argument("--weak-dofs", type=float, default=20e6, help="unknowns per GPU of the weak-scaling leg")
     ap.add_argument("--no-precond", action="store_true", help="skip the preconditioner comparison leg (N = 1)")
-    ap.add_argument("--precond-dofs", type=float, default=2.0e6)
-    ap.add_argument("--precond-timeout", type=float, default=240.0)
+    ap.add_argument("--precond-dofs", type=float, default=1.0e6)
+    ap.add_argument("--precond-timeout", type=float, default=150.0,
+                    help="the preconditioner leg (own process) is abandoned after this many seconds: the default run stays within minutes")
     ap.add_argument("--leg-timeout", type=float, default=420.0,
                     help="seconds each optional leg after the headline may take before the run prints what it has and leaves (0 = no limit)")
     args = ap.parse_args()

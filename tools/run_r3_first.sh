@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 echo "== 1. verified suite (-x): the adaptor test (tests/test_gpu_y_adaptor.py) has never run on a device"
 timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
 echo "== 2. bench line with the preconditioner leg (own process, last)"
-timeout 1200 python bench.py --steps 5 --warmup 3 > gpurun_out/r3a_bench1.json 2> gpurun_out/r3a_bench1.err; echo "bench rc=$?"
+timeout 1200 python bench.py --steps 5 --warmup 3 --precond-dofs 2e6 --precond-timeout 400 > gpurun_out/r3a_bench1.json 2> gpurun_out/r3a_bench1.err; echo "bench rc=$?"
 python - <<'PY'
 import json
 d = json.loads(open("gpurun_out/r3a_bench1.json").read().strip().splitlines()[-1])
