@@ -276,6 +276,75 @@ def gold_mypreA():
     print("mypreA lines", node.lineno, node.end_lineno, "|y_gs|", float(np.linalg.norm(out["y_gs"])), "|y_add|", float(np.linalg.norm(out["y_add"])))
 
 
+def _reference_mypreA(c, GS):
+    """An instance of the reference's MypreA class (source cut out of the reference file, see gold_mypreA) on Case `c` with the
+    stand-in blocks / transform / coarse preconditioner; returns (instance, blocks in the colour-major order the device sweeps)."""
+    import ast
+    import textwrap
+    from navier_stokes_solver_b200.la import color_blocks
+    from oracle.cases import aggregation_transform, dof_blocks
+    path = os.path.join(REF, "templates", "NavierStokesSIMPLE_iterative.py")
+    src = open(path).read()
+    node = next(n for n in ast.walk(ast.parse(src)) if isinstance(n, ast.ClassDef) and n.name == "MypreA")
+    code = textwrap.dedent("\n".join(src.splitlines()[node.lineno - 1:node.end_lineno]))
+    T, Ac = aggregation_transform(c)
+    dc = 1.0 / Ac.diagonal()
+    blocks = dof_blocks(c, 4)
+    order, _ = color_blocks(c.A, blocks)
+    blocks = [blocks[i] for i in order]
+    ns = {"BaseMatrix": ngsolve.BaseMatrix, "transform": SparseMatrix(T), "preAh1": DiagonalMatrix(dc)}
+    exec(compile(code, path + ":MypreA", "exec"), ns)
+    space = type("Space", (), {"ndof": c.n_u})()
+    blf = type("Blf", (), {"mat": SparseMatrix(c.A), "space": space})()
+    return ns["MypreA"](space, blf, blocks, GS=GS), blocks, T, dc
+
+
+def gold_solvers_with_mypreA():
+    """The reference's solver loops with the reference's own MypreA as the velocity preconditioner, all unmodified:
+    BramblePasciakCG(..., preA, preM, ...) exactly as called at templates/NavierStokesSIMPLE_iterative.py:391-397, and MinRes with
+    BlockMatrix([[preA, None], [None, preM]]) (the run.py:46,52 pattern).  lambda_min of preA*A is computed densely (1274 free+fixed
+    velocity dofs) and injected with the factor 0.5 the device test uses."""
+    c = Case("chan2d")
+    out = dict(fingerprint=c.fingerprint())
+    for GS in (True, False):
+        tag = "gs" if GS else "add"
+        preA, blocks, T, dc = _reference_mypreA(c, GS)
+        n = c.n_u
+        P = np.zeros((n, n))
+        for j in range(n):
+            e = np.zeros(n)
+            e[j] = 1.0
+            y = BaseVector(np.zeros(n))
+            preA.Mult(BaseVector(e), y)
+            P[:, j] = y.NumPy()
+        lam_all = np.linalg.eigvals(P @ c.A.toarray()).real
+        lam = 0.5 * float(lam_all[np.abs(lam_all) > 1e-10 * np.abs(lam_all).max()].min())
+        A, B = SparseMatrix(c.A), SparseMatrix(c.B)
+
+        class Blf:
+            def __init__(self, m):
+                self.mat = m
+                self.condense = False
+        sol = BlockVector([BaseVector(c.u0.copy()), BaseVector(np.zeros(c.n_p))])
+        ngla.inject_eigenvalues([lam, 1.0])
+        (it, secs), txt = quiet(ref_bpcg2.BramblePasciakCG, Blf(A), Blf(B), None, BaseVector(c.f.copy()), BaseVector(c.g.copy()), preA,
+                                DiagonalMatrix(c.dM), sol, initialize=False, tol=1e-10, maxsteps=20000, rel_err=True)
+        hist = [float(m.group(2)) for m in re.finditer(r"it =\s+(\d+)\s+err =\s+(\S+)", txt)]
+        out.update({"lam_" + tag: lam, "bpcg_it_" + tag: it, "bpcg_hist_" + tag: np.array(hist), "bpcg_sol_" + tag: sol.NumPy().copy(),
+                    "bpcg_err0_" + tag: float(re.search(r"err0 (\S+)", txt).group(1))})
+        # MinRes on K with the block-diagonal preconditioner
+        K = BlockMatrix([[A, B.T], [B, None]])
+        C = BlockMatrix([[preA, None], [None, DiagonalMatrix(c.dM)]])
+        msol = BlockVector([BaseVector(c.u0.copy()), BaseVector(np.zeros(c.n_p))])
+        (u, errors), _ = quiet(ref_minres.MinRes, mat=K, pre=C, rhs=BlockVector([BaseVector(c.f.copy()), BaseVector(c.g.copy())]),
+                               sol=msol, initialize=False, tol=1e-8, maxsteps=5000)
+        out.update({"minres_errors_" + tag: np.array(errors), "minres_sol_" + tag: msol.NumPy().copy()})
+        print("solvers_mypreA", tag, "lam", lam, "bpcg it", it, "minres iterations", len(errors) - 1, "final", errors[-1])
+    out["block_ptr"] = np.concatenate([[0], np.cumsum([len(b) for b in blocks])])
+    out["block_dofs"] = np.concatenate(blocks)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "solvers_mypreA"), **out)
+
+
 def gold_orth():
     rng = np.random.default_rng(7)
     n, m = 777, 5
@@ -328,3 +397,4 @@ if __name__ == "__main__":
     gold_heat()
     gold_simple()
     gold_mypreA()
+    gold_solvers_with_mypreA()
