@@ -78,3 +78,64 @@ def test_rk_host_algebra_matches_golden():
         np.testing.assert_allclose(w.b, gold["b%d" % deg], rtol=1e-12, atol=1e-15)
         nxt = linear_implicit_runge_kutta_step(w, gold["evo%d" % deg], gold["y%d" % deg], 0.01)
         np.testing.assert_allclose(nxt, gold["next%d" % deg], rtol=1e-10)
+
+
+def _header_params():
+    """name -> list of parameter type strings of every NSB_API declaration in include/nsb200.h."""
+    src = open(os.path.join(ROOT, "include", "nsb200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    out = {}
+    for m in re.finditer(r"^NSB_API\s+([\w\s\*]+?)\b(nsb_\w+)\s*\(([^;]*?)\)\s*;", src, flags=re.M | re.S):
+        params = [p.strip() for p in " ".join(m.group(3).split()).split(",")]
+        if params == ["void"] or params == [""]:
+            params = []
+        out[m.group(2)] = (m.group(1).strip(), params)
+    return out
+
+
+def _klass_of_c(decl):
+    """pointer / float / int class of a C parameter or return declaration."""
+    handles = ("nsb_ctx", "nsb_mat", "nsb_pre", "nsb_halo", "nsb_cond", "nsb_simple")
+    if "*" in decl or "[" in decl or any(re.search(r"\b%s\b" % h, decl) for h in handles):
+        return "ptr"
+    if re.search(r"\bdouble\b", decl):
+        return "float"
+    return "int"
+
+
+def _klass_of_ctypes(t):
+    if t in (ctypes.c_double, ctypes.c_float):
+        return "float"
+    if t in (ctypes.c_int, ctypes.c_int64, ctypes.c_uint64, ctypes.c_int32):
+        return "int"
+    return "ptr"        # c_void_p, c_char_p, POINTER(...)
+
+
+def test_ctypes_argument_lists_match_the_header_parameter_by_parameter():
+    """Arity and pointer / integer / double class of every parameter: an ABI drift between include/nsb200.h and the ctypes table (a
+    forgotten argument, a double passed as an int) shows up here instead of as a crash on the GPU box."""
+    from navier_stokes_solver_b200 import _lib
+    decls = _header_params()
+    assert sorted(decls) == sorted(_lib.SIGNATURES)
+    for name, (ret, params) in decls.items():
+        res, args = _lib.SIGNATURES[name]
+        assert len(args) == len(params), (name, params, args)
+        for k, (p, a) in enumerate(zip(params, args)):
+            assert _klass_of_c(p) == _klass_of_ctypes(a), (name, k, p, a)
+        # 64-bit integers must not be declared as c_int (and vice versa)
+        for k, (p, a) in enumerate(zip(params, args)):
+            if _klass_of_c(p) == "int":
+                assert (a is ctypes.c_int64) == bool(re.search(r"\bint64_t\b", p)), (name, k, p, a)
+        want_ret = "ptr" if ("*" in ret or "char" in ret) else ("int" if re.search(r"\bint(64_t)?\b", ret) else "ptr")
+        assert _klass_of_ctypes(res) == want_ret, (name, ret, res)
+
+
+def test_integration_stub_matches_the_header():
+    """The binding INTEGRATION.md shows a reference maintainer (section 2) declares the same arities as the header."""
+    text = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    decls = _header_params()
+    found = re.findall(r"lib\.(nsb_\w+)\.argtypes\s*=\s*\[(.*?)\]", text, flags=re.S)
+    assert len(found) >= 5
+    for name, body in found:
+        n = len([x for x in re.sub(r"C\.POINTER\(([^)]*)\)", r"PTR", body).split(",") if x.strip()])
+        assert name in decls and n == len(decls[name][1]), (name, n, decls.get(name))
