@@ -139,3 +139,26 @@ def test_integration_stub_matches_the_header():
     for name, body in found:
         n = len([x for x in re.sub(r"C\.POINTER\(([^)]*)\)", r"PTR", body).split(",") if x.strip()])
         assert name in decls and n == len(decls[name][1]), (name, n, decls.get(name))
+
+
+def test_every_python_call_into_the_library_passes_the_declared_number_of_arguments():
+    """Static pass over the host mirror: each `<lib>.nsb_*(...)` call site passes as many positional arguments as the ctypes table
+    declares (ctypes only complains at call time, i.e. on the GPU box)."""
+    import ast
+    from navier_stokes_solver_b200 import _lib
+    pkg = os.path.join(ROOT, "navier-stokes-solver_b200")
+    files = [os.path.join(pkg, f) for f in os.listdir(pkg) if f.endswith(".py")] + [os.path.join(ROOT, f) for f in ("bench.py", "benchlegs.py")]
+    seen = 0
+    for path in files:
+        tree = ast.parse(open(path).read())
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute) and node.func.attr.startswith("nsb_"):
+                name = node.func.attr
+                assert name in _lib.SIGNATURES, (path, node.lineno, name)
+                if any(isinstance(a, ast.Starred) for a in node.args):
+                    fixed = sum(1 for a in node.args if not isinstance(a, ast.Starred))
+                    assert fixed <= len(_lib.SIGNATURES[name][1])
+                else:
+                    assert len(node.args) == len(_lib.SIGNATURES[name][1]) and not node.keywords, (path, node.lineno, name, len(node.args))
+                seen += 1
+    assert seen >= 40
