@@ -1,0 +1,94 @@
+"""Undefined-name pass over the Python that only ever runs on the GPU box (bench legs, torchrun workers, GPU tests, the device side of
+the host mirror): a name that is read in a function must be bound in that function, an enclosing one, the module, or builtins.  No
+linter is installed in the image; this is the part of one that matters for code the CPU suite cannot execute."""
+import ast
+import builtins
+import os
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _bound_in(node):
+    """Names bound anywhere inside `node` without descending into nested function / class bodies (their names are their own)."""
+    out = set()
+
+    def visit(n, top):
+        if isinstance(n, (ast.FunctionDef, ast.AsyncFunctionDef, ast.ClassDef)) and not top:
+            out.add(n.name)
+            return
+        if isinstance(n, ast.Lambda) and not top:
+            return
+        if isinstance(n, ast.Name) and isinstance(n.ctx, (ast.Store, ast.Del)):
+            out.add(n.id)
+        elif isinstance(n, (ast.Import, ast.ImportFrom)):
+            for a in n.names:
+                out.add((a.asname or a.name).split(".")[0])
+        elif isinstance(n, ast.ExceptHandler) and n.name:
+            out.add(n.name)
+        elif isinstance(n, (ast.Global, ast.Nonlocal)):
+            out.update(n.names)
+        elif isinstance(n, ast.arguments):
+            for a in n.posonlyargs + n.args + n.kwonlyargs + ([n.vararg] if n.vararg else []) + ([n.kwarg] if n.kwarg else []):
+                out.add(a.arg)
+        for c in ast.iter_child_nodes(n):
+            visit(c, False)
+    visit(node, True)
+    return out
+
+
+def undefined_names(path):
+    tree = ast.parse(open(path).read(), path)
+    module = _bound_in(tree) | set(dir(builtins)) | {"__file__", "__name__", "__doc__"}
+    bad = []
+
+    def walk(node, scopes):
+        for child in ast.iter_child_nodes(node):
+            if isinstance(child, (ast.FunctionDef, ast.AsyncFunctionDef, ast.Lambda)):
+                inner = scopes + [_bound_in(child)]
+                for d in getattr(child, "decorator_list", []):
+                    walk_expr(d, scopes)
+                for dflt in child.args.defaults + [k for k in child.args.kw_defaults if k is not None]:
+                    walk_expr(dflt, scopes)
+                walk(child, inner)
+            elif isinstance(child, ast.ClassDef):
+                walk(child, scopes + [_bound_in(child)])
+            elif isinstance(child, ast.Name) and isinstance(child.ctx, ast.Load):
+                if not any(child.id in s for s in scopes):
+                    bad.append((child.lineno, child.id))
+            else:
+                walk(child, scopes)
+
+    def walk_expr(expr, scopes):
+        for n in ast.walk(expr):
+            if isinstance(n, ast.Name) and isinstance(n.ctx, ast.Load) and not any(n.id in s for s in scopes):
+                bad.append((n.lineno, n.id))
+    walk(tree, [module])
+    return bad
+
+
+def _targets():
+    pkg = os.path.join(ROOT, "navier-stokes-solver_b200")
+    files = [os.path.join(pkg, f) for f in sorted(os.listdir(pkg)) if f.endswith(".py")]
+    files += [os.path.join(ROOT, f) for f in ("bench.py", "benchlegs.py", "benchlegs_precond.py", "__graft_entry__.py")]
+    files += [os.path.join(ROOT, "tests", f) for f in sorted(os.listdir(os.path.join(ROOT, "tests")))
+              if f.endswith(".py") and (f.startswith(("dist_", "test_gpu_", "test_zz_")) or f == "conftest.py")]
+    files += [os.path.join(ROOT, "tools", f) for f in sorted(os.listdir(os.path.join(ROOT, "tools"))) if f.endswith(".py")]
+    return files
+
+
+@pytest.mark.parametrize("path", _targets(), ids=lambda p: os.path.relpath(p, ROOT))
+def test_no_undefined_names(path):
+    assert undefined_names(path) == []
+
+
+def test_the_pass_sees_what_it_should():
+    import tempfile
+    src = "import os\ndef f(a):\n    b = a + missing\n    return [q for q in range(b)] + [os.sep, later]\ndef g():\n    return f(undefined_too)\nlater = 1\n"
+    with tempfile.NamedTemporaryFile("w", suffix=".py", delete=False) as t:
+        t.write(src)
+    try:
+        assert sorted(n for _, n in undefined_names(t.name)) == ["missing", "undefined_too"]
+    finally:
+        os.unlink(t.name)
