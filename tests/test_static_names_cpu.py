@@ -92,3 +92,45 @@ def test_the_pass_sees_what_it_should():
         assert sorted(n for _, n in undefined_names(t.name)) == ["missing", "undefined_too"]
     finally:
         os.unlink(t.name)
+
+
+def _own_module_attribute_misses(path):
+    """`alias.attr` where alias is one of this repo's modules imported in the file: the attribute must exist on the module."""
+    import importlib
+    import sys
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    tree = ast.parse(open(path).read(), path)
+    own = ("navier_stokes_solver_b200", "benchlegs", "bench", "oracle", "test_partition_smoother_gloo", "test_partition_condensed_gloo")
+    alias = {}
+    for n in ast.walk(tree):
+        if isinstance(n, ast.Import):
+            for a in n.names:
+                if a.name.split(".")[0] in own:
+                    alias[a.asname or a.name.split(".")[0]] = a.name if a.asname else a.name.split(".")[0]
+        elif isinstance(n, ast.ImportFrom) and n.module and n.module.split(".")[0] in own and n.level == 0:
+            for a in n.names:
+                try:
+                    sub = importlib.import_module(n.module + "." + a.name)
+                    alias[a.asname or a.name] = sub.__name__
+                except ImportError:
+                    mod = importlib.import_module(n.module)
+                    if not hasattr(mod, a.name):
+                        return [(n.lineno, n.module + "." + a.name)]
+    misses = []
+    for n in ast.walk(tree):
+        if isinstance(n, ast.Attribute) and isinstance(n.value, ast.Name) and n.value.id in alias:
+            mod = importlib.import_module(alias[n.value.id])
+            if not hasattr(mod, n.attr):
+                try:
+                    importlib.import_module(alias[n.value.id] + "." + n.attr)       # a submodule not yet imported
+                except ImportError:
+                    misses.append((n.lineno, n.value.id + "." + n.attr))
+    return misses
+
+
+@pytest.mark.parametrize("path", _targets(), ids=lambda p: os.path.relpath(p, ROOT))
+def test_attributes_of_own_modules_exist(path):
+    if os.path.basename(path) in ("build.py",):
+        pytest.skip("no own-module attribute access")
+    assert _own_module_attribute_misses(path) == []
