@@ -134,3 +134,52 @@ def test_attributes_of_own_modules_exist(path):
     if os.path.basename(path) in ("build.py",):
         pytest.skip("no own-module attribute access")
     assert _own_module_attribute_misses(path) == []
+
+
+def _own_call_signature_misses(path):
+    """Calls `alias.fn(...)` / `alias.Class(...)` into this repo's own modules must bind to the callee's signature (number of positional
+    arguments, keyword names)."""
+    import importlib
+    import inspect
+    import sys
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    tree = ast.parse(open(path).read(), path)
+    own = ("navier_stokes_solver_b200", "benchlegs", "bench", "oracle", "test_partition_smoother_gloo", "test_partition_condensed_gloo")
+    alias, direct = {}, {}
+    for n in ast.walk(tree):
+        if isinstance(n, ast.Import):
+            for a in n.names:
+                if a.name.split(".")[0] in own:
+                    alias[a.asname or a.name.split(".")[0]] = a.name if a.asname else a.name.split(".")[0]
+        elif isinstance(n, ast.ImportFrom) and n.module and n.module.split(".")[0] in own and n.level == 0:
+            for a in n.names:
+                try:
+                    alias[a.asname or a.name] = importlib.import_module(n.module + "." + a.name).__name__
+                except ImportError:
+                    direct[a.asname or a.name] = getattr(importlib.import_module(n.module), a.name, None)
+    misses = []
+    for n in ast.walk(tree):
+        if not isinstance(n, ast.Call):
+            continue
+        callee = None
+        if isinstance(n.func, ast.Attribute) and isinstance(n.func.value, ast.Name) and n.func.value.id in alias:
+            callee = getattr(importlib.import_module(alias[n.func.value.id]), n.func.attr, None)
+        elif isinstance(n.func, ast.Name) and n.func.id in direct:
+            callee = direct[n.func.id]
+        if callee is None or not (inspect.isfunction(callee) or inspect.isclass(callee)):
+            continue
+        if any(isinstance(a, ast.Starred) for a in n.args) or any(k.arg is None for k in n.keywords):
+            continue
+        try:
+            sig = inspect.signature(callee)
+            sig.bind(*[None] * len(n.args), **{k.arg: None for k in n.keywords})
+        except (TypeError, ValueError) as ex:
+            if isinstance(ex, TypeError):
+                misses.append((n.lineno, getattr(callee, "__name__", "?"), str(ex)))
+    return misses
+
+
+@pytest.mark.parametrize("path", _targets(), ids=lambda p: os.path.relpath(p, ROOT))
+def test_calls_into_own_modules_bind_to_their_signatures(path):
+    assert _own_call_signature_misses(path) == []
