@@ -83,3 +83,11 @@ def test_preconditioner_leg_failure_is_a_key_not_a_crash():
     assert "error" in out and "exited" in out["error"] and "CUDA" in out.get("stderr_tail", "")
     out = benchlegs.precond_leg(6e4, 0.05)
     assert "did not finish" in out["error"]
+
+
+def test_reference_arm_on_a_rank_other_than_zero_exits_quietly():
+    """Under torchrun (N > 1) rank 0 alone runs and prints the reference arm; the other ranks exit 0 without work or output."""
+    env = dict(os.environ, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2", CUDA_VISIBLE_DEVICES="")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "2", "--warmup", "1"],
+                         capture_output=True, text=True, timeout=120, env=env, cwd=ROOT)
+    assert res.returncode == 0 and res.stdout.strip() == ""
