@@ -404,6 +404,35 @@ def distribute_operators(ops, row_spaces, col_space: IndexSpace, rank: int, grou
     return LocalOperators(plan, out, touches)
 
 
+def balanced_row_space(rowptr, nranks: int) -> IndexSpace:
+    """One contiguous range of rows per rank, balanced by stored nonzeros (SpMV work and HBM bytes follow nnz, not rows): the cut
+    after rank r is the first row at which the running nnz reaches (r+1)/nranks of the total.  For operators exported from an
+    unstructured mesh (the reference's Netgen meshes), where no slab structure exists."""
+    rp = np.asarray(rowptr.cpu().numpy() if isinstance(rowptr, torch.Tensor) else rowptr, dtype=np.int64)
+    n = len(rp) - 1
+    if nranks > n:
+        raise ValueError("balanced_row_space: %d ranks for %d rows -- a rank would own no rows" % (nranks, n))
+    total = int(rp[-1])
+    cuts = [0]
+    for r in range(1, nranks):
+        c = int(np.searchsorted(rp, total * r / nranks, side="left"))
+        c = min(max(c, cuts[-1] + 1), n - (nranks - r))          # every rank keeps at least one row
+        cuts.append(c)
+    cuts.append(n)
+    return IndexSpace([[(cuts[r], cuts[r + 1])] for r in range(nranks)])
+
+
+def bandwidth_reducing_order(pattern) -> np.ndarray:
+    """Reverse Cuthill-McKee permutation of a symmetric sparsity pattern (scipy): rows that couple end up close together, so contiguous
+    row ranges cut few couplings.  Apply it to every operator of the space (``M[perm][:, perm]``) and to the vectors before
+    ``balanced_row_space`` / ``distribute_operators``; a mesh numbered by a mesh generator needs it, the structured channel does not."""
+    import scipy.sparse as sp
+    from scipy.sparse.csgraph import reverse_cuthill_mckee
+    P = sp.csr_matrix(pattern)
+    P = (abs(P) + abs(P).T).tocsr()
+    return np.asarray(reverse_cuthill_mckee(P, symmetric_mode=True), dtype=np.int64)
+
+
 def localize_blocks(blocks, color_ptr, space: IndexSpace, rank: int):
     """This rank's share of a coloured block list (la.color_blocks of the GLOBAL pattern: ``blocks`` colour-major, ``color_ptr`` the
     block ranges per colour): the blocks whose dofs it owns, in local numbering, with a colour table of the SAME number of colours

@@ -82,3 +82,37 @@ def test_stacked_plan_delivers_what_the_two_plans_deliver(seed, world):
         tail = xl[r][d["n_owned"]:]
         np.testing.assert_array_equal(tail[tails[0]], xu[pu[r].halo_gids.numpy()])
         np.testing.assert_array_equal(tail[tails[1]], xp[pp[r].halo_gids.numpy()])
+
+
+def test_unstructured_numbering_nnz_balance_and_bandwidth_reduction():
+    """Operators from a mesh generator come in an arbitrary numbering: partition.bandwidth_reducing_order (RCM) + balanced_row_space
+    give contiguous ranges with balanced nonzeros and a small interface, and the exchanged product still equals the global one."""
+    import navier_stokes_solver_b200.partition as P
+    import navier_stokes_solver_b200.synthetic as syn
+    G = syn.assemble_stokes((10, 4, 4), (2.5, 0.41, 0.41))
+    A = G.A.to_scipy()
+    n = A.shape[0]
+    rng = np.random.default_rng(3)
+    shuffle = rng.permutation(n)                                    # "mesh generator" numbering
+    As = A[shuffle][:, shuffle].tocsr()
+    world = 4
+    halo = {}
+    for name, M in (("shuffled", As), ("rcm", None)):
+        if M is None:
+            perm = P.bandwidth_reducing_order(As)
+            M = As[perm][:, perm].tocsr()
+        M.sort_indices()
+        space = P.balanced_row_space(M.indptr, world)
+        need = [torch.as_tensor(M[space.owned_ids(r).numpy()].indices.astype(np.int64)) for r in range(world)]
+        plans = P.make_plans_single_process(space, need)
+        nnz = [int(M[space.owned_ids(r).numpy()].nnz) for r in range(world)]
+        assert max(nnz) < 1.1 * M.nnz / world                        # balanced by nonzeros
+        halo[name] = sum(p.n_halo for p in plans)
+        x = rng.uniform(-1, 1, n)
+        xl = _simulate_exchange(plans, [x[space.owned_ids(r).numpy()] for r in range(world)])
+        for r in range(world):
+            L = P.distribute_operators([M], [space], space, r, plan=plans[r])
+            np.testing.assert_allclose(L.ops[0].to_scipy() @ xl[r], (M @ x)[space.owned_ids(r).numpy()], rtol=0, atol=1e-10)
+    assert halo["rcm"] < 0.25 * halo["shuffled"], halo                # the ordering is what makes contiguous ranges cheap
+    with pytest.raises(ValueError):
+        P.balanced_row_space(np.arange(4), 5)
