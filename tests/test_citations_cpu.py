@@ -37,14 +37,17 @@ def test_reference_citations_point_inside_the_reference(path):
     _index()
     text = open(path, errors="replace").read()
     bad = []
-    # name.py:12, name.py:12-34, dir/name.py:12,56-78   (first number group only: the rest of a comma list repeats the file)
-    for m in re.finditer(r"((?:[\w\-]+/)*[\w\-]+\.py):(\d+)(?:-(\d+))?", text):
-        rel, a, b = m.group(1), int(m.group(2)), int(m.group(3) or m.group(2))
+    # name.py:12, name.py:12-34, dir/name.py:12,56-78
+    for m in re.finditer(r"((?:[\w\-]+/)*[\w\-]+\.py):(\d+(?:-\d+)?(?:,\d+(?:-\d+)?)*)", text):
+        rel = m.group(1)
         base = os.path.basename(rel)
         if base not in KNOWN:
             continue                                     # a file of this repo (tests/..., oracle/...), not a reference citation
         cands = [p for p in KNOWN[base] if p.endswith(rel)] or KNOWN[base]
         nlines = max(sum(1 for _ in open(os.path.join(REF, p), errors="replace")) for p in cands)
-        if not (1 <= a <= b <= nlines):
-            bad.append((m.group(0), nlines))
+        for part in m.group(2).split(","):               # 96,126,145-146: every member of a comma list (no spaces) is checked
+            a, _, b = part.partition("-")
+            a, b = int(a), int(b or a)
+            if not (1 <= a <= b <= nlines):
+                bad.append((rel + ":" + part, nlines))
     assert bad == []
