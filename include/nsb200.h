@@ -56,7 +56,10 @@ typedef struct nsb_halo_s* nsb_halo;
 typedef struct nsb_cond_s* nsb_cond;
 typedef struct nsb_simple_s* nsb_simple;
 
-/* ---- library / context ------------------------------------------------------------------- */
+/* ---- library / context -------------------------------------------------------------------
+ * Infrastructure with no counterpart in the reference (one Python process over NGSolve, no FFI): what SURVEY.md 8(b) "What a
+ * C-ABI replacement must export" lists as items 1 (context: device, stream) and 5 (last-error string), plus the diagnostics
+ * bench.py reads (launch counter, synchronisation statistics, CUDA-graph switch). */
 NSB_API int nsb_version(void);
 NSB_API const char* nsb_last_error(void);
 
@@ -94,7 +97,7 @@ NSB_API int nsb_csr_transpose(nsb_ctx ctx, nsb_mat a, nsb_mat* out);
 NSB_API int nsb_saddle_create(nsb_ctx ctx, nsb_mat A, nsb_mat B, nsb_mat BT, nsb_mat C, nsb_mat* out);
 NSB_API int nsb_mat_destroy(nsb_mat m);
 NSB_API int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz);
-/* storage actually used by the SpMV kernels: rows_per_chunk > 0 when the SELL-LX companion (rows sorted by
+/* (no reference counterpart: NGSolve hides its storage)  storage actually used by the SpMV kernels: rows_per_chunk > 0 when the SELL-LX companion (rows sorted by
  * length inside chunks, sliced-ELL pair-blocks, x staged in shared memory, 16-bit chunk-local column indices)
  * is active, else the CSR-vector kernel runs.  total_distinct = sum over chunks of distinct columns (4 B each
  * of extra index traffic per SpMV); stored_nnz = nonzeros including slice padding; lanes_per_row = lanes that
@@ -102,11 +105,11 @@ NSB_API int nsb_mat_info(nsb_mat m, int64_t* rows, int64_t* cols, int64_t* nnz);
  * of consecutive columns (8 B per run instead of 4 B per column). */
 NSB_API int nsb_mat_format(nsb_mat m, int* rows_per_chunk, int* chunks, int* max_distinct, int64_t* total_distinct,
                            int* lanes_per_row, int64_t* stored_nnz, int64_t* column_runs);
-/* Row panels: rows [bounds[k], bounds[k+1]) get their own SELL-LX shape (chunk size, lanes per row).  For operators whose
+/* (no reference counterpart)  Row panels: rows [bounds[k], bounds[k+1]) get their own SELL-LX shape (chunk size, lanes per row).  For operators whose
  * row blocks differ strongly in length, e.g. the stacked local rows [[A, B^T], [B, 0]] of a row-partitioned saddle-point
  * operator (nsb_saddle_create does this by itself).  Rebuilds the SpMV storage. */
 NSB_API int nsb_mat_set_row_panels(nsb_ctx ctx, nsb_mat m, int nbounds, const int64_t* bounds);
-/* main diagonal of a square (or owned-square) operator, length rows */
+/* main diagonal of a square (or owned-square) operator, length rows: what Preconditioner(bf, 'local') inverts (run.py:62) */
 NSB_API int nsb_mat_diagonal(nsb_ctx ctx, nsb_mat m, double* out);
 /* y = M x   (the `mat * vec` primitive, e.g. minres.py:97).  x has `cols`, y has `rows` entries. */
 NSB_API int nsb_spmv(nsb_ctx ctx, nsb_mat m, const double* x, double* y);
@@ -124,9 +127,10 @@ NSB_API int nsb_mat_set_halo(nsb_mat m, nsb_halo h);
 
 /* ---- preconditioners: replaces Preconditioner(bf, 'local') and block smoothers
  *      (run.py:61-62, stokes_hcurldiv.py:53, NavierStokesSIMPLE_iterative.py:199,360-373) -------- */
-/* y = d .* x with caller-supplied d (already inverted; zero on constrained dofs) */
+/* y = d .* x with caller-supplied d (already inverted; zero on constrained dofs): Preconditioner(bf, 'local') restricted to
+ * FreeDofs (run.py:61-62), the diagonal taken on the host */
 NSB_API int nsb_pre_create_diag(nsb_ctx ctx, int64_t n, const double* d, nsb_pre* out);
-/* Jacobi from the operator's diagonal; free_mask (n bytes, 1 = free) may be NULL */
+/* the same from the device operator's diagonal (run.py:62, stokes_hcurldiv.py:53); free_mask (n bytes, 1 = free: fes.FreeDofs()) may be NULL */
 NSB_API int nsb_pre_create_jacobi(nsb_ctx ctx, nsb_mat m, const uint8_t* free_mask, nsb_pre* out);
 /* BlockMatrix([[preA, None], [None, preS]]) (run.py:46).  Two diagonal preconditioners are merged into one diagonal; with a
  * block smoother / auxiliary-space composite in either block the result applies them block by block and borrows the two handles
