@@ -438,21 +438,27 @@ def localize_blocks(blocks, color_ptr, space: IndexSpace, rank: int):
     block ranges per colour): the blocks whose dofs it owns, in local numbering, with a colour table of the SAME number of colours
     (a colour may be empty here) -- every rank walks all colours, the halo of the iterate is exchanged before each
     (csrc/blockpre.cu).  A block that straddles two ranks is refused: the partition must keep a facet's dofs together."""
-    out, ptr = [], [0]
-    for c in range(len(color_ptr) - 1):
-        for b in range(int(color_ptr[c]), int(color_ptr[c + 1])):
-            gids = torch.as_tensor(np.asarray(blocks[b], dtype=np.int64))
-            if gids.numel() == 0:
-                continue
-            owner, loc = space.lookup(gids)
-            mine = owner == rank
-            if bool(mine.all()):
-                out.append(loc.numpy().astype(np.int32))
-            elif bool(mine.any()):
-                raise ValueError("localize_blocks: block %d has dofs on ranks %s; blocks must not be cut by the row partition"
-                                 % (b, sorted(set(owner.tolist()))))
-        ptr.append(len(out))
-    return out, np.asarray(ptr, dtype=np.int64)
+    nb = len(blocks)
+    sizes = np.array([len(b) for b in blocks], dtype=np.int64)
+    ncol = len(color_ptr) - 1
+    if nb == 0 or int(sizes.sum()) == 0:
+        return [], np.zeros(ncol + 1, dtype=np.int64)
+    dofs = np.concatenate([np.asarray(b, dtype=np.int64) for b in blocks])
+    owner, loc = space.lookup(torch.as_tensor(dofs))            # one lookup for all blocks
+    owner, loc = owner.numpy(), loc.numpy()
+    ptr = np.concatenate([[0], np.cumsum(sizes)])
+    bid = np.repeat(np.arange(nb), sizes)
+    mine_cnt = np.bincount(bid, weights=(owner == rank).astype(np.float64), minlength=nb).astype(np.int64)
+    cut = np.nonzero((mine_cnt > 0) & (mine_cnt < sizes))[0]
+    if cut.size:
+        b = int(cut[0])
+        raise ValueError("localize_blocks: block %d has dofs on ranks %s; blocks must not be cut by the row partition"
+                         % (b, sorted(set(owner[ptr[b]:ptr[b + 1]].tolist()))))
+    keep = (mine_cnt == sizes) & (sizes > 0)
+    out = [loc[ptr[b]:ptr[b + 1]].astype(np.int32) for b in np.nonzero(keep)[0]]
+    kept_before = np.concatenate([[0], np.cumsum(keep)])         # blocks kept among the first k
+    lptr = np.array([kept_before[int(color_ptr[c])] for c in range(ncol + 1)], dtype=np.int64)
+    return out, lptr
 
 
 @dataclass
