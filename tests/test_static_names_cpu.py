@@ -75,6 +75,7 @@ def _targets():
     files += [os.path.join(ROOT, "tests", f) for f in sorted(os.listdir(os.path.join(ROOT, "tests")))
               if f.endswith(".py") and (f.startswith(("dist_", "test_gpu_", "test_zz_")) or f == "conftest.py")]
     files += [os.path.join(ROOT, "tools", f) for f in sorted(os.listdir(os.path.join(ROOT, "tools"))) if f.endswith(".py")]
+    files += [os.path.join(ROOT, "examples", f) for f in sorted(os.listdir(os.path.join(ROOT, "examples"))) if f.endswith(".py")]
     return files
 
 
