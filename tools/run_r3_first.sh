@@ -18,6 +18,8 @@ PY
 echo "== 3. ncu launch list of the preconditioner leg alone (which kernel of the block sweeps costs what)"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/r3a_precond_launches.csv \
     python benchlegs_precond.py --dofs 2e6 --which block_gs --maxsteps 20 > gpurun_out/r3a_precond_ncu.log 2>&1; echo "ncu rc=$?"
+echo "== 3b. the drop-in example (never run on a device)"
+timeout 300 python examples/stokes_channel.py --csv gpurun_out/r3a_example_errors.csv 2>&1 | tail -4
 if [ "$N" -ge 2 ]; then
   echo "== 4. row-partitioned condensed BPCG / block smoother / MypreA / MinRes with the composite: first run on a device"
   NSB_RUN_UNVERIFIED_GPU_TESTS=1 timeout 1500 python -m pytest tests/test_gpu_dist_condensed.py -m gpu -x -q 2>&1 | tail -15
