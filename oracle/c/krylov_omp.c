@@ -1,7 +1,8 @@
 /* krylov_omp.c -- CPU oracle, C + OpenMP restatement of the reference's Krylov hot path.
  *
  * TEST INFRASTRUCTURE.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
- * `--impl reference` legs may load this library; the product (libnsb200.so) never does.
+ * `--impl reference` legs (and its parity objects, where this is the checker of the device result) may load this library; the
+ * product (libnsb200.so) never does.
  *
  * Purpose: the reference runs its loops line by line through NGSolve, which executes every vector
  * expression and every sparse MultAdd as one multi-threaded primitive inside `with TaskManager():`
